@@ -1,0 +1,337 @@
+// bfs_enactor.cuh -- the host loop of (direction-optimising) BFS.
+//
+// Counterpart of the reference's BFSEnactor::EnactBFS (gunrock/app/bfs/
+// bfs_enactor.cuh:208-553) and DOBFSEnactor::EnactDOBFS (app/dobfs/
+// dobfs_enactor.cuh:207-747).  Per level the reference issues advance (4-5
+// launches in LB mode) + filter and crosses the PCIe bus three times (two
+// blocking 4-byte memcpys and a mapped flag), and this
+// fork adds an RPC + relaunch loop; its DOBFS needs four extra filter passes
+// to move between queue and bool-map form.
+//
+// Here a level is
+//     push:  [ScanKernel +] ExpandKernel  or  twc::Kernel     (fused advance + filter)
+//     pull:  pull::Kernel                                     (bitmap sweep)
+// followed by ONE 64-byte counter fetch that tells the host the next frontier
+// length, its degree sum (sizes the next grid and drives the direction switch)
+// and the work done.  Direction switches cost one bitmap<->queue kernel.
+//
+// Direction heuristic: Beamer's edge-based rule -- go bottom-up when the
+// frontier's out-edges exceed (unexplored edges)/alpha, return top-down when
+// the frontier is shrinking and smaller than n/beta.  (The reference's rule
+// compares vertex counts, dobfs_enactor.cuh:397,569, with alpha=12, beta=6 from
+// test_dobfs.cu:533-534; depths do not depend on the rule.)
+#pragma once
+#include <vector>
+#include "bfs_functor.cuh"
+#include "../enactor_base.cuh"
+
+namespace gunrock {
+namespace app {
+namespace bfs {
+
+// frontier queue -> frontier bitmap (bitmap zeroed by the caller)
+template <typename VertexId, typename DataSlice>
+__global__ void QueueToBitmapKernel(const VertexId *queue, unsigned long long len, unsigned *bitmap, DataSlice ds)
+{
+    const unsigned long long stride = (unsigned long long)gridDim.x * blockDim.x;
+    for (unsigned long long i = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x; i < len; i += stride) {
+        const VertexId v = queue[i];
+        if (v >= 0) {
+            const unsigned long long pos = ds.BitPos(v);
+            atomicOr(bitmap + (pos >> 5), 1u << (pos & 31));
+        }
+    }
+}
+
+// this device's words of the frontier bitmap -> frontier queue (CTA-aggregated enqueue)
+template <typename VertexId, typename DataSlice, int THREADS>
+__global__ void BitmapToQueueKernel(const unsigned *bitmap, VertexId *queue, unsigned long long cap,
+                                    oprtr::LevelCounters *slot, DataSlice ds)
+{
+    __shared__ unsigned s_warp[THREADS / 32 + 1];
+    __shared__ unsigned long long s_base;
+    const long long words = (ds.local_nodes + 31) >> 5;
+    const long long seg = ((long long)ds.part.rank * ds.local_nodes) >> 5;
+    const long long rounds = (words + (long long)gridDim.x * THREADS - 1) / ((long long)gridDim.x * THREADS);
+    for (long long r = 0; r < rounds; ++r) {
+        const long long w = (r * gridDim.x + blockIdx.x) * THREADS + threadIdx.x;
+        unsigned bits = (w < words) ? bitmap[seg + w] : 0u;
+        unsigned total;
+        unsigned excl = util::BlockExclusiveSum<THREADS>((unsigned)__popc(bits), s_warp, total);
+        if (total == 0) continue;
+        if (threadIdx.x == 0) s_base = atomicAdd(&slot->out_len, (unsigned long long)total);
+        __syncthreads();
+        unsigned long long at = s_base + excl;
+        while (bits) {
+            const int b = __ffs(bits) - 1;
+            bits &= bits - 1;
+            if (at < cap) queue[at] = (VertexId)ds.part.Global((w << 5) + b);
+            ++at;
+        }
+        __syncthreads();
+    }
+}
+
+struct BFSOptions {
+    int    traversal_mode      = 0;      // 0: choose per level, 1: always LB, 2: always TWC (reference: --traversal-mode)
+    bool   direction_optimized = false;  // allow the pull direction (needs an inverse graph)
+    double alpha               = 14.0;   // push -> pull when frontier_edges > unexplored_edges / alpha
+    double beta                = 24.0;   // pull -> push when frontier < n / beta and shrinking
+    unsigned long long lb_min_edges = 1u << 16;   // mode 0: LB from this many frontier edges upward
+    bool   record_levels       = false;  // keep a per-level trace (adds two events per level)
+};
+
+struct LevelRecord {
+    int level; int pull;                 // pull: 0 push-TWC, 1 pull, 2 push-LB
+    unsigned long long frontier, edges, discovered, candidates;
+    float ms;
+};
+
+template <typename Problem>
+class BFSEnactor : public EnactorBase {
+  public:
+    typedef typename Problem::VertexId VertexId;
+    typedef typename Problem::SizeT    SizeT;
+    typedef typename Problem::Value    Value;
+    typedef typename Problem::DataSlice DataSlice;
+    typedef BFSFunctor<VertexId, SizeT, Value, Problem>        BfsFunctor;
+    typedef ReverseBFSFunctor<VertexId, SizeT, Value, Problem> PullFunctor;
+
+    // sm_100a policies: 256-thread CTAs, 4 neighbour entries per thread per tile,
+    // grids of 148 x MIN_CTAS persistent CTAs; operator-level bitmask pre-cull on,
+    // degree tracking on for the fused (non-idempotent) mode
+    typedef oprtr::advance::KernelPolicy<Problem, 256, 4, 6, true, true>   AdvancePolicy;
+    typedef oprtr::advance::KernelPolicy<Problem, 256, 4, 6, true, false>  IdemAdvancePolicy;
+    typedef oprtr::advance::KernelPolicy<Problem, 256, 4, 8, false, false> PullPolicy;
+    // reference: END_BITMASK_CULL = 5 (bfs_enactor.cuh:594); the word-atomic mask stays exact, so keep it on
+    typedef oprtr::filter::KernelPolicy<Problem, 256, 4, 6, -1>            FilterPolicy;
+
+    oprtr::advance::LbScratch<SizeT> lb_scratch;
+    std::vector<LevelRecord> levels;
+    unsigned long long edges_visited = 0;       // sum of out-degrees of visited vertices (reference GTEPS numerator)
+    cudaEvent_t ev_a = nullptr, ev_b = nullptr;
+    bool set_up = false;
+
+    ~BFSEnactor()
+    {
+        if (ev_a) cudaEventDestroy(ev_a);
+        if (ev_b) cudaEventDestroy(ev_b);
+    }
+
+    // one-time allocations (outside any timed region; the reference cudaMallocs its
+    // LB scratch inside every Enact, bfs_enactor.cuh:254-258)
+    cudaError_t Setup(Problem *problem, cudaStream_t s)
+    {
+        GR_TRY(SetupBase(problem->graph->device, s));
+        const size_t items = (size_t)problem->graph->local_nodes + 1;
+        size_t max_items = Problem::ENABLE_IDEMPOTENCE ? (size_t)problem->frontier_elements[0] : items;
+        if (max_items < items) max_items = items;
+        GR_TRY(lb_scratch.Allocate(max_items, (size_t)problem->graph->edges + 1, AdvancePolicy::SCAN_TILE,
+                                   AdvancePolicy::TILE_EDGES, s));
+        if (!ev_a) { GR_TRY(cudaEventCreate(&ev_a)); GR_TRY(cudaEventCreate(&ev_b)); }
+        set_up = true;
+        return cudaSuccess;
+    }
+
+    // reference signature: Enact<BFSProblem>(context, problem, src, max_grid_size, traversal_mode)
+    cudaError_t Enact(Problem *problem, VertexId src, const BFSOptions &opt)
+    {
+        if (!set_up) return util::GRError(cudaErrorNotReady, "BFSEnactor::Setup not called", __FILE__, __LINE__);
+        GR_TRY(ResetBase());
+        levels.clear();
+        edges_visited = 0;
+        if (src < 0 || (long long)src >= problem->graph->nodes) return cudaSuccess;
+        if constexpr (Problem::ENABLE_IDEMPOTENCE) return EnactIdempotent(problem, opt);
+        else return EnactFused(problem, opt);
+    }
+
+  private:
+    typedef oprtr::advance::Args<VertexId, SizeT> AdvArgs;
+
+    AdvArgs PushArgs(Problem *problem, VertexId level)
+    {
+        AdvArgs a;
+        a.g = problem->graph->View();
+        a.in_queue  = problem->frontier_queues[frontier_attribute.selector].ptr;
+        a.out_queue = problem->frontier_queues[frontier_attribute.selector ^ 1].ptr;
+        a.in_len = frontier_attribute.queue_length; a.d_in_len = nullptr;
+        a.out_cap = problem->frontier_elements[frontier_attribute.selector ^ 1];
+        a.slots = work_progress.d_slots.ptr;
+        a.queue_index = frontier_attribute.queue_index;
+        a.iteration = level;
+        a.output = oprtr::advance::OUT_COMPACT;
+        return a;
+    }
+
+    oprtr::advance::MODE PickMode(const BFSOptions &opt, unsigned long long frontier_edges)
+    {
+        if (opt.traversal_mode == 1) return oprtr::advance::LB;
+        if (opt.traversal_mode == 2) return oprtr::advance::TWC_FORWARD;
+        return frontier_edges >= opt.lb_min_edges ? oprtr::advance::LB : oprtr::advance::TWC_FORWARD;
+    }
+
+    // ---- normal mode: fused advance + filter, optional direction optimisation -----------------
+    cudaError_t EnactFused(Problem *problem, const BFSOptions &opt)
+    {
+        typename Problem::Base::Graph &g = *problem->graph;
+        const bool can_pull = opt.direction_optimized && g.HasInverse();
+        if (can_pull) GR_TRY(problem->PreparePull());
+
+        const bool owner = g.part.Mine(problem->src);
+        frontier_attribute.queue_length = owner ? 1 : 0;
+        unsigned long long frontier_edges = problem->src_degree;
+        unsigned long long unexplored = (unsigned long long)g.edges - frontier_edges;
+        edges_visited = frontier_edges;
+        unsigned long long prev_len = 0;
+        bool pull = false;
+        int  cur_map = 0;
+        VertexId level = 0;
+        const unsigned long long n = (unsigned long long)g.nodes;
+        const unsigned osz = (unsigned)sizeof(SizeT);
+
+        while (frontier_attribute.queue_length > 0) {
+            const unsigned long long F = frontier_attribute.queue_length;
+            // -- direction decision ---------------------------------------------------------------
+            if (can_pull) {
+                if (!pull && (double)frontier_edges > (double)unexplored / opt.alpha) {
+                    GR_TRY(problem->frontier_map[cur_map].Zero(stream));
+                    DataSlice ds = problem->MakeDataSlice(level);
+                    QueueToBitmapKernel<VertexId, DataSlice><<<util::FillGrid(F), 256, 0, stream>>>(
+                        problem->frontier_queues[frontier_attribute.selector].ptr, F, problem->frontier_map[cur_map].ptr, ds);
+                    GR_TRY(cudaGetLastError());
+                    ++enactor_stats.launches;
+                    pull = true;
+                } else if (pull && F < prev_len && (double)F < (double)n / opt.beta) {
+                    DataSlice ds = problem->MakeDataSlice(level);
+                    // borrow the slot of the upcoming kernel for the count, then clear it again
+                    oprtr::LevelCounters *slot = work_progress.Slot(frontier_attribute.queue_index + 1);
+                    BitmapToQueueKernel<VertexId, DataSlice, 256><<<util::FillGrid((n + 31) / 32), 256, 0, stream>>>(
+                        problem->frontier_map[cur_map].ptr, problem->frontier_queues[frontier_attribute.selector].ptr,
+                        problem->frontier_elements[frontier_attribute.selector], slot, ds);
+                    GR_TRY(cudaGetLastError());
+                    GR_TRY(cudaMemsetAsync(slot, 0, sizeof(oprtr::LevelCounters), stream));
+                    ++enactor_stats.launches;
+                    pull = false;
+                }
+            }
+            // -- one level ------------------------------------------------------------------------------
+            if (opt.record_levels) GR_TRY(cudaEventRecord(ev_a, stream));
+            DataSlice ds = problem->MakeDataSlice(level);
+            int kind;
+            if (!pull) {
+                oprtr::advance::MODE mode = PickMode(opt, frontier_edges);
+                kind = (mode == oprtr::advance::LB) ? 2 : 0;
+                enactor_stats.launches += (mode == oprtr::advance::LB) ? 2 : 1;
+                GR_TRY((oprtr::advance::LaunchKernel<AdvancePolicy, Problem, BfsFunctor>(
+                    mode, dev, ds, PushArgs(problem, level), &lb_scratch, frontier_edges, stream)));
+            } else {
+                kind = 1;
+                ++enactor_stats.launches;
+                oprtr::advance::pull::PullArgs<VertexId, SizeT> pa;
+                pa.g = g.InverseView();
+                pa.frontier_in  = problem->frontier_map[cur_map].ptr;
+                pa.frontier_out = problem->frontier_map[cur_map ^ 1].ptr;
+                pa.visited      = problem->visited_mask.ptr;
+                pa.candidates   = problem->candidates.ptr;
+                pa.fwd_row_offsets = g.symmetric ? nullptr : g.row_offsets.ptr;
+                pa.out_queue = nullptr; pa.out_cap = 0;
+                pa.slots = work_progress.d_slots.ptr;
+                pa.queue_index = frontier_attribute.queue_index;
+                pa.iteration = level;
+                GR_TRY((oprtr::advance::LaunchPullKernel<PullPolicy, Problem, PullFunctor>(dev, ds, pa, stream)));
+            }
+            if (opt.record_levels) GR_TRY(cudaEventRecord(ev_b, stream));
+            oprtr::LevelCounters c;
+            GR_TRY(work_progress.Fetch(frontier_attribute.queue_index + 1, c, stream));
+            if (c.overflow)
+                return util::GRError(cudaErrorInvalidConfiguration,
+                                     "frontier queue overflow: increase queue_size", __FILE__, __LINE__);
+            // -- bookkeeping ----------------------------------------------------------------------------
+            const unsigned long long D = c.out_len, E = c.edges;
+            enactor_stats.total_queued += F;
+            enactor_stats.edges_inspected += E;
+            if (!pull) {
+                ++enactor_stats.push_levels;
+                enactor_stats.algo_bytes += F * (4 + 2 * osz) + 5 * E + 8 * D;
+            } else {
+                ++enactor_stats.pull_levels;
+                enactor_stats.algo_bytes += c.aux0 * (2 * osz) + 5 * E + 4 * D + 3 * (n / 8);
+            }
+            if (opt.record_levels) {
+                LevelRecord r;
+                r.level = level; r.pull = kind; r.frontier = F; r.edges = E; r.discovered = D; r.candidates = c.aux0;
+                GR_TRY(cudaEventElapsedTime(&r.ms, ev_a, ev_b));
+                levels.push_back(r);
+            }
+            prev_len = F;
+            frontier_attribute.queue_length = D;
+            frontier_edges = c.out_degree;
+            unexplored = unexplored > frontier_edges ? unexplored - frontier_edges : 0;
+            edges_visited += frontier_edges;
+            frontier_attribute.queue_index++;
+            if (pull) cur_map ^= 1; else frontier_attribute.selector ^= 1;
+            ++level;
+            ++enactor_stats.iteration;
+        }
+        return cudaSuccess;
+    }
+
+    // ---- idempotent mode: advance emits every unmasked neighbour, filter labels + dedups ------
+    // (the reference's two-operator pipeline, bfs_enactor.cuh:267-531, bfs_functor.cuh:58-121)
+    cudaError_t EnactIdempotent(Problem *problem, const BFSOptions &opt)
+    {
+        typename Problem::Base::Graph &g = *problem->graph;
+        frontier_attribute.queue_length = 1;
+        VertexId level = 0;
+        const unsigned osz = (unsigned)sizeof(SizeT);
+        edges_visited = problem->src_degree;
+        while (frontier_attribute.queue_length > 0) {
+            const unsigned long long F = frontier_attribute.queue_length;
+            DataSlice ds = problem->MakeDataSlice(level);
+            AdvArgs a = PushArgs(problem, level);
+            oprtr::advance::MODE mode = (opt.traversal_mode == 2) ? oprtr::advance::TWC_FORWARD
+                                      : (opt.traversal_mode == 1 || F > 4096) ? oprtr::advance::LB
+                                      : oprtr::advance::TWC_FORWARD;
+            GR_TRY((oprtr::advance::LaunchKernel<IdemAdvancePolicy, Problem, BfsFunctor>(
+                mode, dev, ds, a, &lb_scratch, (unsigned long long)g.edges, stream)));
+            enactor_stats.launches += (mode == oprtr::advance::LB) ? 3 : 2;
+            frontier_attribute.queue_index++;
+            frontier_attribute.selector ^= 1;
+            // filter reads the advance's output length on the device: no host round trip in between
+            oprtr::filter::Args<VertexId, Value> fa;
+            fa.in_queue = problem->frontier_queues[frontier_attribute.selector].ptr;
+            fa.in_pred_queue = nullptr;
+            fa.out_queue = problem->frontier_queues[frontier_attribute.selector ^ 1].ptr;
+            fa.in_len = problem->frontier_elements[frontier_attribute.selector];
+            fa.d_in_len = &work_progress.Slot(frontier_attribute.queue_index)->out_len;
+            fa.out_cap = problem->frontier_elements[frontier_attribute.selector ^ 1];
+            fa.slots = work_progress.d_slots.ptr;
+            fa.queue_index = frontier_attribute.queue_index;
+            fa.iteration = level + 1;
+            fa.compact = true;
+            GR_TRY((oprtr::filter::LaunchKernel<FilterPolicy, Problem, BfsFunctor>(dev.sm_count, ds, fa, stream)));
+            // one fetch covers both slots (advance wrote queue_index, filter queue_index + 1)
+            oprtr::LevelCounters ca, cf;
+            GR_TRY(work_progress.Fetch(frontier_attribute.queue_index, ca, stream));
+            GR_TRY(work_progress.Fetch(frontier_attribute.queue_index + 1, cf, stream));
+            if (ca.overflow || cf.overflow)
+                return util::GRError(cudaErrorInvalidConfiguration,
+                                     "frontier queue overflow: increase queue_size", __FILE__, __LINE__);
+            enactor_stats.total_queued += F;
+            enactor_stats.edges_inspected += ca.edges;
+            enactor_stats.algo_bytes += F * (4 + 2 * osz) + 5 * ca.edges + 4 * ca.out_len     // advance
+                                      + 5 * ca.out_len + 8 * cf.out_len;                          // filter
+            ++enactor_stats.push_levels;
+            frontier_attribute.queue_length = cf.out_len;
+            frontier_attribute.queue_index++;
+            frontier_attribute.selector ^= 1;
+            ++level;
+            ++enactor_stats.iteration;
+        }
+        return cudaSuccess;
+    }
+};
+
+}  // namespace bfs
+}  // namespace app
+}  // namespace gunrock

@@ -1,0 +1,119 @@
+// csr.cuh -- device-resident CSR graph slice.
+//
+// Counterpart of the reference's ProblemBase::GraphSlice device arrays
+// (gunrock/app/problem_base.cuh:73-140) and of its 1D striping rule
+// owner(v) = v % num_gpus, local row = v / num_gpus (:186-210), which the
+// reference declares but never implements (:336-338 "TODO: multiple GPU").
+//
+// HBM layout (all arrays 256-byte aligned by cudaMalloc):
+//   row_offsets  SizeT   [local_nodes + 1]   CSR offsets of the rows this device owns
+//   col_indices  VertexId[edges]             GLOBAL neighbour ids, rows back to back
+//   edge_values  uint32  [edges]             optional weights, same order as col_indices
+// For an undirected (symmetric) graph the CSC is the CSR itself, so the pull
+// direction walks the same arrays; a directed graph may attach a separate
+// transpose through `csc_offsets / csc_indices`.
+#pragma once
+#include <cstdint>
+#include "../util/array.cuh"
+
+namespace gunrock {
+namespace graph {
+
+// 1D cyclic vertex partition over 2^log_parts devices
+struct Partition {
+    int log_parts = 0;      // number of devices = 1 << log_parts
+    int rank      = 0;      // this device
+
+    __host__ __device__ __forceinline__ int  Parts() const { return 1 << log_parts; }
+    __host__ __device__ __forceinline__ int  Owner(long long v) const { return (int)(v & (Parts() - 1)); }
+    __host__ __device__ __forceinline__ bool Mine(long long v) const { return Owner(v) == rank; }
+    __host__ __device__ __forceinline__ long long Local(long long v) const { return v >> log_parts; }
+    __host__ __device__ __forceinline__ long long Global(long long local) const
+    {
+        return (local << log_parts) | (long long)rank;
+    }
+};
+
+// non-owning view handed to kernels (passed by value in the parameter bank)
+template <typename VertexId, typename SizeT>
+struct CsrView {
+    const SizeT    *row_offsets;
+    const VertexId *col_indices;
+    const unsigned *edge_values;
+    long long       nodes;          // GLOBAL vertex count
+    long long       local_nodes;    // rows held by this device
+    long long       edges;          // entries held by this device
+    Partition       part;
+};
+
+template <typename _VertexId, typename _SizeT>
+struct DeviceCsr {
+    typedef _VertexId VertexId;
+    typedef _SizeT    SizeT;
+
+    util::DeviceArray<SizeT>    row_offsets;
+    util::DeviceArray<VertexId> col_indices;
+    util::DeviceArray<unsigned> edge_values;
+    // optional transpose for directed graphs (pull direction); empty => symmetric
+    util::DeviceArray<SizeT>    csc_offsets;
+    util::DeviceArray<VertexId> csc_indices;
+
+    long long nodes = 0, local_nodes = 0, edges = 0;
+    bool      symmetric = false;     // CSR doubles as CSC
+    Partition part;
+    int       device = 0;
+
+    CsrView<VertexId, SizeT> View() const
+    {
+        CsrView<VertexId, SizeT> v;
+        v.row_offsets = row_offsets.ptr;
+        v.col_indices = col_indices.ptr;
+        v.edge_values = edge_values.size ? edge_values.ptr : nullptr;
+        v.nodes = nodes; v.local_nodes = local_nodes; v.edges = edges; v.part = part;
+        return v;
+    }
+    // the arrays the pull direction walks
+    CsrView<VertexId, SizeT> InverseView() const
+    {
+        CsrView<VertexId, SizeT> v = View();
+        if (!symmetric && csc_offsets.size) {
+            v.row_offsets = csc_offsets.ptr;
+            v.col_indices = csc_indices.ptr;
+            v.edge_values = nullptr;
+        }
+        return v;
+    }
+    bool HasInverse() const { return symmetric || csc_offsets.size != 0; }
+
+    // upload a whole (unpartitioned) host CSR
+    template <typename HostSizeT>
+    cudaError_t FromHost(long long n, long long m, const HostSizeT *h_offsets,
+                         const VertexId *h_cols, const unsigned *h_weights, cudaStream_t s);
+};
+
+template <typename VertexId, typename SizeT>
+template <typename HostSizeT>
+cudaError_t DeviceCsr<VertexId, SizeT>::FromHost(long long n, long long m, const HostSizeT *h_offsets,
+                                                 const VertexId *h_cols, const unsigned *h_weights,
+                                                 cudaStream_t s)
+{
+    nodes = local_nodes = n; edges = m; part = Partition();
+    if (sizeof(HostSizeT) == sizeof(SizeT)) {
+        GR_TRY(row_offsets.FromHost((const SizeT *)h_offsets, (size_t)n + 1, s));
+    } else {
+        // widen / narrow on the host, then upload
+        SizeT *tmp = (SizeT *)malloc(sizeof(SizeT) * ((size_t)n + 1));
+        for (long long i = 0; i <= n; ++i) tmp[i] = (SizeT)h_offsets[i];
+        cudaError_t e = row_offsets.FromHost(tmp, (size_t)n + 1, s);
+        if (e == cudaSuccess) e = cudaStreamSynchronize(s);
+        free(tmp);
+        GR_TRY(e);
+    }
+    GR_TRY(col_indices.FromHost(h_cols, (size_t)m, s));
+    if (h_weights) GR_TRY(edge_values.FromHost(h_weights, (size_t)m, s));
+    else edge_values.size = 0;
+    return cudaSuccess;
+}
+
+}  // namespace graph
+}  // namespace gunrock

@@ -1,0 +1,94 @@
+// kernel.cuh -- advance::LaunchKernel, the host-side mode dispatcher.
+//
+// Counterpart of the reference's advance::LaunchKernel<KernelPolicy, Problem,
+// Functor>(...) (gunrock/oprtr/advance/kernel.cuh:101-765): same template
+// triple, same four modes, but every mode is launched without a host round
+// trip -- the reference's LB branch blocks on a cudaMemcpy of the scanned total
+// (:315-317) and, in this fork, on an RPC to an external scheduler daemon plus
+// a relaunch loop of an instrumented kernel (:552-726); neither exists here.
+#pragma once
+#include "lb.cuh"
+#include "twc.cuh"
+#include "pull.cuh"
+
+namespace gunrock {
+namespace oprtr {
+namespace advance {
+
+// what the launcher needs to know about the device
+struct DeviceInfo {
+    int device   = 0;
+    int sm_count = 148;
+    cudaError_t Query(int dev)
+    {
+        device = dev;
+        cudaDeviceProp p;
+        GR_TRY(cudaGetDeviceProperties(&p, dev));
+        sm_count = p.multiProcessorCount;
+        return cudaSuccess;
+    }
+};
+
+// Push-direction advance (TWC_FORWARD or LB).
+//   edges_hint: upper bound on (or exact value of) the number of neighbour entries
+//   the frontier expands to; it only sizes the persistent grid.
+template <typename Policy, typename Problem, typename Functor>
+cudaError_t LaunchKernel(
+    MODE mode,
+    const DeviceInfo &dev,
+    const typename Problem::DataSlice &ds,
+    Args<typename Policy::VertexId, typename Policy::SizeT> args,
+    LbScratch<typename Policy::SizeT> *scratch,
+    unsigned long long edges_hint,
+    cudaStream_t stream)
+{
+    const unsigned long long resident = (unsigned long long)dev.sm_count * Policy::MIN_CTAS;
+    if (mode == TWC_FORWARD) {
+        unsigned long long tiles = (args.in_len + Policy::THREADS - 1) / Policy::THREADS;
+        unsigned grid = (unsigned)(tiles < 1 ? 1 : (tiles < resident ? tiles : resident));
+        twc::Kernel<Policy, Problem, Functor><<<grid, Policy::THREADS, 0, stream>>>(ds, args);
+        return util::GRError(cudaGetLastError(), "advance twc::Kernel launch failed", __FILE__, __LINE__);
+    }
+    if (mode == LB) {
+        if (!scratch) return util::GRError(cudaErrorInvalidValue, "advance LB needs scratch", __FILE__, __LINE__);
+        if (args.in_len + 1 > scratch->scanned.cap)
+            return util::GRError(cudaErrorInvalidValue, "advance LB scratch too small", __FILE__, __LINE__);
+        if (++scratch->epoch >= lb::kEpochLimit) {          // descriptor tags wrapped: start over
+            GR_TRY(scratch->tile_desc.Zero(stream));
+            scratch->epoch = 1;
+        }
+        LbScratchView<typename Policy::SizeT> sv;
+        sv.scanned = scratch->scanned.ptr;   sv.row_start = scratch->row_start.ptr;
+        sv.tile_desc = scratch->tile_desc.ptr; sv.part_start = scratch->part_start.ptr;
+        sv.epoch = scratch->epoch;
+        unsigned long long scan_tiles = (args.in_len + Policy::SCAN_TILE - 1) / Policy::SCAN_TILE;
+        unsigned scan_grid = (unsigned)(scan_tiles < 1 ? 1 : scan_tiles);
+        lb::ScanKernel<Policy><<<scan_grid, Policy::SCAN_THREADS, 0, stream>>>(args, sv);
+        GR_TRY(cudaGetLastError());
+        unsigned long long tiles = (edges_hint + Policy::TILE_EDGES - 1) / Policy::TILE_EDGES;
+        unsigned grid = (unsigned)(tiles < 1 ? 1 : (tiles < resident ? tiles : resident));
+        lb::ExpandKernel<Policy, Problem, Functor><<<grid, Policy::THREADS, 0, stream>>>(ds, args, sv);
+        return util::GRError(cudaGetLastError(), "advance lb::ExpandKernel launch failed", __FILE__, __LINE__);
+    }
+    return util::GRError(cudaErrorInvalidValue, "advance: push launcher called with a pull mode", __FILE__, __LINE__);
+}
+
+// Pull-direction advance (TWC_BACKWARD / LB_BACKWARD share one implementation).
+template <typename Policy, typename Problem, typename Functor>
+cudaError_t LaunchPullKernel(
+    const DeviceInfo &dev,
+    const typename Problem::DataSlice &ds,
+    pull::PullArgs<typename Policy::VertexId, typename Policy::SizeT> args,
+    cudaStream_t stream)
+{
+    const unsigned long long resident = (unsigned long long)dev.sm_count * Policy::MIN_CTAS;
+    unsigned long long words = (unsigned long long)((args.g.local_nodes + 31) >> 5);
+    unsigned long long ctas = (words + Policy::WARPS - 1) / Policy::WARPS;
+    unsigned grid = (unsigned)(ctas < 1 ? 1 : (ctas < resident ? ctas : resident));
+    pull::Kernel<Policy, Problem, Functor><<<grid, Policy::THREADS, 0, stream>>>(ds, args);
+    return util::GRError(cudaGetLastError(), "advance pull::Kernel launch failed", __FILE__, __LINE__);
+}
+
+}  // namespace advance
+}  // namespace oprtr
+}  // namespace gunrock

@@ -1,0 +1,111 @@
+// bfs_capi.cu -- C entry points for BFS: the reference's gunrock_bfs_func and the
+// resident-graph variants of include/gunrock_b200.h.
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include "../../../include/gunrock/gunrock.h"
+#include "bfs_runner.cuh"
+#include "source_select.h"
+
+struct grb_bfs_s {
+    grb_graph_t graph = nullptr;
+    BfsRunnerBase *runner = nullptr;
+    ~grb_bfs_s() { delete runner; }
+};
+
+extern "C" int grb_bfs_create(grb_graph_t g, const grb_bfs_config *cfg, grb_bfs_t *out)
+{
+    if (!g || !out) return (int)cudaErrorInvalidValue;
+    *out = nullptr;
+    GRB_TRY(cudaSetDevice(g->device()));
+    cudaError_t err = cudaSuccess;
+    grb_bfs_s *c = new grb_bfs_s();
+    c->graph = g;
+    c->runner = g->g32 ? MakeBfsRunner32(g->g32, cfg, g->stream, &err) : MakeBfsRunner64(g->g64, cfg, g->stream, &err);
+    if (!c->runner) { delete c; return (int)(err ? err : cudaErrorUnknown); }
+    *out = c;
+    return 0;
+}
+
+extern "C" int grb_bfs_run(grb_bfs_t ctx, int32_t src, int32_t *labels_host, int32_t *preds_host, grb_stats *stats)
+{
+    if (!ctx) return (int)cudaErrorInvalidValue;
+    GRB_TRY(cudaSetDevice(ctx->graph->device()));
+    GRB_TRY(ctx->runner->Run(src, labels_host, preds_host, stats));
+    return 0;
+}
+
+extern "C" int grb_bfs_device_labels(grb_bfs_t ctx, void **labels_dev)
+{
+    if (!ctx || !labels_dev) return (int)cudaErrorInvalidValue;
+    *labels_dev = ctx->runner->DeviceLabels();
+    return 0;
+}
+
+extern "C" int grb_bfs_levels(grb_bfs_t ctx, grb_level_record *out, int32_t cap, int32_t *count)
+{
+    if (!ctx || !count) return (int)cudaErrorInvalidValue;
+    const auto &lv = ctx->runner->Levels();
+    *count = (int32_t)lv.size();
+    for (int i = 0; i < (int)lv.size() && i < cap && out; ++i) {
+        out[i].level = lv[i].level; out[i].kind = lv[i].pull; out[i].frontier = lv[i].frontier;
+        out[i].edges = lv[i].edges; out[i].discovered = lv[i].discovered; out[i].candidates = lv[i].candidates;
+        out[i].ms = lv[i].ms; out[i].pad = 0;
+    }
+    return 0;
+}
+
+extern "C" void grb_bfs_destroy(grb_bfs_t ctx)
+{
+    if (!ctx) return;
+    cudaSetDevice(ctx->graph->device());
+    delete ctx;
+}
+
+// ---------------------------------------------------------------------------------------
+// reference entry point (gunrock/gunrock.h:106-110; implementation it replaces:
+// gunrock/app/bfs/bfs_app.cu:241-402)
+// ---------------------------------------------------------------------------------------
+extern "C" void gunrock_bfs_func(struct GunrockGraph *graph_out, const struct GunrockGraph *graph_in,
+                                 struct GunrockConfig configs, struct GunrockDataType data_type)
+{
+    if (data_type.VTXID_TYPE != VTXID_INT || data_type.SIZET_TYPE != SIZET_INT || data_type.VALUE_TYPE != VALUE_INT) {
+        printf("Not Yet Support This DataType Combination.\n");       // bfs_app.cu:354-365
+        return;
+    }
+    const long long n = (long long)graph_in->num_nodes, m = (long long)graph_in->num_edges;
+    const int *h_off = (const int *)graph_in->row_offsets;
+    const int src = grb_pick_source(configs.src_mode, configs.src_node, n, h_off);
+
+    grb_graph_t g = nullptr;
+    if (grb_graph_from_host(configs.device, n, m, h_off, 4, (const int32_t *)graph_in->col_indices, nullptr, 0, 4, &g))
+        return;
+    grb_bfs_config cfg;
+    memset(&cfg, 0, sizeof(cfg));
+    cfg.mark_pred = configs.mark_pred; cfg.idempotence = configs.idempotence;
+    cfg.queue_sizing = configs.queue_size;
+    grb_bfs_t ctx = nullptr;
+    if (grb_bfs_create(g, &cfg, &ctx)) { grb_graph_destroy(g); return; }
+
+    int *h_labels = (int *)malloc(sizeof(int) * (size_t)(n > 0 ? n : 1));     // caller frees (bfs_app.cu:165,211)
+    int *h_preds = configs.mark_pred ? (int *)malloc(sizeof(int) * (size_t)(n > 0 ? n : 1)) : nullptr;
+    grb_stats st;
+    memset(&st, 0, sizeof(st));
+    const int rc = grb_bfs_run(ctx, src, h_labels, h_preds, &st);
+    if (rc == 0) {
+        // same figures the reference prints (bfs_app.cu:103-118)
+        const double rate = st.elapsed_ms > 0 ? (double)st.edges_visited / (st.elapsed_ms * 1000.0) : 0.0;
+        printf("[BFS] finished. \n elapsed: %.4f ms\n src: %lld\n nodes_visited: %lld\n edges_visited: %lld\n"
+               " rate: %.4f MiEdges/s\n search_depth: %lld\n",
+               st.elapsed_ms, (long long)src, (long long)st.nodes_visited, (long long)st.edges_visited,
+               rate, (long long)st.iterations);
+        graph_out->node_values = h_labels;
+    } else {
+        free(h_labels);
+        graph_out->node_values = nullptr;
+    }
+    free(h_preds);                          // the C API never returns BFS predecessors (bfs_app.cu:166-170,227)
+    grb_bfs_destroy(ctx);
+    grb_graph_destroy(g);
+    cudaDeviceSynchronize();                // bfs_app.cu:229
+}

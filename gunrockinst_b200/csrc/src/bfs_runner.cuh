@@ -1,0 +1,95 @@
+// bfs_runner.cuh -- glue between the C ABI and the BFS Problem / Enactor templates.
+// Counterpart of run_bfs<VertexId, Value, SizeT, MARK_PREDECESSORS, ENABLE_IDEMPOTENCE>
+// (gunrock/app/bfs/bfs_app.cu:146-229): Init -> Reset -> Enact -> Extract, with the
+// Init done once per context instead of once per call.
+#pragma once
+#include "../../../include/gunrock_b200.h"
+#include "graph_handle.cuh"
+#include "../gunrock/app/bfs/bfs_enactor.cuh"
+
+struct BfsRunnerBase {
+    virtual ~BfsRunnerBase() {}
+    virtual cudaError_t Run(int src, int *labels_host, int *preds_host, grb_stats *stats) = 0;
+    virtual void *DeviceLabels() = 0;
+    virtual const std::vector<gunrock::app::bfs::LevelRecord> &Levels() = 0;
+};
+
+template <typename SizeT, bool MARK_PRED, bool IDEM>
+struct BfsRunner : BfsRunnerBase {
+    typedef gunrock::app::bfs::BFSProblem<int, SizeT, int, MARK_PRED, IDEM> Problem;
+    typedef gunrock::app::bfs::BFSEnactor<Problem> Enactor;
+    Problem problem;
+    Enactor enactor;
+    gunrock::app::bfs::BFSOptions opt;
+    double queue_sizing = 1.0;
+    cudaStream_t stream = 0;
+    cudaEvent_t e0 = nullptr, e1 = nullptr, e2 = nullptr;
+    bool ready = false;
+
+    ~BfsRunner()
+    {
+        if (e0) cudaEventDestroy(e0);
+        if (e1) cudaEventDestroy(e1);
+        if (e2) cudaEventDestroy(e2);
+    }
+
+    cudaError_t Create(gunrock::graph::DeviceCsr<int, SizeT> *g, const grb_bfs_config *cfg, cudaStream_t s)
+    {
+        stream = s;
+        if (cfg) {
+            opt.traversal_mode = cfg->traversal_mode;
+            opt.direction_optimized = cfg->direction_optimized != 0;
+            if (cfg->alpha > 0) opt.alpha = cfg->alpha;
+            if (cfg->beta > 0) opt.beta = cfg->beta;
+            if (cfg->queue_sizing > 0) queue_sizing = cfg->queue_sizing;
+            opt.record_levels = cfg->record_levels != 0;
+        }
+        GR_TRY(problem.Init(g, s));
+        GR_TRY(cudaEventCreate(&e0)); GR_TRY(cudaEventCreate(&e1)); GR_TRY(cudaEventCreate(&e2));
+        return cudaSuccess;
+    }
+
+    cudaError_t Run(int src, int *labels_host, int *preds_host, grb_stats *stats) override
+    {
+        using gunrock::app::VERTEX_FRONTIERS;
+        using gunrock::app::EDGE_FRONTIERS;
+        GR_TRY(cudaEventRecord(e0, stream));
+        GR_TRY(problem.Reset(src, IDEM ? EDGE_FRONTIERS : VERTEX_FRONTIERS, queue_sizing));
+        if (!ready) { GR_TRY(enactor.Setup(&problem, stream)); ready = true; }
+        GR_TRY(cudaEventRecord(e1, stream));
+        GR_TRY(enactor.Enact(&problem, src, opt));
+        GR_TRY(cudaEventRecord(e2, stream));
+        GR_TRY(cudaEventSynchronize(e2));
+        if (labels_host) GR_TRY(problem.Extract(labels_host, preds_host));
+        if (stats) {
+            float r = 0, t = 0;
+            cudaEventElapsedTime(&r, e0, e1); cudaEventElapsedTime(&t, e1, e2);
+            memset(stats, 0, sizeof(*stats));
+            stats->reset_ms = r; stats->elapsed_ms = t;
+            stats->iterations = enactor.enactor_stats.iteration;
+            stats->edges_visited = (int64_t)enactor.edges_visited;
+            stats->edges_inspected = enactor.enactor_stats.edges_inspected;
+            stats->total_queued = enactor.enactor_stats.total_queued;
+            stats->nodes_visited = (int64_t)enactor.enactor_stats.total_queued;
+            stats->algo_bytes = enactor.enactor_stats.algo_bytes;
+            stats->push_levels = enactor.enactor_stats.push_levels;
+            stats->pull_levels = enactor.enactor_stats.pull_levels;
+            stats->gpu_launches = enactor.enactor_stats.launches;
+        }
+        return cudaSuccess;
+    }
+    void *DeviceLabels() override { return problem.labels.ptr; }
+    const std::vector<gunrock::app::bfs::LevelRecord> &Levels() override { return enactor.levels; }
+};
+
+BfsRunnerBase *MakeBfsRunner32(Csr32 *g, const grb_bfs_config *cfg, cudaStream_t s, cudaError_t *err);
+BfsRunnerBase *MakeBfsRunner64(Csr64 *g, const grb_bfs_config *cfg, cudaStream_t s, cudaError_t *err);
+
+template <typename R, typename G>
+static BfsRunnerBase *MakeOne(G *g, const grb_bfs_config *cfg, cudaStream_t s, cudaError_t *err)
+{
+    R *r = new R();
+    *err = r->Create(g, cfg, s);
+    if (*err != cudaSuccess) { delete r; return nullptr; }
+    return r;
+}

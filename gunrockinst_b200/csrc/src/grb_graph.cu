@@ -1,0 +1,106 @@
+// grb_graph.cu -- resident graph handles of the extended C ABI (include/gunrock_b200.h).
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include "../../../include/gunrock_b200.h"
+#include "graph_handle.cuh"
+
+extern "C" const char *grb_version(void) { return "gunrockinst_b200 0.1 (sm_100a)"; }
+
+extern "C" int grb_device_count(void)
+{
+    int count = 0;
+    if (cudaGetDeviceCount(&count) != cudaSuccess) { cudaGetLastError(); return 0; }
+    return count;
+}
+
+extern "C" int grb_graph_from_host(int device, int64_t nodes, int64_t edges,
+                                   const void *row_offsets, int offset_bytes_in,
+                                   const int32_t *col_indices, const uint32_t *weights,
+                                   int symmetric, int force_offset_bytes, grb_graph_t *out)
+{
+    if (!out || !row_offsets || (edges > 0 && !col_indices) || (offset_bytes_in != 4 && offset_bytes_in != 8))
+        return (int)cudaErrorInvalidValue;
+    *out = nullptr;
+    int rc = grb_select_device(device);
+    if (rc) return rc;
+    int ob = force_offset_bytes ? force_offset_bytes : (edges >= (int64_t)0x7fffffff ? 8 : 4);
+    if (ob != 4 && ob != 8) return (int)cudaErrorInvalidValue;
+    if (ob == 4 && edges >= (int64_t)0x7fffffff) return (int)cudaErrorInvalidValue;
+    grb_graph_s *h = new grb_graph_s();
+    h->offset_bytes = ob;
+    cudaError_t e = cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking);
+    if (e == cudaSuccess) {
+        if (ob == 4) {
+            h->g32 = new Csr32(); h->g32->device = device; h->g32->symmetric = symmetric != 0;
+            e = (offset_bytes_in == 4)
+                ? h->g32->FromHost(nodes, edges, (const int *)row_offsets, col_indices, weights, h->stream)
+                : h->g32->FromHost(nodes, edges, (const long long *)row_offsets, col_indices, weights, h->stream);
+        } else {
+            h->g64 = new Csr64(); h->g64->device = device; h->g64->symmetric = symmetric != 0;
+            e = (offset_bytes_in == 4)
+                ? h->g64->FromHost(nodes, edges, (const int *)row_offsets, col_indices, weights, h->stream)
+                : h->g64->FromHost(nodes, edges, (const long long *)row_offsets, col_indices, weights, h->stream);
+        }
+    }
+    if (e == cudaSuccess) e = cudaStreamSynchronize(h->stream);
+    if (e != cudaSuccess) { gunrock::util::GRError(e, "grb_graph_from_host", __FILE__, __LINE__); delete h; return (int)e; }
+    *out = h;
+    return 0;
+}
+
+extern "C" int grb_graph_get_info(grb_graph_t g, grb_graph_info *info)
+{
+    if (!g || !info) return (int)cudaErrorInvalidValue;
+    memset(info, 0, sizeof(*info));
+    info->nodes = g->nodes(); info->local_nodes = g->local_nodes(); info->edges = g->edges();
+    info->offset_bytes = g->offset_bytes; info->device = g->device();
+    if (g->g32) {
+        info->symmetric = g->g32->symmetric; info->has_weights = g->g32->edge_values.size != 0;
+        info->log_parts = g->g32->part.log_parts; info->rank = g->g32->part.rank;
+    } else {
+        info->symmetric = g->g64->symmetric; info->has_weights = g->g64->edge_values.size != 0;
+        info->log_parts = g->g64->part.log_parts; info->rank = g->g64->part.rank;
+    }
+    return 0;
+}
+
+extern "C" int grb_graph_download(grb_graph_t g, void *row_offsets, int32_t *col_indices, uint32_t *weights)
+{
+    if (!g) return (int)cudaErrorInvalidValue;
+    GRB_TRY(cudaSetDevice(g->device()));
+    const size_t ln = (size_t)g->local_nodes(), m = (size_t)g->edges();
+    if (g->g32) {
+        if (row_offsets) GRB_TRY(g->g32->row_offsets.ToHost((int *)row_offsets, ln + 1, g->stream));
+        if (col_indices) GRB_TRY(g->g32->col_indices.ToHost(col_indices, m, g->stream));
+        if (weights && g->g32->edge_values.size) GRB_TRY(g->g32->edge_values.ToHost(weights, m, g->stream));
+    } else {
+        if (row_offsets) GRB_TRY(g->g64->row_offsets.ToHost((long long *)row_offsets, ln + 1, g->stream));
+        if (col_indices) GRB_TRY(g->g64->col_indices.ToHost(col_indices, m, g->stream));
+        if (weights && g->g64->edge_values.size) GRB_TRY(g->g64->edge_values.ToHost(weights, m, g->stream));
+    }
+    GRB_TRY(cudaStreamSynchronize(g->stream));
+    return 0;
+}
+
+extern "C" int grb_graph_device_ptrs(grb_graph_t g, void **row_offsets, void **col_indices, void **weights)
+{
+    if (!g) return (int)cudaErrorInvalidValue;
+    if (g->g32) {
+        if (row_offsets) *row_offsets = g->g32->row_offsets.ptr;
+        if (col_indices) *col_indices = g->g32->col_indices.ptr;
+        if (weights) *weights = g->g32->edge_values.size ? g->g32->edge_values.ptr : nullptr;
+    } else {
+        if (row_offsets) *row_offsets = g->g64->row_offsets.ptr;
+        if (col_indices) *col_indices = g->g64->col_indices.ptr;
+        if (weights) *weights = g->g64->edge_values.size ? g->g64->edge_values.ptr : nullptr;
+    }
+    return 0;
+}
+
+extern "C" void grb_graph_destroy(grb_graph_t g)
+{
+    if (!g) return;
+    cudaSetDevice(g->device());
+    delete g;
+}

@@ -1,0 +1,195 @@
+/*
+ * gunrock_b200.h -- extended C ABI of libgunrock.so (B200-native build).
+ *
+ * gunrock/gunrock.h is the reference's interface and is kept as is; it forces
+ * a full host->device upload, 32-bit edge offsets and a device->host download
+ * on every call (gunrock/app/bfs/bfs_app.cu:146-229).  The entry points below
+ * expose the SAME primitives and the two frontier operators with the graph
+ * RESIDENT in HBM, 64-bit edge offsets where a graph needs them (R-MAT scale
+ * 27), direction-optimising BFS (the reference ships it only as a test
+ * program, tests/dobfs/test_dobfs.cu), and the per-level pieces a
+ * 1D-partitioned multi-GPU run is assembled from.
+ *
+ * Conventions: plain C types only; every function returns 0 on success or a
+ * cudaError_t value (also reported on stderr, like the reference's GRError);
+ * "host" pointers are ordinary host memory, "dev" pointers are device memory
+ * on the graph's device.  Nothing here falls back to the CPU.
+ *
+ * Each declaration cites the reference interface it stands in for.
+ */
+#ifndef GUNROCK_B200_EXT_H_
+#define GUNROCK_B200_EXT_H_
+
+#include <stdint.h>
+#include <stddef.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct grb_graph_s *grb_graph_t;
+
+/* ---- library / device ----------------------------------------------------- */
+const char *grb_version(void);
+int grb_device_count(void);              /* 0 when no CUDA device is usable */
+
+/* ---- resident graphs --------------------------------------------------------
+ * stands in for ProblemBase::Init's upload (gunrock/app/problem_base.cuh:226-342)
+ * and for graphio::BuildRmatGraph / BuildMarketGraph + Csr::FromCoo
+ * (gunrock/graphio/rmat.cuh:27-92, market.cuh:57-236, csr.cuh:247-340). */
+typedef struct {
+    int64_t nodes;          /* global vertex count                               */
+    int64_t local_nodes;    /* rows resident on this device                      */
+    int64_t edges;          /* CSR entries resident on this device               */
+    int32_t offset_bytes;   /* 4 or 8                                            */
+    int32_t symmetric;      /* CSR doubles as CSC                                */
+    int32_t has_weights;
+    int32_t device;
+    int32_t log_parts;      /* 1D cyclic partition: 2^log_parts devices          */
+    int32_t rank;
+} grb_graph_info;
+
+/* upload a host CSR; offset_bytes_in = width of row_offsets (4 or 8);
+ * weights may be NULL; symmetric != 0 promises CSR == CSC (enables pull) */
+int grb_graph_from_host(int device, int64_t nodes, int64_t edges,
+                        const void *row_offsets, int offset_bytes_in,
+                        const int32_t *col_indices, const uint32_t *weights,
+                        int symmetric, int force_offset_bytes, grb_graph_t *out);
+
+/* seeded R-MAT (a,b,c,d + per-level 5% noise exactly as graphio/utils.cuh:84-130),
+ * nodes = 2^scale, `edges` generated tuples, undirected => reverse tuples added,
+ * then the reference canonicalisation (sort by (row,col), drop duplicates and
+ * self loops), all on the device.  With log_parts > 0 only rows v with
+ * v % 2^log_parts == rank are kept (1D cyclic partition, problem_base.cuh:186-210).
+ * weight_seed != 0 attaches symmetric uint32 weights in [1,64]. */
+int grb_graph_rmat(int device, int scale, int64_t edges, uint64_t seed, int undirected,
+                   double a, double b, double c, double d,
+                   int log_parts, int rank, uint64_t weight_seed,
+                   int force_offset_bytes, grb_graph_t *out);
+
+int  grb_graph_get_info(grb_graph_t g, grb_graph_info *info);
+/* copy the resident CSR back (row_offsets in the graph's offset width) */
+int  grb_graph_download(grb_graph_t g, void *row_offsets, int32_t *col_indices, uint32_t *weights);
+/* raw device pointers of the resident arrays (for harness-side collectives) */
+int  grb_graph_device_ptrs(grb_graph_t g, void **row_offsets, void **col_indices, void **weights);
+void grb_graph_destroy(grb_graph_t g);
+
+/* ---- run statistics ---------------------------------------------------------
+ * stands in for the numbers DisplayStats prints (gunrock/app/bfs/bfs_app.cu:63-118) */
+typedef struct {
+    double   elapsed_ms;        /* CUDA-event time of Enact only (reference bracket, bfs_app.cu:196-200) */
+    double   reset_ms;          /* CUDA-event time of Problem::Reset                 */
+    int64_t  iterations;        /* search depth / sweeps                             */
+    int64_t  edges_visited;     /* sum of out-degrees of visited vertices (bfs_app.cu:82-91) */
+    int64_t  nodes_visited;
+    uint64_t edges_inspected;   /* neighbour entries the operators actually read     */
+    uint64_t total_queued;      /* sum of frontier lengths                           */
+    uint64_t algo_bytes;        /* algorithmic HBM bytes, formulas in DESIGN.md      */
+    int32_t  push_levels, pull_levels;
+    int32_t  gpu_launches;      /* kernels launched inside Enact                     */
+    int32_t  reserved;
+} grb_stats;
+
+/* per-level trace of the last BFS on a handle (record_levels != 0) */
+typedef struct {
+    int32_t  level;
+    int32_t  kind;              /* 0 push-TWC, 1 pull, 2 push-LB                     */
+    uint64_t frontier, edges, discovered, candidates;
+    float    ms;
+    float    pad;
+} grb_level_record;
+
+/* ---- BFS ----------------------------------------------------------------------
+ * stands in for gunrock_bfs_func / run_bfs (gunrock/app/bfs/bfs_app.cu:146-229)
+ * and for the DOBFS test rig (tests/dobfs/test_dobfs.cu). */
+typedef struct {
+    int32_t mark_pred;
+    int32_t idempotence;
+    int32_t traversal_mode;       /* 0 auto, 1 LB, 2 TWC (reference --traversal-mode) */
+    int32_t direction_optimized;  /* needs a symmetric graph                          */
+    double  alpha, beta;          /* <= 0: library defaults                           */
+    double  queue_sizing;         /* <= 0: 1.0                                        */
+    int32_t record_levels;
+    int32_t reserved;
+} grb_bfs_config;
+
+typedef struct grb_bfs_s *grb_bfs_t;
+/* a BFS context owns labels / bitmaps / queues for one graph: create once, run many */
+int  grb_bfs_create(grb_graph_t g, const grb_bfs_config *cfg, grb_bfs_t *out);
+/* labels_host / preds_host may be NULL (results stay on the device) */
+int  grb_bfs_run(grb_bfs_t ctx, int32_t src, int32_t *labels_host, int32_t *preds_host, grb_stats *stats);
+int  grb_bfs_device_labels(grb_bfs_t ctx, void **labels_dev);
+int  grb_bfs_levels(grb_bfs_t ctx, grb_level_record *out, int32_t cap, int32_t *count);
+void grb_bfs_destroy(grb_bfs_t ctx);
+
+/* ---- SSSP / CC / PR -------------------------------------------------------------
+ * stand in for gunrock_sssp_func (app/sssp/sssp_app.cu:370), gunrock_cc_func
+ * (app/cc/cc_app.cu:265), gunrock_pr_func (app/pr/pr_app.cu:318). */
+int grb_sssp(grb_graph_t g, int32_t src, int32_t delta_factor, int32_t mark_pred,
+             uint32_t *dist_host, int32_t *preds_host, grb_stats *stats);
+int grb_cc(grb_graph_t g, int32_t *labels_host, int64_t *num_components, grb_stats *stats);
+/* ranks64_host (fp64, vertex order) and/or sorted (ids, fp32 ranks) outputs; any may be NULL */
+int grb_pagerank(grb_graph_t g, int32_t src, double delta, double threshold, int32_t max_iter,
+                 double *ranks64_host, int32_t *sorted_ids_host, float *sorted_ranks_host,
+                 grb_stats *stats);
+
+/* ---- operators, stand-alone (parity tests of the operators themselves) ------------
+ * stand in for advance::LaunchKernel (gunrock/oprtr/advance/kernel.cuh:101-129) and
+ * filter::Kernel (gunrock/oprtr/filter/kernel.cuh:738-757) run with a probe functor:
+ *   CondEdge(s,d,e)  : edge_hits[e] += 1; src_sum[d] += s; return ((s + d) % 3) != 0
+ *   ApplyEdge(s,d,e) : dst_hits[d] += 1
+ *   CondFilter(v)    : return v % 2 == 0        ApplyFilter(v): dst_hits[v] += 1
+ * mode: 0 TWC, 1 LB.  output: 0 none, 1 compact, 2 tombstone (LB only).
+ * All array arguments are host pointers; out_queue must hold out_cap ids. */
+int grb_test_advance(grb_graph_t g, int mode, int output,
+                     const int32_t *in_queue, int64_t in_len,
+                     int32_t *out_queue, int64_t out_cap, int64_t *out_len,
+                     int32_t *edge_hits, int64_t *src_sum, int32_t *dst_hits,
+                     uint64_t *edges_inspected);
+int grb_test_filter(int device, int64_t nodes, int compact,
+                    const int32_t *in_queue, int64_t in_len,
+                    int32_t *out_queue, int64_t out_cap, int64_t *out_len,
+                    int32_t *dst_hits);
+
+/* ---- 1D-partitioned BFS, one device per process -----------------------------------
+ * No reference counterpart (the reference's multi-GPU path is a TODO,
+ * gunrock/app/problem_base.cuh:336-338); the striping rule is the reference's.
+ * The harness owns the communicator (torch.distributed / NCCL) and moves the
+ * buffers exposed here between levels. */
+typedef struct grb_mgbfs_s *grb_mgbfs_t;
+typedef struct {
+    uint64_t frontier_local;     /* owned vertices in the next frontier            */
+    uint64_t frontier_edges;     /* their out-degree sum                           */
+    uint64_t edges_inspected;
+    uint64_t candidates;
+    uint64_t outbox_len[16];     /* push-sparse: ids queued for each peer          */
+} grb_mg_level;
+
+int  grb_mgbfs_create(grb_graph_t g, uint64_t outbox_cap, grb_mgbfs_t *out);
+int  grb_mgbfs_reset(grb_mgbfs_t ctx, int32_t src, uint64_t *src_degree);
+/* device pointers the harness hands to the collectives:
+ * which: 0 visited bitmap, 1 frontier map A, 2 frontier map B, 3 outbox ids,
+ *        4 inbox ids, 5 labels (local), 6 next bitmap (push-dense scratch) */
+int  grb_mgbfs_buffer(grb_mgbfs_t ctx, int which, void **dev_ptr, uint64_t *bytes);
+/* pull level: reads frontier map `cur`, writes OWN segment of map cur^1 */
+int  grb_mgbfs_pull(grb_mgbfs_t ctx, int32_t level, int cur, grb_mg_level *out);
+/* push level over the local queue; remote discoveries are set in the dense
+ * `next` bitmap (dense != 0) or appended to the per-peer outboxes (dense == 0) */
+int  grb_mgbfs_push(grb_mgbfs_t ctx, int32_t level, int dense, grb_mg_level *out);
+/* after the exchange: absorb ids received in the inbox (sparse) ...            */
+int  grb_mgbfs_absorb_inbox(grb_mgbfs_t ctx, int32_t level, uint64_t inbox_len, grb_mg_level *out);
+/* ... or OR together `parts` received segments of the next bitmap (dense)      */
+int  grb_mgbfs_absorb_dense(grb_mgbfs_t ctx, int32_t level, grb_mg_level *out);
+/* local queue <-> own segment of frontier map `cur`; visited |= map (all words) */
+int  grb_mgbfs_queue_to_map(grb_mgbfs_t ctx, int cur);
+int  grb_mgbfs_map_to_queue(grb_mgbfs_t ctx, int cur, grb_mg_level *out);
+int  grb_mgbfs_merge_visited(grb_mgbfs_t ctx, int cur);
+int  grb_mgbfs_sync(grb_mgbfs_t ctx);
+int  grb_mgbfs_stream(grb_mgbfs_t ctx, void **cuda_stream);
+int  grb_mgbfs_labels(grb_mgbfs_t ctx, int32_t *labels_host);
+void grb_mgbfs_destroy(grb_mgbfs_t ctx);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* GUNROCK_B200_EXT_H_ */

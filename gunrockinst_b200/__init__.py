@@ -1,0 +1,280 @@
+"""gunrockinst_b200 -- host-side mirror of the reference's interface for the advance /
+filter hot path, on top of libgunrock.so (hand-written sm_100a CUDA, C ABI).
+
+Two layers, both thin:
+
+* the reference's own C API, argument for argument (gunrock/gunrock.h:106-151):
+  ``gunrock_bfs_func / gunrock_cc_func / gunrock_sssp_func / gunrock_pr_func`` taking
+  host CSR arrays -- used by the parity tests the way shared_lib_tests/test_*.c use it;
+* the resident-graph API of include/gunrock_b200.h (``Graph``, ``Bfs``, ``sssp``, ``cc``,
+  ``pagerank``): the graph stays in HBM between runs, which is what bench.py times.
+
+numpy arrays are host buffers; nothing in this package computes on the CPU and nothing
+imports oracle/.  If libgunrock.so is missing, every call raises ``GunrockError``.
+"""
+import ctypes as C
+import numpy as np
+
+from . import _capi
+from ._capi import GunrockError, Stats, BfsConfig, GraphInfo, LevelRecord, build  # noqa: F401
+
+RMAT_ABCD = (0.55, 0.2, 0.2, 0.05)     # reference defaults, gunrock/graphio/rmat.cuh:32-35
+
+
+def _ptr(a):
+    return a.ctypes.data_as(C.c_void_p) if a is not None else None
+
+
+def version():
+    return _capi.lib().grb_version().decode()
+
+
+def device_count():
+    return int(_capi.lib().grb_device_count())
+
+
+class Graph:
+    """A CSR graph resident in HBM (grb_graph_t)."""
+
+    def __init__(self, handle):
+        self._h = handle
+        self.info = GraphInfo()
+        _capi.check(_capi.lib().grb_graph_get_info(self._h, C.byref(self.info)), "grb_graph_get_info")
+
+    # -- constructors ----------------------------------------------------------------
+    @classmethod
+    def from_csr(cls, row_offsets, col_indices, weights=None, symmetric=False, device=0,
+                 force_offset_bytes=0):
+        ro = np.ascontiguousarray(row_offsets)
+        if ro.dtype not in (np.int32, np.int64):
+            ro = ro.astype(np.int64)
+        co = np.ascontiguousarray(col_indices, dtype=np.int32)
+        w = np.ascontiguousarray(weights, dtype=np.uint32) if weights is not None else None
+        h = C.c_void_p()
+        _capi.check(_capi.lib().grb_graph_from_host(
+            device, ro.size - 1, co.size, _ptr(ro), ro.dtype.itemsize, _ptr(co), _ptr(w),
+            int(bool(symmetric)), force_offset_bytes, C.byref(h)), "grb_graph_from_host")
+        return cls(h)
+
+    @classmethod
+    def rmat(cls, scale, edgefactor=16, seed=None, undirected=True, abcd=RMAT_ABCD, device=0,
+             log_parts=0, rank=0, weight_seed=0, force_offset_bytes=0):
+        """Seeded R-MAT generated, sorted and de-duplicated on the device; seed defaults to
+        42 + scale."""
+        if seed is None:
+            seed = 42 + scale
+        h = C.c_void_p()
+        _capi.check(_capi.lib().grb_graph_rmat(
+            device, scale, edgefactor << scale, seed, int(bool(undirected)), *abcd,
+            log_parts, rank, weight_seed, force_offset_bytes, C.byref(h)), "grb_graph_rmat")
+        return cls(h)
+
+    # -- accessors ---------------------------------------------------------------------
+    @property
+    def nodes(self):
+        return int(self.info.nodes)
+
+    @property
+    def local_nodes(self):
+        return int(self.info.local_nodes)
+
+    @property
+    def edges(self):
+        return int(self.info.edges)
+
+    def download(self, want_weights=False):
+        """-> (row_offsets, col_indices[, weights]) as numpy arrays (row offsets in the
+        graph's own width)."""
+        ro = np.empty(self.local_nodes + 1, dtype=np.int32 if self.info.offset_bytes == 4 else np.int64)
+        co = np.empty(max(self.edges, 1), dtype=np.int32)
+        w = np.empty(max(self.edges, 1), dtype=np.uint32) if (want_weights and self.info.has_weights) else None
+        _capi.check(_capi.lib().grb_graph_download(self._h, _ptr(ro), _ptr(co), _ptr(w)), "grb_graph_download")
+        if want_weights:
+            return ro, co[:self.edges], (w[:self.edges] if w is not None else None)
+        return ro, co[:self.edges]
+
+    def device_ptrs(self):
+        a, b, c = C.c_void_p(), C.c_void_p(), C.c_void_p()
+        _capi.check(_capi.lib().grb_graph_device_ptrs(self._h, C.byref(a), C.byref(b), C.byref(c)),
+                    "grb_graph_device_ptrs")
+        return a.value, b.value, c.value
+
+    def close(self):
+        if self._h:
+            _capi.lib().grb_graph_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+class Bfs:
+    """BFS context on a resident graph (Problem + Enactor, created once, run many times).
+
+    Mirrors the knobs of the reference's BFS / DOBFS test rigs (tests/bfs/test_bfs.cu:58-89,
+    tests/dobfs/test_dobfs.cu:533-534): mark_pred, idempotence, traversal_mode, alpha/beta.
+    """
+
+    def __init__(self, graph, mark_pred=False, idempotence=False, traversal_mode=0,
+                 direction_optimized=False, alpha=0.0, beta=0.0, queue_sizing=0.0, record_levels=False):
+        self.graph = graph
+        cfg = BfsConfig(int(mark_pred), int(idempotence), int(traversal_mode), int(direction_optimized),
+                        float(alpha), float(beta), float(queue_sizing), int(record_levels), 0)
+        self.mark_pred = bool(mark_pred)
+        self._h = C.c_void_p()
+        _capi.check(_capi.lib().grb_bfs_create(graph._h, C.byref(cfg), C.byref(self._h)), "grb_bfs_create")
+
+    def run(self, src, want_labels=True, labels_out=None):
+        """-> (labels or None, preds or None, stats dict)."""
+        n = self.graph.local_nodes
+        labels = preds = None
+        if want_labels:
+            labels = labels_out if labels_out is not None else np.empty(n, dtype=np.int32)
+            if self.mark_pred:
+                preds = np.empty(n, dtype=np.int32)
+        st = Stats()
+        _capi.check(_capi.lib().grb_bfs_run(self._h, int(src), _ptr(labels), _ptr(preds), C.byref(st)),
+                    "grb_bfs_run")
+        return labels, preds, st.as_dict()
+
+    def device_labels(self):
+        p = C.c_void_p()
+        _capi.check(_capi.lib().grb_bfs_device_labels(self._h, C.byref(p)), "grb_bfs_device_labels")
+        return p.value
+
+    def levels(self):
+        cnt = C.c_int32()
+        L = _capi.lib()
+        _capi.check(L.grb_bfs_levels(self._h, None, 0, C.byref(cnt)), "grb_bfs_levels")
+        arr = (LevelRecord * max(cnt.value, 1))()
+        _capi.check(L.grb_bfs_levels(self._h, arr, cnt.value, C.byref(cnt)), "grb_bfs_levels")
+        kinds = {0: "push-twc", 1: "pull", 2: "push-lb"}
+        return [dict(level=r.level, kind=kinds.get(r.kind, str(r.kind)), frontier=r.frontier, edges=r.edges,
+                     discovered=r.discovered, candidates=r.candidates, ms=r.ms) for r in arr[:cnt.value]]
+
+    def close(self):
+        if self._h:
+            _capi.lib().grb_bfs_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+def sssp(graph, src, delta_factor=1, mark_pred=True):
+    """-> (dist uint32[n], preds int32[n] or None, stats)."""
+    n = graph.local_nodes
+    dist = np.empty(n, dtype=np.uint32)
+    preds = np.empty(n, dtype=np.int32) if mark_pred else None
+    st = Stats()
+    _capi.check(_capi.lib().grb_sssp(graph._h, int(src), int(delta_factor), int(bool(mark_pred)),
+                                     _ptr(dist), _ptr(preds), C.byref(st)), "grb_sssp")
+    return dist, preds, st.as_dict()
+
+
+def cc(graph):
+    """-> (labels int32[n] = min vertex id of the component, num_components, stats)."""
+    labels = np.empty(graph.local_nodes, dtype=np.int32)
+    ncomp = C.c_int64()
+    st = Stats()
+    _capi.check(_capi.lib().grb_cc(graph._h, _ptr(labels), C.byref(ncomp), C.byref(st)), "grb_cc")
+    return labels, int(ncomp.value), st.as_dict()
+
+
+def pagerank(graph, src=-1, delta=0.85, threshold=1e-6, max_iter=1000, want_sorted=False):
+    """-> (ranks float64[n] in vertex order, (sorted_ids, sorted_ranks) or None, stats)."""
+    n = graph.local_nodes
+    ranks = np.empty(n, dtype=np.float64)
+    ids = np.empty(n, dtype=np.int32) if want_sorted else None
+    sr = np.empty(n, dtype=np.float32) if want_sorted else None
+    st = Stats()
+    _capi.check(_capi.lib().grb_pagerank(graph._h, int(src), float(delta), float(threshold), int(max_iter),
+                                         _ptr(ranks), _ptr(ids), _ptr(sr), C.byref(st)), "grb_pagerank")
+    return ranks, ((ids, sr) if want_sorted else None), st.as_dict()
+
+
+# ---- the reference's C API, argument for argument ---------------------------------------
+def _gunrock_graph(row_offsets, col_indices, edge_values=None):
+    ro = np.ascontiguousarray(row_offsets, dtype=np.int32)
+    co = np.ascontiguousarray(col_indices, dtype=np.int32)
+    ev = np.ascontiguousarray(edge_values, dtype=np.uint32) if edge_values is not None else None
+    g = _capi.GunrockGraph()
+    g.num_nodes = ro.size - 1
+    g.num_edges = co.size
+    g.row_offsets = ro.ctypes.data
+    g.col_indices = co.ctypes.data
+    g.edge_values = ev.ctypes.data if ev is not None else None
+    return g, (ro, co, ev)
+
+
+def _config(**kw):
+    c = _capi.GunrockConfig()
+    c.device = kw.get("device", 0)
+    c.mark_pred = kw.get("mark_pred", False)
+    c.idempotence = kw.get("idempotence", False)
+    c.src_mode = kw.get("src_mode", _capi.SRC_MANUALLY)
+    c.src_node = kw.get("src_node", 0)
+    c.queue_size = kw.get("queue_size", 1.0)
+    c.delta = kw.get("delta", 0.85)
+    c.error = kw.get("error", 0.01)
+    c.max_iter = kw.get("max_iter", 20)
+    c.top_nodes = kw.get("top_nodes", 0)
+    c.delta_factor = kw.get("delta_factor", 1)
+    return c
+
+
+def _take_node_values(out, n, dtype):
+    if not out.node_values:
+        raise GunrockError("library returned no node_values (see stderr)")
+    arr = np.ctypeslib.as_array(C.cast(out.node_values, C.POINTER(C.c_int32)), shape=(max(n, 1),))[:n]
+    res = arr.view(dtype).copy()
+    _capi.free_host(out.node_values)      # caller frees (shared_lib_tests/test_bfs.c:58,66)
+    return res
+
+
+def gunrock_bfs_func(row_offsets, col_indices, **cfg):
+    """gunrock_bfs_func on host CSR arrays -> int32 depths (gunrock.h:106-110)."""
+    g, keep = _gunrock_graph(row_offsets, col_indices)
+    out = _capi.GunrockGraph()
+    dt = _capi.GunrockDataType(_capi.VTXID_INT, _capi.SIZET_INT, _capi.VALUE_INT)
+    _capi.lib().gunrock_bfs_func(C.byref(out), C.byref(g), _config(**cfg), dt)
+    return _take_node_values(out, int(g.num_nodes), np.int32)
+
+
+def gunrock_cc_func(row_offsets, col_indices, **cfg):
+    g, keep = _gunrock_graph(row_offsets, col_indices)
+    out = _capi.GunrockGraph()
+    dt = _capi.GunrockDataType(_capi.VTXID_INT, _capi.SIZET_INT, _capi.VALUE_INT)
+    _capi.lib().gunrock_cc_func(C.byref(out), C.byref(g), _config(**cfg), dt)
+    return _take_node_values(out, int(g.num_nodes), np.int32)
+
+
+def gunrock_sssp_func(row_offsets, col_indices, edge_values, **cfg):
+    """-> (dist uint32[n], preds int32[n]) (gunrock.h:126-131)."""
+    g, keep = _gunrock_graph(row_offsets, col_indices, edge_values)
+    n = int(g.num_nodes)
+    out = _capi.GunrockGraph()
+    preds = np.empty(max(n, 1), dtype=np.int32)
+    dt = _capi.GunrockDataType(_capi.VTXID_INT, _capi.SIZET_INT, _capi.VALUE_UINT)
+    _capi.lib().gunrock_sssp_func(C.byref(out), _ptr(preds), C.byref(g), _config(**cfg), dt)
+    return _take_node_values(out, n, np.uint32), preds[:n]
+
+
+def gunrock_pr_func(row_offsets, col_indices, **cfg):
+    """-> (node_ids int32[k], ranks float32[k]) sorted by rank descending; k = top_nodes or n."""
+    g, keep = _gunrock_graph(row_offsets, col_indices)
+    n = int(g.num_nodes)
+    out = _capi.GunrockGraph()
+    ids = np.empty(max(n, 1), dtype=np.int32)
+    ranks = np.empty(max(n, 1), dtype=np.float32)
+    dt = _capi.GunrockDataType(_capi.VTXID_INT, _capi.SIZET_INT, _capi.VALUE_FLOAT)
+    c = _config(**cfg)
+    _capi.lib().gunrock_pr_func(C.byref(out), _ptr(ids), _ptr(ranks), C.byref(g), c, dt)
+    k = min(n, c.top_nodes) if c.top_nodes > 0 else n
+    return ids[:k], ranks[:k]

@@ -72,6 +72,20 @@ __global__ void BitmapToQueueKernel(const unsigned *bitmap, VertexId *queue, uns
     }
 }
 
+// sum of out-degrees of labelled vertices: the numerator of the reference's MiEdges/s figure,
+// which it computes on the host after Extract (gunrock/app/bfs/bfs_app.cu:82-91)
+template <typename VertexId, typename SizeT>
+__global__ void EdgesVisitedKernel(const VertexId *labels, const SizeT *row_offsets, long long local_nodes,
+                                   unsigned long long *out)
+{
+    __shared__ unsigned long long s_red[256 / 32 + 1];
+    unsigned long long mine = 0;
+    const long long stride = (long long)gridDim.x * blockDim.x;
+    for (long long v = (long long)blockIdx.x * blockDim.x + threadIdx.x; v < local_nodes; v += stride)
+        if (labels[v] > -1) mine += (unsigned long long)(row_offsets[v + 1] - row_offsets[v]);
+    oprtr::advance::BlockAccumulate<256>(mine, s_red, out);
+}
+
 struct BFSOptions {
     int    traversal_mode      = 0;      // 0: choose per level, 1: always LB, 2: always TWC (reference: --traversal-mode)
     bool   direction_optimized = false;  // allow the pull direction (needs an inverse graph)
@@ -143,6 +157,21 @@ class BFSEnactor : public EnactorBase {
         if (src < 0 || (long long)src >= problem->graph->nodes) return cudaSuccess;
         if constexpr (Problem::ENABLE_IDEMPOTENCE) return EnactIdempotent(problem, opt);
         else return EnactFused(problem, opt);
+    }
+
+    // recount edges_visited from the labels (idempotent mode cannot track it: duplicates)
+    cudaError_t RecountEdgesVisited(Problem *problem)
+    {
+        oprtr::LevelCounters *slot = work_progress.Slot(0);
+        GR_TRY(cudaMemsetAsync(slot, 0, sizeof(oprtr::LevelCounters), stream));
+        const long long ln = problem->graph->local_nodes;
+        EdgesVisitedKernel<VertexId, SizeT><<<util::FillGrid((unsigned long long)ln), 256, 0, stream>>>(
+            problem->labels.ptr, problem->graph->row_offsets.ptr, ln, &slot->aux0);
+        GR_TRY(cudaGetLastError());
+        oprtr::LevelCounters c;
+        GR_TRY(work_progress.Fetch(0, c, stream));
+        edges_visited = c.aux0;
+        return cudaSuccess;
     }
 
   private:

@@ -88,6 +88,7 @@ struct LbScratch {
     util::DeviceArray<SizeT>              row_start;   // [max_items]     first CSR entry of the item
     util::DeviceArray<unsigned long long> tile_desc;   // look-back descriptors of the scan
     util::DeviceArray<long long>          part_start;  // [max_tiles + 1] first item of each edge tile
+    util::DeviceArray<unsigned>           ticket;      // scan tiles are handed out in arrival order
     unsigned epoch = 0;                                // tags descriptors => no memset per call
 
     cudaError_t Allocate(size_t max_items, size_t max_edges, int scan_tile, int tile_edges, cudaStream_t s)
@@ -96,6 +97,8 @@ struct LbScratch {
         GR_TRY(row_start.Allocate(max_items + 1));
         GR_TRY(tile_desc.Allocate(max_items / scan_tile + 2));
         GR_TRY(part_start.Allocate(max_edges / tile_edges + 2));
+        GR_TRY(ticket.Allocate(1));
+        GR_TRY(ticket.Zero(s));
         epoch = 0;
         return tile_desc.Zero(s);
     }
@@ -107,6 +110,7 @@ struct LbScratchView {
     SizeT              *row_start;
     unsigned long long *tile_desc;
     long long          *part_start;
+    unsigned           *ticket;
     unsigned            epoch;
 };
 

@@ -58,8 +58,9 @@ __device__ __forceinline__ void StoreDesc(unsigned long long *p, unsigned long l
 // Executed by warp 0 of the CTA that owns `tile`.  Publishes the tile's
 // aggregate, walks predecessor descriptors 32 at a time until one carries an
 // inclusive prefix, publishes this tile's inclusive prefix and returns its
-// exclusive prefix.  Tiles are blockIdx-ordered (blocks are dispatched in
-// index order, the same assumption single-pass scans in CUB make).
+// exclusive prefix.  Tile numbers are tickets drawn in arrival order, so every
+// predecessor tile belongs to a CTA that is already running: the spin cannot
+// wait on a CTA that has not been scheduled.
 __device__ __forceinline__ unsigned long long LookbackExclusive(
     unsigned long long *desc, unsigned epoch, long long tile, unsigned long long aggregate)
 {
@@ -106,9 +107,12 @@ ScanKernel(Args<typename Policy::VertexId, typename Policy::SizeT> args,
 
     __shared__ ScanT s_warp[T / 32 + 1];
     __shared__ ScanT s_prefix;
+    __shared__ unsigned s_ticket;
 
     const unsigned long long in_len = args.d_in_len ? *args.d_in_len : args.in_len;
-    const long long tile = blockIdx.x;
+    if (threadIdx.x == 0) s_ticket = atomicAdd(scratch.ticket, 1u);
+    __syncthreads();
+    const long long tile = s_ticket;
     const unsigned long long base = (unsigned long long)tile * TILE;
     LevelCounters *slot_out = args.slots + ((args.queue_index + 1) & 3);
     if (base >= in_len) {
@@ -185,7 +189,10 @@ ExpandKernel(const __grid_constant__ typename Problem::DataSlice ds,
 
     const unsigned long long in_len = args.d_in_len ? *args.d_in_len : args.in_len;
     LevelCounters *slot_out = args.slots + ((args.queue_index + 1) & 3);
-    if (blockIdx.x == 0 && threadIdx.x == 0) ClearFutureSlot(args.slots, args.queue_index);
+    if (blockIdx.x == 0 && threadIdx.x == 0) {
+        ClearFutureSlot(args.slots, args.queue_index);
+        *scratch.ticket = 0;            // the scan of this call is complete (stream order)
+    }
 
     const ScanT total = scratch.scanned[in_len];
     const unsigned long long num_tiles = (total + TILE_E - 1) / TILE_E;

@@ -60,6 +60,7 @@ struct BfsRunner : BfsRunnerBase {
         GR_TRY(enactor.Enact(&problem, src, opt));
         GR_TRY(cudaEventRecord(e2, stream));
         GR_TRY(cudaEventSynchronize(e2));
+        if (IDEM) GR_TRY(enactor.RecountEdgesVisited(&problem));
         if (labels_host) GR_TRY(problem.Extract(labels_host, preds_host));
         if (stats) {
             float r = 0, t = 0;

@@ -1,0 +1,177 @@
+"""CPU: pins oracle/ (the checker) against the reference's golden vectors, against the
+reference's own graph code compiled here (oracle/_ref, when /root/reference exists) and
+against independent formulations."""
+import json
+import os
+
+import numpy as np
+import pytest
+
+from conftest import GOLDEN, load_golden, rmat_graph
+
+FIXTURE_FILES = {
+    "bips98_606": "simple_example/bips98_606.mtx",
+    "test_cc": "dataset/small/test_cc.mtx",
+    "test_pr": "dataset/small/test_pr.mtx",
+    "test_bc": "dataset/small/test_bc.mtx",
+    "chesapeake": "dataset/small/chesapeake.mtx",
+}
+HAVE_REF = os.path.isdir("/root/reference/gunrock")
+
+
+def test_shared_lib_goldens(orc, shared_lib):
+    """the vectors behind CMakeLists.txt:215-229 (BFS node 2 -> 1, CC node 1 -> 0,
+    SSSP node 1 -> 39 pred 0) on the 7-vertex graph of shared_lib_tests/test_*.c"""
+    ro, co, w = shared_lib["row_offsets"], shared_lib["col_indices"], shared_lib["edge_values"]
+    assert orc.bfs(ro, co, 0).tolist() == shared_lib["bfs_labels"]
+    dist, preds = orc.sssp(ro, co, w, 0)
+    assert dist.tolist() == shared_lib["sssp_dist"]
+    assert dist[1] == 39 and preds[1] == 0 and preds[0] == 0
+    labels, ncomp = orc.cc(ro, co)
+    assert labels.tolist() == shared_lib["cc_labels"] and ncomp == 1
+
+
+def test_random_node_sequence_matches_reference():
+    """RandomNode draws of an unseeded process (fixture made by the reference's own code)"""
+    import subprocess
+    import sys
+    want = json.load(open(os.path.join(GOLDEN, "randomnode.json")))
+    for n, seq in want.items():
+        code = ("import oracle; print(' '.join(str(oracle.random_node(%s)) for _ in range(8)))" % n)
+        out = subprocess.check_output([sys.executable, "-c", code], cwd=os.path.dirname(GOLDEN) + "/..")
+        assert [int(x) for x in out.split()] == seq
+    assert want["7"][0] == 0        # test_bfs.c / test_sssp.c (src_mode = randomize) start at vertex 0
+
+
+@pytest.mark.skipif(not HAVE_REF, reason="reference tree not present on this machine")
+@pytest.mark.parametrize("name", sorted(FIXTURE_FILES))
+@pytest.mark.parametrize("undirected", [True, False])
+def test_reader_matches_reference_graphio(orc, name, undirected):
+    n, ro, co, vals = orc.market_read(os.path.join("/root/reference", FIXTURE_FILES[name]), undirected=undirected)
+    gn, gro, gco, gvals = load_golden(name + ("" if undirected else "_dir"))
+    assert n == gn
+    assert np.array_equal(ro, gro) and np.array_equal(co, gco)
+    assert np.array_equal(vals.astype(np.int32), gvals)
+
+
+def test_bips98_shape():
+    n, ro, co, _ = load_golden("bips98_606")
+    assert (n, co.size) == (7135, 30380)        # SURVEY.md probe of the reference reader
+
+
+def test_coo_to_csr_rules(orc):
+    # duplicates, self loops, unsorted input, trailing empty rows (csr.cuh:266-288)
+    rows = [3, 0, 0, 2, 2, 0, 1, 1]
+    cols = [0, 2, 2, 2, 1, 1, 1, 0]
+    ro, co, _ = orc.coo_to_csr(6, rows, cols)
+    assert ro.tolist() == [0, 2, 3, 4, 5, 5, 5]
+    assert co.tolist() == [1, 2, 0, 1, 0]
+    ro, co, _ = orc.coo_to_csr(3, [], [])
+    assert ro.tolist() == [0, 0, 0, 0] and co.size == 0
+
+
+def _bfs_numpy(ro, co, src):
+    n = ro.size - 1
+    lab = np.full(n, -1, np.int32)
+    lab[src] = 0
+    frontier = np.array([src])
+    d = 0
+    while frontier.size:
+        d += 1
+        starts, ends = ro[frontier], ro[frontier + 1]
+        idx = np.concatenate([np.arange(s, e) for s, e in zip(starts, ends)]) if frontier.size < 2000 else \
+            np.repeat(starts - np.concatenate(([0], np.cumsum(ends - starts)[:-1])), ends - starts) + np.arange((ends - starts).sum())
+        nb = np.unique(co[idx])
+        nb = nb[lab[nb] == -1]
+        lab[nb] = d
+        frontier = nb
+    return lab
+
+
+@pytest.mark.parametrize("name", ["bips98_606", "chesapeake", "test_cc"])
+def test_bfs_against_level_synchronous_formulation(orc, name):
+    n, ro, co, _ = load_golden(name)
+    for src in (0, n // 2, n - 1):
+        assert np.array_equal(orc.bfs(ro, co, src), _bfs_numpy(ro, co, src))
+
+
+def test_bfs_preds_are_tree_edges(orc):
+    ro, co = rmat_graph(orc, 12)
+    labels, preds, depth = orc.bfs(ro, co, 0, want_preds=True)
+    assert preds[0] == -1 and depth == labels.max() + 1
+    v = np.nonzero((labels > 0))[0]
+    assert np.all(labels[preds[v]] + 1 == labels[v])
+    assert np.all(preds[labels == -1] == -1)
+
+
+def test_sssp_against_bellman_ford(orc):
+    ro, co = rmat_graph(orc, 10)
+    w = orc.edge_weights(ro, co, 7)
+    assert w.min() >= 1 and w.max() <= 64
+    dist, preds = orc.sssp(ro, co, w, 0)
+    n = ro.size - 1
+    src_of = np.repeat(np.arange(n), np.diff(ro))
+    d = np.full(n, np.iinfo(np.int64).max // 4, np.int64)
+    d[0] = 0
+    for _ in range(n):
+        nd = d.copy()
+        np.minimum.at(nd, co, d[src_of] + w)
+        if np.array_equal(nd, d):
+            break
+        d = nd
+    reach = d < np.iinfo(np.int64).max // 4
+    assert np.array_equal(dist[reach].astype(np.int64), d[reach])
+    assert np.all(dist[~reach] == np.uint32(0xFFFFFFFF))
+    # weights are symmetric (market.cuh:173-181 gives both directions the same value)
+    assert orc.lib().orc_edge_weight(3, 9, 7) == orc.lib().orc_edge_weight(9, 3, 7)
+
+
+def test_cc_min_label_and_count(orc):
+    n, ro, co, _ = load_golden("test_cc")
+    labels, ncomp = orc.cc(ro, co)
+    assert ncomp == 2                                   # {0..6}, {7..10}
+    assert labels.tolist() == [0] * 7 + [7] * 4
+    import scipy.sparse as sp
+    import scipy.sparse.csgraph as csg
+    ro2, co2 = rmat_graph(orc, 12)
+    n2 = ro2.size - 1
+    A = sp.csr_matrix((np.ones(co2.size, np.int8), co2, ro2), shape=(n2, n2))
+    k, lab = csg.connected_components(A, directed=False)
+    mine, ncomp2 = orc.cc(ro2, co2)
+    assert k == ncomp2
+    first = np.full(k, n2, np.int64)
+    np.minimum.at(first, lab, np.arange(n2))
+    assert np.array_equal(mine, first[lab].astype(np.int32))
+
+
+def test_pagerank_fixed_point(orc):
+    """PARITY UNPINNED by the reference's own tests (stale 0.402378 golden):
+    the restatement is checked for self-consistency only"""
+    n, ro, co, _ = load_golden("chesapeake")
+    r, it = orc.pagerank(ro, co, 0.85, 1e-12, 10000, -1)
+    deg = np.diff(ro)
+    src_of = np.repeat(np.arange(n), deg)
+    nxt = np.zeros(n)
+    np.add.at(nxt, co, (r / deg)[src_of])
+    assert np.allclose(0.85 * nxt + 0.15, r, atol=1e-9)
+    # the shipped semantics on shared_lib_tests/test_pr.c's config, as computed in SURVEY.md s4
+    ro7 = [0, 3, 6, 9, 11, 14, 15, 15]
+    co7 = [1, 2, 3, 0, 2, 4, 3, 4, 5, 5, 6, 2, 5, 6, 6]
+    r7, it7 = orc.pagerank(ro7, co7, 0.85, 0.01, 20, 0)
+    assert r7[6] == 0.0 and r7[5] == 0.0               # zero-out-degree vertices are pruned, iteratively
+
+
+def test_rmat_is_deterministic_and_canonical(orc):
+    ro, co = orc.rmat_csr(10, 16)
+    ro2, co2 = orc.rmat_csr(10, 16)
+    assert np.array_equal(ro, ro2) and np.array_equal(co, co2)
+    n = ro.size - 1
+    src_of = np.repeat(np.arange(n), np.diff(ro))
+    assert not np.any(src_of == co)                     # no self loops
+    key = src_of.astype(np.int64) * n + co
+    assert np.all(np.diff(key) > 0)                     # sorted by (row, col), no duplicates
+    import scipy.sparse as sp
+    A = sp.csr_matrix((np.ones(co.size, np.int8), co, ro), shape=(n, n))
+    assert (A != A.T).nnz == 0                          # undirected => symmetric
+    # skew like the reference's generator (a = 0.55): vertex 0 is a hub
+    assert np.diff(ro)[0] == np.diff(ro).max()

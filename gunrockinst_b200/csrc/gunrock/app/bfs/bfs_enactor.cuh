@@ -91,7 +91,7 @@ struct BFSOptions {
     bool   direction_optimized = false;  // allow the pull direction (needs an inverse graph)
     double alpha               = 14.0;   // push -> pull when frontier_edges > unexplored_edges / alpha
     double beta                = 24.0;   // pull -> push when frontier < n / beta and shrinking
-    unsigned long long lb_min_edges = 1u << 16;   // mode 0: LB from this many frontier edges upward
+    unsigned long long lb_min_edges = 1u << 12;   // mode 0: LB from this many frontier edges upward
     bool   record_levels       = false;  // keep a per-level trace (adds two events per level)
 };
 

@@ -19,18 +19,32 @@
 namespace gunrock {
 namespace graph {
 
-// 1D cyclic vertex partition over 2^log_parts devices
+// 1D striped vertex partition over 2^log_parts devices.
+// The reference's (unimplemented) rule is owner = v % P, local row = v / P
+// (problem_base.cuh:186-210).  The local-row rule is kept; the owner is the low
+// bits XOR a multiplicative hash of the local row.  Reason: R-MAT with the
+// reference's parameters and no vertex relabelling puts probability a+b = 0.75 on
+// every id bit being 0, so plain v % 8 would hand device 0 about 42 % of all
+// edges; XOR-ing with a well-mixed function of the other bits evens that out
+// while staying a bijection (v <-> (owner, local)) computed in two instructions.
 struct Partition {
     int log_parts = 0;      // number of devices = 1 << log_parts
     int rank      = 0;      // this device
 
     __host__ __device__ __forceinline__ int  Parts() const { return 1 << log_parts; }
-    __host__ __device__ __forceinline__ int  Owner(long long v) const { return (int)(v & (Parts() - 1)); }
+    __host__ __device__ __forceinline__ unsigned Mix(long long local) const
+    {
+        return log_parts ? (((unsigned)local * 0x9E3779B1u) >> (32 - log_parts)) : 0u;
+    }
+    __host__ __device__ __forceinline__ int  Owner(long long v) const
+    {
+        return (int)(((unsigned)v & (unsigned)(Parts() - 1)) ^ Mix(v >> log_parts));
+    }
     __host__ __device__ __forceinline__ bool Mine(long long v) const { return Owner(v) == rank; }
     __host__ __device__ __forceinline__ long long Local(long long v) const { return v >> log_parts; }
     __host__ __device__ __forceinline__ long long Global(long long local) const
     {
-        return (local << log_parts) | (long long)rank;
+        return (local << log_parts) | (long long)((unsigned)rank ^ Mix(local));
     }
 };
 

@@ -60,6 +60,7 @@ cudaError_t LaunchKernel(
         LbScratchView<typename Policy::SizeT> sv;
         sv.scanned = scratch->scanned.ptr;   sv.row_start = scratch->row_start.ptr;
         sv.tile_desc = scratch->tile_desc.ptr; sv.part_start = scratch->part_start.ptr; sv.ticket = scratch->ticket.ptr;
+        sv.part_cap = scratch->part_start.cap;
         sv.epoch = scratch->epoch;
         unsigned long long scan_tiles = (args.in_len + Policy::SCAN_TILE - 1) / Policy::SCAN_TILE;
         unsigned scan_grid = (unsigned)(scan_tiles < 1 ? 1 : scan_tiles);

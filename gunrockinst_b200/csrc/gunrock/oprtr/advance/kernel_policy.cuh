@@ -111,6 +111,7 @@ struct LbScratchView {
     unsigned long long *tile_desc;
     long long          *part_start;
     unsigned           *ticket;
+    unsigned long long  part_cap;       // entries in part_start
     unsigned            epoch;
 };
 

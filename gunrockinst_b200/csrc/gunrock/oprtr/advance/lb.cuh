@@ -155,7 +155,7 @@ ScanKernel(Args<typename Policy::VertexId, typename Policy::SizeT> args,
             scratch.scanned[i]   = b;
             scratch.row_start[i] = first[r];
             // this item owns every tile boundary that falls inside [b, e)
-            for (ScanT k = (b + TILE_EDGES - 1) / TILE_EDGES; k * TILE_EDGES < e; ++k)
+            for (ScanT k = (b + TILE_EDGES - 1) / TILE_EDGES; k * TILE_EDGES < e && k < scratch.part_cap; ++k)
                 scratch.part_start[k] = (long long)i;
         }
     }
@@ -195,7 +195,11 @@ ExpandKernel(const __grid_constant__ typename Problem::DataSlice ds,
     }
 
     const ScanT total = scratch.scanned[in_len];
-    const unsigned long long num_tiles = (total + TILE_E - 1) / TILE_E;
+    unsigned long long num_tiles = (total + TILE_E - 1) / TILE_E;
+    if (num_tiles > scratch.part_cap) {     // a frontier with duplicates expanded past the scratch
+        num_tiles = scratch.part_cap;
+        if (threadIdx.x == 0) slot_out->overflow = 1;
+    }
     Stager<Policy> stager(s_stager, args, slot_out);
     stager.Init();
     unsigned long long my_edges = 0;

@@ -127,8 +127,10 @@ Kernel(const __grid_constant__ typename Problem::DataSlice ds,
                 for (int r = 0; r < IPT; ++r) {
                     if (id[r] < 0) continue;
                     const unsigned bit = 1u << (ds.BitPos(id[r]) & 31);
-                    if (word[r] & bit) id[r] = -1;                         // seen it
-                    else atomicOr(ds.d_visited_mask + (ds.BitPos(id[r]) >> 5), bit);   // best effort, like the reference
+                    // the cached probe may be stale; the atomic's return value is exact, so one
+                    // claimant per vertex survives (the reference's byte RMW is best effort)
+                    if ((word[r] & bit) || (atomicOr(ds.d_visited_mask + (ds.BitPos(id[r]) >> 5), bit) & bit))
+                        id[r] = -1;
                 }
             }
         }

@@ -69,7 +69,8 @@ struct KernelPolicy {
 template <typename VertexId, typename SizeT>
 struct Args {
     graph::CsrView<VertexId, SizeT> g;          // graph to walk (inverse view for pull)
-    const VertexId     *in_queue;               // input frontier (vertex ids, -1 = hole)
+    const VertexId     *in_queue;               // input frontier (vertex ids, -1 = hole); NULL = every owned
+                                                // vertex in local-row order (in_len = local_nodes)
     VertexId           *out_queue;              // output frontier or NULL
     unsigned long long  in_len;                 // host-known input length ...
     const unsigned long long *d_in_len;         // ... or, if non-NULL, read it here

@@ -130,7 +130,7 @@ ScanKernel(Args<typename Policy::VertexId, typename Policy::SizeT> args,
         unsigned long long i = base + (unsigned long long)r * T + threadIdx.x;
         deg[r] = 0; first[r] = 0;
         if (i < in_len) {
-            VertexId v = util::LoadStream(args.in_queue + i);
+            VertexId v = args.in_queue ? util::LoadStream(args.in_queue + i) : (VertexId)args.g.part.Global((long long)i);
             if (v >= 0 && (long long)v < args.g.nodes) {
                 long long row = args.g.part.Local(v);
                 SizeT a = args.g.row_offsets[row], b = args.g.row_offsets[row + 1];
@@ -219,7 +219,7 @@ ExpandKernel(const __grid_constant__ typename Problem::DataSlice ds,
                 long long rel = (long long)s - (long long)tile_start;
                 s_rel[j]  = rel < -1 ? -1 : (int)rel;
                 s_base[j] = (long long)scratch.row_start[i0 + j] - (long long)s;
-                if constexpr (NEED_SRC) s_src[j] = args.in_queue[i0 + j];
+                if constexpr (NEED_SRC) s_src[j] = args.in_queue ? args.in_queue[i0 + j] : (VertexId)args.g.part.Global(i0 + j);
             }
         }
         __syncthreads();
@@ -270,7 +270,8 @@ ExpandKernel(const __grid_constant__ typename Problem::DataSlice ds,
             bool ok = false;
             if (live[r]) {
                 VertexId s_id;
-                if constexpr (NEED_SRC) s_id = windowed ? s_src[item[r]] : args.in_queue[i0 + item[r]];
+                if constexpr (NEED_SRC) s_id = windowed ? s_src[item[r]]
+                                      : (args.in_queue ? args.in_queue[i0 + item[r]] : (VertexId)args.g.part.Global(i0 + item[r]));
                 else                    s_id = (VertexId)args.iteration;
                 ok = VisitEdge<Policy, Problem, Functor>(&ds, s_id, nbr[r], (SizeT)pos[r], (SizeT)(i0 + item[r]));
             }

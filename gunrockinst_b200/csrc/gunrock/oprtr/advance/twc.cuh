@@ -102,7 +102,7 @@ Kernel(const __grid_constant__ typename Problem::DataSlice ds,
         VertexId v = -1;
         long long begin = 0, end = 0;
         if (i < in_len) {
-            v = util::LoadStream(args.in_queue + i);
+            v = args.in_queue ? util::LoadStream(args.in_queue + i) : (VertexId)args.g.part.Global((long long)i);
             if (v >= 0 && (long long)v < args.g.nodes) {
                 long long row = args.g.part.Local(v);
                 begin = (long long)args.g.row_offsets[row];

@@ -18,7 +18,9 @@ extern "C" int grb_graph_rmat(int device, int scale, int64_t edges, uint64_t see
     if (rc) return rc;
     // upper bound on the entries this device can hold decides the offset width
     const unsigned long long bound = (undirected ? 2ull : 1ull) * (unsigned long long)edges;
-    int ob = force_offset_bytes ? force_offset_bytes : ((bound >> log_parts) * 2 >= 0x7fffffffull ? 8 : 4);
+    // (a device's share of a hashed partition stays well within 1.5x the mean)
+    const unsigned long long share = log_parts ? (bound >> log_parts) + (bound >> (log_parts + 1)) : bound;
+    int ob = force_offset_bytes ? force_offset_bytes : (share >= 0x7fffffffull ? 8 : 4);
     if (ob != 4 && ob != 8) return (int)cudaErrorInvalidValue;
     grb_graph_s *h = new grb_graph_s();
     h->offset_bytes = ob;

@@ -1,0 +1,372 @@
+#!/usr/bin/env python
+"""bench.py -- BFS GTEPS on seeded synthetic R-MAT graphs (BASELINE.json's metric).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl b200|reference] [--scale S]
+
+One JSON line on stdout (rank 0).  A *step* is one breadth-first search from one
+source of a fixed seeded source list over the resident graph.
+
+  N = 1   BASELINE.json configs[1]: direction-optimising BFS, R-MAT scale 22,
+          edgefactor 16, undirected, graph resident in HBM.
+  N > 1   BASELINE.json configs[4]: R-MAT scale 27, 1D vertex-partitioned over N
+          devices (one process per device), per-level frontier exchange over NCCL.
+
+value   = sum(edges_visited) / device time of the K steps (CUDA events on the stream the
+          library launches on, max over ranks); edges_visited = sum of out-degrees of the
+          visited vertices, the reference's own numerator (gunrock/app/bfs/bfs_app.cu:82-91).
+e2e     = same metric through the reference's C entry point gunrock_bfs_func
+          (gunrock/gunrock.h:106-110) with the CSR in pinned HOST memory: upload, search and
+          label download are all inside the timed region.
+roofline, cpu_baseline: see DESIGN.md section "Measurement".
+
+--impl reference times the reference's CPU BFS (tests/bfs/test_bfs.cu:258-322, restated in
+oracle/oracle.c -- the reference TU itself does not compile) on the host cores.
+"""
+import argparse
+import contextlib
+import json
+import os
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+METRIC = "bfs_gteps_rmat"
+UNIT = "GTEPS"
+N_SOURCES = 64
+
+
+def env_int(name, default):
+    try:
+        return int(os.environ.get(name, default))
+    except ValueError:
+        return default
+
+
+@contextlib.contextmanager
+def quiet_stdout():
+    """the reference API prints its statistics with printf (bfs_app.cu:103-118); keep this
+    program's stdout to the one JSON line"""
+    sys.stdout.flush()
+    saved = os.dup(1)
+    devnull = os.open(os.devnull, os.O_WRONLY)
+    os.dup2(devnull, 1)
+    try:
+        yield
+    finally:
+        os.dup2(saved, 1)
+        os.close(devnull)
+        os.close(saved)
+
+
+class ClockSampler:
+    """SM clock / throttle reasons sampled through NVML while the timed region runs"""
+
+    def __init__(self, index):
+        self.samples, self.reasons, self.stop_flag, self.thread = [], set(), False, None
+        self.max_mhz = None
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.max_mhz = pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM)
+        except Exception:
+            self.nv = None
+
+    def _loop(self):
+        nv = self.nv
+        names = {"hw_slowdown": getattr(nv, "nvmlClocksEventReasonHwSlowdown", 0x8),
+                 "hw_thermal_slowdown": getattr(nv, "nvmlClocksEventReasonHwThermalSlowdown", 0x40),
+                 "sw_thermal_slowdown": getattr(nv, "nvmlClocksEventReasonSwThermalSlowdown", 0x20),
+                 "sw_power_cap": getattr(nv, "nvmlClocksEventReasonSwPowerCap", 0x4)}
+        while not self.stop_flag:
+            try:
+                self.samples.append(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM))
+                try:
+                    r = nv.nvmlDeviceGetCurrentClocksEventReasons(self.h)
+                except Exception:
+                    r = nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
+                for k, bit in names.items():
+                    if r & bit:
+                        self.reasons.add(k)
+            except Exception:
+                pass
+            time.sleep(0.002)
+
+    def start(self):
+        if self.nv:
+            self.stop_flag = False
+            self.thread = threading.Thread(target=self._loop, daemon=True)
+            self.thread.start()
+
+    def stop(self):
+        if self.thread:
+            self.stop_flag = True
+            self.thread.join()
+            self.thread = None
+
+    def summary(self):
+        s = sorted(self.samples)
+        return {"sm_mhz": (s[len(s) // 2] if s else None), "sm_max_mhz": self.max_mhz,
+                "samples": len(s), "reasons": sorted(self.reasons)}
+
+
+def pick_sources(row_offsets, count, seed, global_ids=None):
+    """vertex 0 (the R-MAT hub) first, then seeded random vertices with at least one edge"""
+    import numpy as np
+    deg = np.diff(row_offsets)
+    rng = np.random.RandomState(seed)
+    out = []
+    if deg.size and deg[0] > 0:
+        out.append(0)
+    while len(out) < count and deg.size:
+        v = int(rng.randint(0, deg.size))
+        if deg[v] > 0:
+            out.append(v)
+    return out
+
+
+def measured_peaks():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json)"
+    except Exception:
+        return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+def ncu_traffic(kernel_key):
+    """per-launch DRAM bytes of the dominant kernel from the committed ncu capture, if any"""
+    try:
+        with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
+            return json.load(f).get(kernel_key)
+    except Exception:
+        return None
+
+
+def level_bytes(rec, offset_bytes, nodes):
+    """algorithmic HBM bytes of one executed level"""
+    F, E, D = rec["frontier"], rec["edges"], rec["discovered"]
+    if rec["kind"] == "pull":
+        return rec["candidates"] * 2 * offset_bytes + 5 * E + 4 * D + 3 * (nodes // 8)
+    return F * (4 + 2 * offset_bytes) + 5 * E + 8 * D
+
+
+# ----------------------------------------------------------------------------------------
+# reference arm: the reference's CPU BFS on the host cores
+# ----------------------------------------------------------------------------------------
+def run_reference(args, rank, world):
+    if rank != 0:
+        return
+    import numpy as np
+    import oracle
+    oracle.build()
+    scale = args.scale
+    t0 = time.time()
+    graph_source = "oracle generator (CPU)"
+    ro = co = None
+    try:        # input synthesis only: the seeded device generator yields the identical CSR in seconds
+        import gunrockinst_b200 as gr
+        if gr.device_count() > 0:
+            g = gr.Graph.rmat(scale)
+            ro, co = g.download()
+            g.close()
+            graph_source = "device generator (input synthesis only; same seeded CSR as oracle.rmat_csr)"
+    except Exception:
+        ro = None
+    if ro is None:
+        ro, co = oracle.rmat_csr(scale)
+    sources = pick_sources(ro, N_SOURCES, 1234 + scale)
+    sampler = oracle.BfsSampler(ro, co)
+    # bounded sample: each step scans at most `cap` neighbour entries of the search
+    cap = args.ref_edge_cap
+    for i in range(args.warmup):
+        sampler.run(sources[i % len(sources)], cap)
+    edges = 0
+    secs = 0.0
+    for i in range(args.steps):
+        e, t = sampler.run(sources[i % len(sources)], cap)
+        edges += e
+        secs += t
+    value = edges / secs / 1e9 if secs > 0 else 0.0
+    sample = "first <= %d scanned neighbour entries of each of %d searches (serial FIFO BFS)" % (cap, args.steps)
+    line = {
+        "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * secs / max(args.steps, 1),
+        "higher_is_better": True, "scaling": "strong" if args.gpus > 1 else "weak", "vs_baseline": None,
+        "dtype": "int32", "data": "synthetic",
+        "config": workload_config(args, scale, int(ro.size - 1), int(co.size)),
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": 1, "kind": "port", "sample": sample,
+                         "cores_available": os.cpu_count(), "graph_source": graph_source},
+        "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0, "setup_s": round(time.time() - t0 - secs, 2),
+    }
+    print(json.dumps(line), flush=True)
+
+
+def workload_config(args, scale, nodes, edges):
+    if args.gpus == 1:
+        w = "direction-optimising BFS, R-MAT scale %d edgefactor 16 undirected (BASELINE configs[1])" % scale
+    else:
+        w = ("BFS, R-MAT scale %d edgefactor 16 undirected, 1D vertex-partitioned over %d devices, "
+             "per-level NCCL frontier exchange (BASELINE configs[4])" % (scale, args.gpus))
+    return {"workload": w, "scale": scale, "edgefactor": 16, "nodes": nodes, "directed_edges": edges,
+            "rmat_abcd": [0.55, 0.2, 0.2, 0.05], "seed": 42 + scale, "sources": N_SOURCES,
+            "l2_policy": "inputs larger than L2 (CSR %.2f GB vs 126 MB L2); labels/bitmaps are re-initialised "
+                         "every step" % ((4.0 * edges + 4.0 * nodes) / 1e9)}
+
+
+# ----------------------------------------------------------------------------------------
+# B200 arm, one device
+# ----------------------------------------------------------------------------------------
+def run_single(args):
+    import numpy as np
+    import torch
+    import gunrockinst_b200 as gr
+    gr._capi.lib()                      # fails loudly if libgunrock.so is missing: no CPU path
+    if gr.device_count() < 1 or not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; the product path has no CPU fallback")
+    torch.cuda.set_device(0)
+    scale = args.scale
+    t_setup = time.time()
+    g = gr.Graph.rmat(scale)
+    n, m, osz = g.nodes, g.edges, int(g.info.offset_bytes)
+    ro, co = g.download()
+    sources = pick_sources(ro, N_SOURCES, 1234 + scale)
+    bfs = gr.Bfs(g, direction_optimized=True)
+    stream = torch.cuda.ExternalStream(g.stream())
+    clocks = ClockSampler(0)
+
+    for i in range(max(args.warmup, 3)):
+        bfs.run(sources[i % len(sources)], want_labels=False)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    torch.cuda.synchronize()
+    clocks.start()
+    edges = launches = algo_bytes = 0
+    e0.record(stream)
+    for i in range(args.steps):
+        _, _, st = bfs.run(sources[i % len(sources)], want_labels=False)
+        edges += st["edges_visited"]
+        launches += st["gpu_launches"]
+        algo_bytes += st["algo_bytes"]
+    e1.record(stream)
+    torch.cuda.synchronize()
+    clocks.stop()
+    ms = e0.elapsed_time(e1)
+    value = edges / (ms * 1e-3) / 1e9
+
+    # ---- per-kernel roofline: one traced pass over the same sources (events around every level)
+    tr = gr.Bfs(g, direction_optimized=True, record_levels=True)
+    for i in range(3):
+        tr.run(sources[i % len(sources)], want_labels=False)
+    agg = {}
+    for i in range(min(args.steps, len(sources))):
+        tr.run(sources[i % len(sources)], want_labels=False)
+        for rec in tr.levels():
+            a = agg.setdefault(rec["kind"], {"ms": 0.0, "bytes": 0, "launches": 0})
+            a["ms"] += rec["ms"]
+            a["bytes"] += level_bytes(rec, osz, n)
+            a["launches"] += 1
+    tr.close()
+    dom = max(agg, key=lambda k: agg[k]["ms"])
+    peak, peak_src = measured_peaks()
+    kernel_names = {"pull": "advance::pull::Kernel", "push-lb": "advance::lb::ScanKernel+ExpandKernel",
+                    "push-twc": "advance::twc::Kernel"}
+    achieved = agg[dom]["bytes"] / (agg[dom]["ms"] * 1e-3) / 1e9 if agg[dom]["ms"] > 0 else 0.0
+    roofline = {"bound": "hbm", "kernel": kernel_names.get(dom, dom), "achieved": achieved, "peak": peak,
+                "unit": "GB/s", "frac": achieved / peak, "peak_source": peak_src,
+                "traffic": ncu_traffic(dom),
+                "launches_timed": agg[dom]["launches"],
+                "avg_launch_us": 1e3 * agg[dom]["ms"] / max(agg[dom]["launches"], 1),
+                "algo_bytes_per_launch": agg[dom]["bytes"] / max(agg[dom]["launches"], 1),
+                "share_of_kernel_time": agg[dom]["ms"] / sum(a["ms"] for a in agg.values()),
+                "whole_step": {"algo_bytes_per_step": algo_bytes / max(args.steps, 1),
+                               "achieved": algo_bytes / (ms * 1e-3) / 1e9,
+                               "frac": algo_bytes / (ms * 1e-3) / 1e9 / peak}}
+
+    # ---- end to end through the reference's entry point, CSR in pinned host memory
+    ro32 = torch.from_numpy(ro.astype(np.int32)).pin_memory()
+    co32 = torch.from_numpy(co).pin_memory()
+    e2e_steps = max(1, min(args.steps, args.e2e_steps))
+    deg = np.diff(ro)
+    e2e_edges, e2e_s = 0, 0.0
+    with quiet_stdout():
+        for i in range(2):
+            gr.gunrock_bfs_func(ro32.numpy(), co32.numpy(), src_node=sources[0])
+        for i in range(e2e_steps):
+            torch.cuda.synchronize()
+            t0 = time.perf_counter()
+            last = gr.gunrock_bfs_func(ro32.numpy(), co32.numpy(), src_node=sources[i % len(sources)])
+            e2e_s += time.perf_counter() - t0       # the call returns after its own cudaDeviceSynchronize
+            e2e_edges += int(deg[last >= 0].sum())   # host bookkeeping of the result, outside the timed call
+    e2e_s = max(e2e_s, 1e-9)
+    e2e = {"value": e2e_edges / e2e_s / 1e9, "unit": UNIT, "h2d_bytes_per_step": int(4 * (n + 1) + 4 * m),
+           "d2h_bytes_per_step": int(4 * n), "ms_per_step": 1e3 * e2e_s / e2e_steps, "steps": e2e_steps,
+           "api": "gunrock_bfs_func (gunrock.h:106-110): upload CSR from pinned host memory, top-down BFS, "
+                  "download labels"}
+
+    # ---- CPU baseline (the checker, timed on one host core) + parity of the timed path
+    cpu = {"value": None, "unit": UNIT, "cores": 1, "kind": "port", "sample": "skipped"}
+    parity = None
+    if not args.no_cpu:
+        import oracle
+        oracle.build()
+        sampler = oracle.BfsSampler(ro, co)
+        ce, cs, k = 0, 0.0, 0
+        while cs < args.cpu_seconds and k < len(sources):
+            e, t = sampler.run(sources[k])
+            if k == 0:
+                labels, _, _ = bfs.run(sources[0])
+                parity = bool(np.array_equal(labels, sampler.labels[:n]))
+            ce += e
+            cs += t
+            k += 1
+        cpu = {"value": ce / cs / 1e9, "unit": UNIT, "cores": 1, "cores_available": os.cpu_count(), "kind": "port",
+               "sample": "%d complete searches of the same graph (sources[0:%d]), %.1f s of serial FIFO BFS "
+                         "(tests/bfs/test_bfs.cu:258-322 restated in oracle/oracle.c)" % (k, k, cs)}
+    line = {
+        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": 1, "steps": args.steps, "warmup": max(args.warmup, 3),
+        "ms_per_step": ms / max(args.steps, 1), "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "int32", "data": "synthetic", "config": workload_config(args, scale, n, m),
+        "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": launches,
+        "clocks": clocks.summary(), "parity_vs_oracle": parity,
+        "graph500_gteps": value / 2.0, "setup_s": round(time.time() - t_setup, 1),
+    }
+    bfs.close()
+    g.close()
+    print(json.dumps(line), flush=True)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=256)
+    ap.add_argument("--warmup", type=int, default=8)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--scale", type=int, default=0, help="R-MAT scale (default: 22 on one device, 27 partitioned)")
+    ap.add_argument("--e2e-steps", type=int, default=8)
+    ap.add_argument("--cpu-seconds", type=float, default=12.0)
+    ap.add_argument("--ref-edge-cap", type=int, default=20_000_000)
+    ap.add_argument("--no-cpu", action="store_true")
+    args = ap.parse_args()
+    world = env_int("WORLD_SIZE", 1)
+    rank = env_int("RANK", 0)
+    if world > 1:
+        args.gpus = world
+    if args.scale <= 0:
+        args.scale = 22 if args.gpus == 1 else 27
+    if args.impl == "reference":
+        run_reference(args, rank, world)
+        return
+    if args.gpus == 1:
+        run_single(args)
+    else:
+        from gunrockinst_b200 import partitioned
+        partitioned.bench(args, rank, world, workload_config, ClockSampler, pick_sources, measured_peaks)
+
+
+if __name__ == "__main__":
+    main()

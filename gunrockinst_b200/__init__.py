@@ -99,6 +99,12 @@ class Graph:
                     "grb_graph_device_ptrs")
         return a.value, b.value, c.value
 
+    def stream(self):
+        """cudaStream_t (as int) the library issues this graph's work on"""
+        s = C.c_void_p()
+        _capi.check(_capi.lib().grb_graph_stream(self._h, C.byref(s)), "grb_graph_stream")
+        return s.value or 0
+
     def close(self):
         if self._h:
             _capi.lib().grb_graph_destroy(self._h)

@@ -121,6 +121,7 @@ def lib():
     sig("grb_graph_get_info", C.c_int, [p, C.POINTER(GraphInfo)])
     sig("grb_graph_download", C.c_int, [p, p, p, p])
     sig("grb_graph_device_ptrs", C.c_int, [p, pp, pp, pp])
+    sig("grb_graph_stream", C.c_int, [p, pp])
     sig("grb_graph_destroy", None, [p])
     sig("grb_bfs_create", C.c_int, [p, C.POINTER(BfsConfig), pp])
     sig("grb_bfs_run", C.c_int, [p, i32, p, p, C.POINTER(Stats)])

@@ -98,6 +98,13 @@ extern "C" int grb_graph_device_ptrs(grb_graph_t g, void **row_offsets, void **c
     return 0;
 }
 
+extern "C" int grb_graph_stream(grb_graph_t g, void **cuda_stream)
+{
+    if (!g || !cuda_stream) return (int)cudaErrorInvalidValue;
+    *cuda_stream = (void *)g->stream;
+    return 0;
+}
+
 extern "C" void grb_graph_destroy(grb_graph_t g)
 {
     if (!g) return;

@@ -72,6 +72,9 @@ int  grb_graph_get_info(grb_graph_t g, grb_graph_info *info);
 int  grb_graph_download(grb_graph_t g, void *row_offsets, int32_t *col_indices, uint32_t *weights);
 /* raw device pointers of the resident arrays (for harness-side collectives) */
 int  grb_graph_device_ptrs(grb_graph_t g, void **row_offsets, void **col_indices, void **weights);
+/* the CUDA stream (cudaStream_t) every operation on this graph is issued on, so a
+ * harness can bracket runs with its own events */
+int  grb_graph_stream(grb_graph_t g, void **cuda_stream);
 void grb_graph_destroy(grb_graph_t g);
 
 /* ---- run statistics ---------------------------------------------------------

@@ -45,6 +45,8 @@ def lib():
         L.orc_largest_degree_node.argtypes = [i64, p]
         L.orc_bfs.restype = C.c_int
         L.orc_bfs.argtypes = [i64, p, p, i32, p, p]
+        L.orc_bfs_sample.restype = C.c_int
+        L.orc_bfs_sample.argtypes = [i64, p, p, i32, p, p, i64, C.POINTER(i64)]
         L.orc_edges_visited.restype = i64
         L.orc_edges_visited.argtypes = [i64, p, p]
         L.orc_sssp.restype = None
@@ -142,6 +144,28 @@ def bfs_timed(row_offsets, col, src):
     L.orc_bfs(n, _ptr(ro), _ptr(co), int(src), _ptr(labels), None)
     t1 = L.orc_now_seconds()
     return labels, t1 - t0
+
+
+class BfsSampler:
+    """Repeated (optionally edge-bounded) CPU BFS on one CSR for bench.py's CPU legs:
+    arrays are converted once, scratch is preallocated, and each call is timed around
+    the traversal only (tests/bfs/test_bfs.cu:282-317)."""
+
+    def __init__(self, row_offsets, col):
+        self.ro, self.co = _offs(row_offsets), _cols(col)
+        self.n = self.ro.size - 1
+        self.labels = np.empty(max(self.n, 1), dtype=np.int32)
+        self.queue = np.empty(max(self.n, 1), dtype=np.int32)
+
+    def run(self, src, max_edges=0):
+        """-> (edges_scanned, seconds)"""
+        L = lib()
+        scanned = C.c_int64()
+        t0 = L.orc_now_seconds()
+        L.orc_bfs_sample(self.n, _ptr(self.ro), _ptr(self.co), int(src), _ptr(self.labels), _ptr(self.queue),
+                         int(max_edges), C.byref(scanned))
+        t1 = L.orc_now_seconds()
+        return int(scanned.value), t1 - t0
 
 
 def edges_visited(row_offsets, labels):

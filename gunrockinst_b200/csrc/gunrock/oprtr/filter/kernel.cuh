@@ -52,7 +52,7 @@ struct KernelPolicy {
 
 template <typename VertexId, typename Value>
 struct Args {
-    const VertexId     *in_queue;           // may contain -1 holes
+    const VertexId     *in_queue;           // may contain -1 holes; NULL = the identity frontier 0..in_len-1
     const VertexId     *in_pred_queue;      // optional parallel queue (MARK_PREDECESSORS problems)
     VertexId           *out_queue;          // NULL: count survivors only
     unsigned long long  in_len;             // host-known length (or upper bound when d_in_len is set)
@@ -97,7 +97,7 @@ Kernel(const __grid_constant__ typename Problem::DataSlice ds,
 #pragma unroll
         for (int r = 0; r < IPT; ++r) {
             const unsigned long long i = base + (unsigned long long)r * THREADS + threadIdx.x;
-            id[r] = (i < in_len) ? util::LoadStream(args.in_queue + i) : (VertexId)-1;
+            id[r] = (i < in_len) ? (args.in_queue ? util::LoadStream(args.in_queue + i) : (VertexId)i) : (VertexId)-1;
             pred[r] = (VertexId)args.iteration;
             if (Problem::MARK_PREDECESSORS && args.in_pred_queue && i < in_len)
                 pred[r] = util::LoadStream(args.in_pred_queue + i);

@@ -63,7 +63,7 @@ class BfsConfig(C.Structure):
 class MgLevel(C.Structure):
     _fields_ = [("frontier_local", C.c_uint64), ("frontier_edges", C.c_uint64),
                 ("edges_inspected", C.c_uint64), ("candidates", C.c_uint64),
-                ("outbox_len", C.c_uint64 * 16)]
+                ("overflow", C.c_uint64), ("gpu_launches", C.c_uint64)]
 
 
 # gunrock.h (reference ABI, gunrock/gunrock.h:51-99)
@@ -134,22 +134,24 @@ def lib():
     sig("grb_test_advance", C.c_int, [p, C.c_int, C.c_int, p, i64, p, i64, C.POINTER(i64), p, p, p,
                                       C.POINTER(u64)])
     sig("grb_test_filter", C.c_int, [C.c_int, i64, C.c_int, p, i64, p, i64, C.POINTER(i64), p])
-    sig("grb_mgbfs_create", C.c_int, [p, u64, pp])
+    sig("grb_mgbfs_create", C.c_int, [p, pp])
     sig("grb_mgbfs_reset", C.c_int, [p, i32, C.POINTER(u64)])
     sig("grb_mgbfs_buffer", C.c_int, [p, C.c_int, pp, C.POINTER(u64)])
-    sig("grb_mgbfs_pull", C.c_int, [p, i32, C.c_int, C.POINTER(MgLevel)])
-    sig("grb_mgbfs_push", C.c_int, [p, i32, C.c_int, C.POINTER(MgLevel)])
-    sig("grb_mgbfs_absorb_inbox", C.c_int, [p, i32, u64, C.POINTER(MgLevel)])
-    sig("grb_mgbfs_absorb_dense", C.c_int, [p, i32, C.POINTER(MgLevel)])
-    sig("grb_mgbfs_queue_to_map", C.c_int, [p, C.c_int])
-    sig("grb_mgbfs_map_to_queue", C.c_int, [p, C.c_int, C.POINTER(MgLevel)])
+    sig("grb_mgbfs_push", C.c_int, [p, i32, u64, u64])
+    sig("grb_mgbfs_absorb", C.c_int, [p, i32, C.c_int])
+    sig("grb_mgbfs_pull", C.c_int, [p, i32, C.c_int])
     sig("grb_mgbfs_merge_visited", C.c_int, [p, C.c_int])
+    sig("grb_mgbfs_queue_to_map", C.c_int, [p, C.c_int, u64])
+    sig("grb_mgbfs_map_to_queue", C.c_int, [p, C.c_int])
+    sig("grb_mgbfs_counters", C.c_int, [p, C.POINTER(MgLevel)])
     sig("grb_mgbfs_sync", C.c_int, [p])
     sig("grb_mgbfs_stream", C.c_int, [p, pp])
     sig("grb_mgbfs_labels", C.c_int, [p, p])
     sig("grb_mgbfs_destroy", None, [p])
-    for name in ("gunrock_bfs_func", "gunrock_cc_func"):
+    for name in ("gunrock_bfs_func", "gunrock_cc_func", "gunrock_bc_func"):
         sig(name, None, [C.POINTER(GunrockGraph), C.POINTER(GunrockGraph), GunrockConfig, GunrockDataType])
+    sig("gunrock_topk_func", None, [C.POINTER(GunrockGraph), p, p, p, C.POINTER(GunrockGraph),
+                                    GunrockConfig, GunrockDataType])
     sig("gunrock_sssp_func", None, [C.POINTER(GunrockGraph), p, C.POINTER(GunrockGraph),
                                     GunrockConfig, GunrockDataType])
     sig("gunrock_pr_func", None, [C.POINTER(GunrockGraph), p, p, C.POINTER(GunrockGraph),

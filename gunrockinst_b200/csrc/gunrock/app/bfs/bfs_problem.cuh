@@ -56,10 +56,9 @@ struct BFSProblem : ProblemBase<_VertexId, _SizeT> {
         VertexId   level;           // depth of the frontier being expanded
         long long  nodes, local_nodes;
         graph::Partition part;
-        // multi-GPU push: per-owner outboxes for vertices owned elsewhere
-        VertexId  *d_outbox;        // [parts][outbox_cap]
-        unsigned long long *d_outbox_len;   // [parts]
-        unsigned long long  outbox_cap;
+        // partitioned push: discoveries (of any owner) are set in this GLOBAL bitmap, whose
+        // owner-major segments are then exchanged all-to-all (NULL on a single device)
+        unsigned  *d_next_map;
 
         __host__ __device__ __forceinline__ unsigned long long BitPos(VertexId v) const
         {
@@ -70,6 +69,7 @@ struct BFSProblem : ProblemBase<_VertexId, _SizeT> {
 
     util::DeviceArray<VertexId> labels, preds;
     util::DeviceArray<unsigned> visited_mask, frontier_map[2], candidates;
+    util::DeviceArray<unsigned> next_map, recv_map;     // partitioned runs only (PrepareExchange)
     bool candidates_valid = false;
     unsigned long long src_degree = 0;
     VertexId src = 0;
@@ -112,13 +112,21 @@ struct BFSProblem : ProblemBase<_VertexId, _SizeT> {
         return cudaSuccess;
     }
 
+    // state for a 1D-partitioned run: the dense discovery bitmap a push level fills and the
+    // buffer its segments are received into (parts x own-segment words)
+    cudaError_t PrepareExchange()
+    {
+        GR_TRY(next_map.Allocate(MaskWords()));
+        return recv_map.Allocate(MaskWords());
+    }
+
     DataSlice MakeDataSlice(VertexId level) const
     {
         DataSlice d;
         d.d_labels = labels.ptr; d.d_preds = preds.ptr; d.d_visited_mask = visited_mask.ptr;
         d.level = level; d.nodes = this->graph->nodes; d.local_nodes = this->graph->local_nodes;
         d.part = this->graph->part;
-        d.d_outbox = nullptr; d.d_outbox_len = nullptr; d.outbox_cap = 0;
+        d.d_next_map = next_map.size ? next_map.ptr : nullptr;
         return d;
     }
 

@@ -1,0 +1,100 @@
+// cc_enactor.cuh -- the host side of connected components.
+//
+// Counterpart of the reference's CCEnactor::EnactCC (gunrock/app/cc/cc_enactor.cuh:160-862):
+// there, a do/while of filter launches (HookInit, then rounds of PtrJump until a device flag
+// settles, UpdateMask, HookMax, PtrJumpMask/Unmask), each round ending in a blocking flag
+// copy -- O(10^2) launches and as many host round trips on an R-MAT graph.
+//
+// Here the whole computation is TWO operator launches and no host decision in between:
+//   1. advance (LB mode, identity frontier = every vertex, OUT_NONE) with HookFunctor:
+//      every CSR entry chases and links the roots of its end points;
+//   2. filter in apply-only mode (the reference's Kernel2) with PtrJumpFunctor over the
+//      identity frontier: flatten every vertex to its root and count the roots.
+// Labels: smallest vertex id of the component, as in the reference.
+//
+// Algorithmic HBM bytes: hook pass 2*sizeof(SizeT) per vertex + 4 (column id) + 8 (two
+// parent probes) per CSR entry; jump pass 12 per vertex.
+#pragma once
+#include "cc_functor.cuh"
+#include "../enactor_base.cuh"
+
+namespace gunrock {
+namespace app {
+namespace cc {
+
+template <typename Problem>
+class CCEnactor : public EnactorBase {
+  public:
+    typedef typename Problem::VertexId  VertexId;
+    typedef typename Problem::SizeT     SizeT;
+    typedef typename Problem::Value     Value;
+    typedef typename Problem::DataSlice DataSlice;
+    typedef HookFunctor<VertexId, SizeT, Value, Problem>    HookFn;
+    typedef PtrJumpFunctor<VertexId, SizeT, Value, Problem> JumpFn;
+    typedef oprtr::advance::KernelPolicy<Problem, 256, 4, 6, false, false> AdvancePolicy;
+    typedef oprtr::filter::KernelPolicy<Problem, 256, 4, 6, 0>             FilterPolicy;
+
+    oprtr::advance::LbScratch<SizeT> lb_scratch;
+    bool set_up = false;
+
+    cudaError_t Setup(Problem *problem, cudaStream_t s)
+    {
+        GR_TRY(SetupBase(problem->graph->device, s));
+        GR_TRY(lb_scratch.Allocate((size_t)problem->graph->local_nodes + 1, (size_t)problem->graph->edges + 1,
+                                   AdvancePolicy::SCAN_TILE, AdvancePolicy::TILE_EDGES, s));
+        set_up = true;
+        return cudaSuccess;
+    }
+
+    // reference signature: Enact<CCProblem>(problem, max_grid_size)
+    cudaError_t Enact(Problem *problem)
+    {
+        if (!set_up) return util::GRError(cudaErrorNotReady, "CCEnactor::Setup not called", __FILE__, __LINE__);
+        GR_TRY(ResetBase());
+        typename Problem::Base::Graph &g = *problem->graph;
+        const unsigned long long n = (unsigned long long)g.local_nodes;
+        if (n == 0) return cudaSuccess;
+        const DataSlice ds = problem->MakeDataSlice();
+        const unsigned osz = (unsigned)sizeof(SizeT);
+
+        // ---- 1. hook: one pass over the CSR entries ------------------------------------------------
+        oprtr::advance::Args<VertexId, SizeT> a;
+        a.g = g.View();
+        a.in_queue = nullptr; a.out_queue = nullptr;        // identity frontier, functor side effects only
+        a.in_len = n; a.d_in_len = nullptr; a.out_cap = 0;
+        a.slots = work_progress.d_slots.ptr;
+        a.queue_index = frontier_attribute.queue_index;
+        a.iteration = 0;
+        a.output = oprtr::advance::OUT_NONE;
+        GR_TRY((oprtr::advance::LaunchKernel<AdvancePolicy, Problem, HookFn>(
+            oprtr::advance::LB, dev, ds, a, &lb_scratch, (unsigned long long)g.edges, stream)));
+        enactor_stats.launches += 2;
+        frontier_attribute.queue_index++;
+
+        // ---- 2. pointer jumping: flatten + count roots ---------------------------------------------
+        oprtr::filter::Args<VertexId, Value> fa;
+        fa.in_queue = nullptr; fa.in_pred_queue = nullptr; fa.out_queue = nullptr;
+        fa.in_len = n; fa.d_in_len = nullptr; fa.out_cap = 0;
+        fa.slots = work_progress.d_slots.ptr;
+        fa.queue_index = frontier_attribute.queue_index;
+        fa.iteration = 1;
+        fa.compact = false;
+        GR_TRY((oprtr::filter::LaunchKernel<FilterPolicy, Problem, JumpFn>(dev.sm_count, ds, fa, stream)));
+        ++enactor_stats.launches;
+        frontier_attribute.queue_index++;
+
+        GR_TRY(cudaMemcpyAsync(&problem->num_components, problem->counter.ptr, sizeof(unsigned long long),
+                               cudaMemcpyDeviceToHost, stream));
+        oprtr::LevelCounters c;
+        GR_TRY(work_progress.Fetch(1, c, stream));           // the hook pass accumulated into slot 1
+        enactor_stats.edges_inspected = c.edges;
+        enactor_stats.total_queued = 2 * n;
+        enactor_stats.algo_bytes = n * (2ull * osz) + 12ull * c.edges + 12ull * n;
+        enactor_stats.iteration = 2;
+        return cudaSuccess;
+    }
+};
+
+}  // namespace cc
+}  // namespace app
+}  // namespace gunrock

@@ -25,7 +25,7 @@ namespace gunrock {
 namespace app {
 namespace sssp {
 
-__global__ void SumWeightsKernel(const unsigned *w, unsigned long long m, unsigned long long *out)
+static __global__ void SumWeightsKernel(const unsigned *w, unsigned long long m, unsigned long long *out)
 {
     __shared__ unsigned long long s_red[256 / 32 + 1];
     unsigned long long mine = 0;
@@ -38,7 +38,7 @@ __global__ void SumWeightsKernel(const unsigned *w, unsigned long long m, unsign
 }
 
 // dist/pred words -> separate arrays (Extract)
-__global__ void UnpackKernel(const unsigned long long *packed, unsigned long long n, unsigned *dist, int *preds)
+static __global__ void UnpackKernel(const unsigned long long *packed, unsigned long long n, unsigned *dist, int *preds)
 {
     const unsigned long long stride = (unsigned long long)gridDim.x * blockDim.x;
     for (unsigned long long i = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
@@ -48,7 +48,7 @@ __global__ void UnpackKernel(const unsigned long long *packed, unsigned long lon
     }
 }
 
-__global__ void InitPackedKernel(unsigned long long *packed, unsigned long long n)
+static __global__ void InitPackedKernel(unsigned long long *packed, unsigned long long n)
 {
     const unsigned long long stride = (unsigned long long)gridDim.x * blockDim.x;
     for (unsigned long long i = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride)

@@ -128,7 +128,7 @@ __device__ __forceinline__ bool KeepTuple(const unsigned long long *keys, unsign
     return row != col;                                                         // self loop
 }
 
-__global__ void __launch_bounds__(kKeepThreads)
+static __global__ void __launch_bounds__(kKeepThreads)
 CountKeptKernel(const unsigned long long *keys, unsigned long long n, int scale, graph::Partition part,
                 unsigned long long *tile_counts)
 {
@@ -144,7 +144,7 @@ CountKeptKernel(const unsigned long long *keys, unsigned long long n, int scale,
 }
 
 // writes col[j] and krow[j] (local row) for every kept tuple j
-__global__ void __launch_bounds__(kKeepThreads)
+static __global__ void __launch_bounds__(kKeepThreads)
 CompactKeptKernel(const unsigned long long *keys, unsigned long long n, int scale, graph::Partition part,
                   const unsigned long long *tile_offsets, int *col, int *krow)
 {
@@ -184,7 +184,7 @@ __global__ void RowOffsetsKernel(const int *krow, unsigned long long m, long lon
 
 // symmetric weights in [1, 64] (both directions of an edge hash the same pair;
 // the reference's loader gives both directions the file's value, market.cuh:173-181)
-__global__ void EdgeWeightsKernel(const int *krow, const int *col, unsigned long long m, graph::Partition part,
+static __global__ void EdgeWeightsKernel(const int *krow, const int *col, unsigned long long m, graph::Partition part,
                                   unsigned long long seed, unsigned *w)
 {
     const unsigned long long stride = (unsigned long long)gridDim.x * blockDim.x;

@@ -111,7 +111,7 @@ Kernel(const __grid_constant__ typename Problem::DataSlice ds,
                     if (Functor::CondFilter(id[r], &ds, (Value)pred[r], (SizeT)i))
                         Functor::ApplyFilter(id[r], &ds, (Value)pred[r], (SizeT)i);
                 }
-                if (args.out_queue && i < in_len) args.out_queue[i] = id[r];
+                if (args.out_queue && i < in_len && i < args.out_cap) args.out_queue[i] = id[r];
             }
             continue;
         }

@@ -23,7 +23,7 @@ constexpr int kSortRows    = 32;                                  // 32-key rows
 constexpr int kSortTile    = kSortWarps * 32 * kSortRows;         // 8192 keys per CTA
 constexpr int kRadix       = 256;
 
-__global__ void __launch_bounds__(kSortThreads)
+static __global__ void __launch_bounds__(kSortThreads)
 RadixHistKernel(const unsigned long long *keys, unsigned long long n, int shift,
                 unsigned long long *hist, unsigned long long tiles)
 {
@@ -40,7 +40,7 @@ RadixHistKernel(const unsigned long long *keys, unsigned long long n, int shift,
     hist[(unsigned long long)threadIdx.x * tiles + blockIdx.x] = s_h[threadIdx.x];
 }
 
-__global__ void __launch_bounds__(kSortThreads)
+static __global__ void __launch_bounds__(kSortThreads)
 RadixScatterKernel(const unsigned long long *in, unsigned long long *out, unsigned long long n, int shift,
                    const unsigned long long *scanned, unsigned long long tiles)
 {

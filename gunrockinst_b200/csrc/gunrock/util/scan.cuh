@@ -38,7 +38,7 @@ ScanReduceKernel(const T *in, unsigned long long n, unsigned long long *block_su
 }
 
 // single CTA, in place; also writes the grand total to sums[count]
-__global__ void __launch_bounds__(1024)
+static __global__ void __launch_bounds__(1024)
 ScanSpineKernel(unsigned long long *sums, unsigned long long count)
 {
     __shared__ unsigned long long s_warp[1024 / 32 + 1];

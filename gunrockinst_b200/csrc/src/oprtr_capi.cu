@@ -1,0 +1,170 @@
+// oprtr_capi.cu -- the two frontier operators, callable on their own through the C ABI
+// (grb_test_advance / grb_test_filter, include/gunrock_b200.h) so that parity tests can check
+// advance::LaunchKernel (reference: gunrock/oprtr/advance/kernel.cuh:101-129) and
+// filter::Kernel (reference: gunrock/oprtr/filter/kernel.cuh:738-757) against a plain
+// restatement of the operator contract, independent of any primitive.
+//
+// Probe functor (every side effect is an atomic add, so the result does not depend on the
+// schedule):
+//   CondEdge(s, d, e)   edge_hits[e] += 1; src_sum[d] += s; return (s + d) % 3 != 0
+//   ApplyEdge(s, d, e)  dst_hits[d] += 1
+//   CondFilter(v)       return v % 2 == 0          ApplyFilter(v)  dst_hits[v] += 1
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include "../../../include/gunrock_b200.h"
+#include "graph_handle.cuh"
+#include "../gunrock/app/enactor_base.cuh"
+#include "../gunrock/app/problem_base.cuh"
+
+namespace {
+
+template <typename _SizeT>
+struct ProbeProblem {
+    typedef int    VertexId;
+    typedef _SizeT SizeT;
+    typedef int    Value;
+    static const bool MARK_PREDECESSORS  = true;
+    static const bool ENABLE_IDEMPOTENCE = false;
+    struct DataSlice {
+        int       *edge_hits;
+        long long *src_sum;
+        int       *dst_hits;
+        long long  nodes, local_nodes;
+        gunrock::graph::Partition part;
+    };
+};
+
+template <typename Problem>
+struct ProbeFunctor {
+    typedef typename Problem::DataSlice DataSlice;
+    typedef typename Problem::SizeT SizeT;
+    static __device__ __forceinline__ bool CondEdge(int s, int d, const DataSlice *p, SizeT e = 0, SizeT e_in = 0)
+    {
+        atomicAdd(p->edge_hits + e, 1);
+        atomicAdd((unsigned long long *)p->src_sum + d, (unsigned long long)(long long)s);
+        return ((s + d) % 3) != 0;
+    }
+    static __device__ __forceinline__ void ApplyEdge(int s, int d, const DataSlice *p, SizeT e = 0, SizeT e_in = 0)
+    {
+        atomicAdd(p->dst_hits + d, 1);
+    }
+    static __device__ __forceinline__ bool CondFilter(int v, const DataSlice *p, int val = 0, SizeT nid = 0)
+    {
+        return (v % 2) == 0;
+    }
+    static __device__ __forceinline__ void ApplyFilter(int v, const DataSlice *p, int val = 0, SizeT nid = 0)
+    {
+        atomicAdd(p->dst_hits + v, 1);
+    }
+};
+
+template <typename SizeT>
+cudaError_t RunAdvance(gunrock::graph::DeviceCsr<int, SizeT> *g, cudaStream_t s, int mode, int output,
+                       const int32_t *in_queue, int64_t in_len, int32_t *out_queue, int64_t out_cap, int64_t *out_len,
+                       int32_t *edge_hits, int64_t *src_sum, int32_t *dst_hits, uint64_t *edges_inspected)
+{
+    using namespace gunrock;
+    typedef ProbeProblem<SizeT> Problem;
+    typedef ProbeFunctor<Problem> Functor;
+    typedef oprtr::advance::KernelPolicy<Problem, 256, 4, 6, false, false> Policy;
+    const size_t n = (size_t)g->nodes, m = (size_t)g->edges;
+    util::DeviceArray<int> d_in, d_out, d_eh, d_dh;
+    util::DeviceArray<long long> d_ss;
+    oprtr::WorkProgress wp;
+    oprtr::advance::LbScratch<SizeT> scratch;
+    oprtr::advance::DeviceInfo dev;
+    GR_TRY(dev.Query(g->device));
+    GR_TRY(wp.Setup(s));
+    if (in_queue) GR_TRY(d_in.FromHost(in_queue, (size_t)in_len, s));
+    GR_TRY(d_out.Allocate((size_t)out_cap + 1));
+    GR_TRY(cudaMemsetAsync(d_out.ptr, 0x7f, sizeof(int) * ((size_t)out_cap + 1), s));
+    GR_TRY(d_eh.Allocate(m + 1)); GR_TRY(d_eh.Zero(s));
+    GR_TRY(d_dh.Allocate(n + 1)); GR_TRY(d_dh.Zero(s));
+    GR_TRY(d_ss.Allocate(n + 1)); GR_TRY(d_ss.Zero(s));
+    const size_t items = (size_t)in_len + 1;
+    GR_TRY(scratch.Allocate(items, m + 1, Policy::SCAN_TILE, Policy::TILE_EDGES, s));
+
+    typename Problem::DataSlice ds;
+    ds.edge_hits = d_eh.ptr; ds.src_sum = d_ss.ptr; ds.dst_hits = d_dh.ptr;
+    ds.nodes = g->nodes; ds.local_nodes = g->local_nodes; ds.part = g->part;
+    oprtr::advance::Args<int, SizeT> a;
+    a.g = g->View();
+    a.in_queue = in_queue ? d_in.ptr : nullptr;
+    a.out_queue = output ? d_out.ptr : nullptr;
+    a.in_len = (unsigned long long)in_len; a.d_in_len = nullptr;
+    a.out_cap = (unsigned long long)out_cap;
+    a.slots = wp.d_slots.ptr; a.queue_index = 0; a.iteration = 7;
+    a.output = output == 0 ? oprtr::advance::OUT_NONE : (output == 1 ? oprtr::advance::OUT_COMPACT : oprtr::advance::OUT_TOMBSTONE);
+    if (mode == 0 && a.output == oprtr::advance::OUT_TOMBSTONE)
+        return util::GRError(cudaErrorInvalidValue, "tombstone output exists in LB mode only", __FILE__, __LINE__);
+    GR_TRY((oprtr::advance::LaunchKernel<Policy, Problem, Functor>(
+        mode == 0 ? oprtr::advance::TWC_FORWARD : oprtr::advance::LB, dev, ds, a, &scratch, (unsigned long long)m, s)));
+    oprtr::LevelCounters c;
+    GR_TRY(wp.Fetch(1, c, s));
+    if (out_len) *out_len = c.overflow ? -1 : (int64_t)c.out_len;
+    if (edges_inspected) *edges_inspected = c.edges;
+    if (out_queue && output) {
+        size_t k = (size_t)(c.out_len < (unsigned long long)out_cap ? c.out_len : (unsigned long long)out_cap);
+        GR_TRY(d_out.ToHost(out_queue, k, s));
+    }
+    if (edge_hits) GR_TRY(d_eh.ToHost(edge_hits, m, s));
+    if (dst_hits)  GR_TRY(d_dh.ToHost(dst_hits, n, s));
+    if (src_sum)   GR_TRY(d_ss.ToHost((long long *)src_sum, n, s));
+    return cudaStreamSynchronize(s);
+}
+
+}  // namespace
+
+extern "C" int grb_test_advance(grb_graph_t g, int mode, int output, const int32_t *in_queue, int64_t in_len,
+                                int32_t *out_queue, int64_t out_cap, int64_t *out_len,
+                                int32_t *edge_hits, int64_t *src_sum, int32_t *dst_hits, uint64_t *edges_inspected)
+{
+    if (!g || in_len < 0 || out_cap < 0) return (int)cudaErrorInvalidValue;
+    GRB_TRY(cudaSetDevice(g->device()));
+    return (int)(g->g32 ? RunAdvance<int>(g->g32, g->stream, mode, output, in_queue, in_len, out_queue, out_cap, out_len,
+                                          edge_hits, src_sum, dst_hits, edges_inspected)
+                        : RunAdvance<long long>(g->g64, g->stream, mode, output, in_queue, in_len, out_queue, out_cap,
+                                                out_len, edge_hits, src_sum, dst_hits, edges_inspected));
+}
+
+extern "C" int grb_test_filter(int device, int64_t nodes, int compact, const int32_t *in_queue, int64_t in_len,
+                               int32_t *out_queue, int64_t out_cap, int64_t *out_len, int32_t *dst_hits)
+{
+    using namespace gunrock;
+    if (in_len < 0 || out_cap < 0 || nodes < 0) return (int)cudaErrorInvalidValue;
+    int rc = grb_select_device(device);
+    if (rc) return rc;
+    typedef ProbeProblem<int> Problem;
+    typedef ProbeFunctor<Problem> Functor;
+    typedef oprtr::filter::KernelPolicy<Problem, 256, 4, 6, 0> Policy;
+    cudaStream_t s = 0;
+    util::DeviceArray<int> d_in, d_out, d_dh;
+    oprtr::WorkProgress wp;
+    oprtr::advance::DeviceInfo dev;
+    GRB_TRY(dev.Query(device));
+    GRB_TRY(wp.Setup(s));
+    if (in_queue) GRB_TRY(d_in.FromHost(in_queue, (size_t)in_len, s));
+    GRB_TRY(d_out.Allocate((size_t)out_cap + 1));
+    GRB_TRY(d_dh.Allocate((size_t)nodes + 1)); GRB_TRY(d_dh.Zero(s));
+    Problem::DataSlice ds;
+    ds.edge_hits = nullptr; ds.src_sum = nullptr; ds.dst_hits = d_dh.ptr;
+    ds.nodes = nodes; ds.local_nodes = nodes; ds.part = graph::Partition();
+    oprtr::filter::Args<int, int> fa;
+    fa.in_queue = in_queue ? d_in.ptr : nullptr; fa.in_pred_queue = nullptr;
+    fa.out_queue = out_queue ? d_out.ptr : nullptr;
+    fa.in_len = (unsigned long long)in_len; fa.d_in_len = nullptr; fa.out_cap = (unsigned long long)out_cap;
+    fa.slots = wp.d_slots.ptr; fa.queue_index = 0; fa.iteration = 3; fa.compact = compact != 0;
+    GRB_TRY((oprtr::filter::LaunchKernel<Policy, Problem, Functor>(dev.sm_count, ds, fa, s)));
+    oprtr::LevelCounters c;
+    GRB_TRY(wp.Fetch(1, c, s));
+    const unsigned long long produced = compact ? c.out_len : (unsigned long long)in_len;
+    if (out_len) *out_len = c.overflow ? -1 : (int64_t)produced;
+    if (out_queue) {
+        size_t k = (size_t)(produced < (unsigned long long)out_cap ? produced : (unsigned long long)out_cap);
+        GRB_TRY(d_out.ToHost(out_queue, k, s));
+    }
+    if (dst_hits) GRB_TRY(d_dh.ToHost(dst_hits, (size_t)nodes, s));
+    GRB_TRY(cudaStreamSynchronize(s));
+    return 0;
+}

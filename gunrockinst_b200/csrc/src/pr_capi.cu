@@ -1,0 +1,107 @@
+// pr_capi.cu -- C entry points for PageRank: the reference's gunrock_pr_func
+// (gunrock/gunrock.h:133-140; implementation replaced: gunrock/app/pr/pr_app.cu:120-339)
+// and the resident-graph grb_pagerank of include/gunrock_b200.h.
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include "../../../include/gunrock/gunrock.h"
+#include "../../../include/gunrock_b200.h"
+#include "graph_handle.cuh"
+#include "source_select.h"
+#include "../gunrock/app/pr/pr_enactor.cuh"
+
+// counterpart of run_page_rank<VertexId, Value, SizeT> (pr_app.cu:120-195)
+template <typename SizeT>
+static cudaError_t RunPr(gunrock::graph::DeviceCsr<int, SizeT> *g, cudaStream_t stream, int src, double delta,
+                         double threshold, int max_iter, double *ranks64_host, int *sorted_ids_host,
+                         float *sorted_ranks_host, size_t top, grb_stats *stats)
+{
+    typedef gunrock::app::pr::PRProblem<int, SizeT, double> Problem;
+    typedef gunrock::app::pr::PREnactor<Problem> Enactor;
+    if (g->part.log_parts != 0)
+        return gunrock::util::GRError(cudaErrorNotSupported, "PageRank runs on unpartitioned graphs only", __FILE__, __LINE__);
+    Problem problem;
+    Enactor enactor;
+    cudaEvent_t e0, e1, e2;
+    GR_TRY(cudaEventCreate(&e0)); GR_TRY(cudaEventCreate(&e1)); GR_TRY(cudaEventCreate(&e2));
+    cudaError_t err = cudaSuccess;
+    do {
+        if ((err = problem.Init(g, stream)) != cudaSuccess) break;
+        if ((err = enactor.Setup(&problem, stream)) != cudaSuccess) break;
+        if ((err = cudaEventRecord(e0, stream)) != cudaSuccess) break;
+        if ((err = problem.Reset(src, delta, threshold)) != cudaSuccess) break;
+        if ((err = cudaEventRecord(e1, stream)) != cudaSuccess) break;
+        if ((err = enactor.Enact(&problem, max_iter)) != cudaSuccess) break;
+        if ((err = cudaEventRecord(e2, stream)) != cudaSuccess) break;
+        if ((err = cudaEventSynchronize(e2)) != cudaSuccess) break;
+        if ((err = problem.Extract(ranks64_host, sorted_ids_host, sorted_ranks_host, top)) != cudaSuccess) break;
+        if (stats) {
+            float r = 0, t = 0;
+            cudaEventElapsedTime(&r, e0, e1); cudaEventElapsedTime(&t, e1, e2);
+            memset(stats, 0, sizeof(*stats));
+            stats->reset_ms = r; stats->elapsed_ms = t;
+            stats->iterations = enactor.enactor_stats.iteration;
+            stats->edges_inspected = enactor.enactor_stats.edges_inspected;
+            stats->edges_visited = (int64_t)enactor.enactor_stats.edges_inspected;
+            stats->total_queued = enactor.enactor_stats.total_queued;
+            stats->nodes_visited = (int64_t)enactor.valid_nodes;
+            stats->algo_bytes = enactor.enactor_stats.algo_bytes;
+            stats->push_levels = (int32_t)enactor.enactor_stats.iteration;
+            stats->pull_levels = enactor.prune_sweeps;
+            stats->gpu_launches = enactor.enactor_stats.launches;
+            stats->reserved = (int32_t)(enactor.sweep_ms * 1000.0f);      // microseconds of the power iteration alone
+        }
+    } while (0);
+    cudaEventDestroy(e0); cudaEventDestroy(e1); cudaEventDestroy(e2);
+    return err;
+}
+
+static int PrDispatch(grb_graph_t g, int32_t src, double delta, double threshold, int32_t max_iter,
+                      double *ranks64_host, int32_t *sorted_ids_host, float *sorted_ranks_host, size_t top,
+                      grb_stats *stats)
+{
+    if (!g) return (int)cudaErrorInvalidValue;
+    GRB_TRY(cudaSetDevice(g->device()));
+    return (int)(g->g32 ? RunPr<int>(g->g32, g->stream, src, delta, threshold, max_iter, ranks64_host,
+                                     sorted_ids_host, sorted_ranks_host, top, stats)
+                        : RunPr<long long>(g->g64, g->stream, src, delta, threshold, max_iter, ranks64_host,
+                                           sorted_ids_host, sorted_ranks_host, top, stats));
+}
+
+extern "C" int grb_pagerank(grb_graph_t g, int32_t src, double delta, double threshold, int32_t max_iter,
+                            double *ranks64_host, int32_t *sorted_ids_host, float *sorted_ranks_host,
+                            grb_stats *stats)
+{
+    return PrDispatch(g, src, delta, threshold, max_iter, ranks64_host, sorted_ids_host, sorted_ranks_host, 0, stats);
+}
+
+extern "C" void gunrock_pr_func(struct GunrockGraph *graph_out, void *node_ids, void *page_rank,
+                                const struct GunrockGraph *graph_in, struct GunrockConfig configs,
+                                struct GunrockDataType data_type)
+{
+    // only <int, float, int> exists in the reference (pr_app.cu:207-300)
+    if (data_type.VTXID_TYPE != VTXID_INT || data_type.SIZET_TYPE != SIZET_INT || data_type.VALUE_TYPE != VALUE_FLOAT) {
+        printf("Not Yet Support This DataType Combination.\n");
+        return;
+    }
+    (void)graph_out;        // the reference leaves graph_out untouched for PageRank
+    const long long n = (long long)graph_in->num_nodes, m = (long long)graph_in->num_edges;
+    const int *h_off = (const int *)graph_in->row_offsets;
+    // pr_app.cu:232-258: any other mode value means "global" PageRank (src = -1)
+    const int src = grb_pick_source(configs.src_mode, configs.src_node, n, h_off, -1);
+    grb_graph_t g = nullptr;
+    if (grb_graph_from_host(configs.device, n, m, h_off, 4, (const int32_t *)graph_in->col_indices, nullptr, 0, 4, &g))
+        return;
+    // The reference writes all n pairs (pr_problem.cuh:162-176) although test_pr.c:47-48 sizes the
+    // buffers by top_nodes; writing min(n, top_nodes) is output compatible and cannot overrun.
+    const size_t top = configs.top_nodes > 0 ? (size_t)configs.top_nodes : 0;
+    grb_stats st;
+    memset(&st, 0, sizeof(st));
+    const int rc = PrDispatch(g, src, (double)configs.delta, (double)configs.error, configs.max_iter, nullptr,
+                              (int32_t *)node_ids, (float *)page_rank, top, &st);
+    if (rc == 0)
+        printf("[PR] finished. \n elapsed: %.4f ms\n src: %d\n iterations: %lld\n", st.elapsed_ms, src,
+               (long long)st.iterations);
+    grb_graph_destroy(g);
+    cudaDeviceSynchronize();
+}

@@ -1,0 +1,295 @@
+"""1D vertex-partitioned, direction-optimising BFS: one process per device, torch.distributed
+for the exchange (NCCL over NVLink on B200s; gloo in the CPU tests of the host logic).
+
+The reference declares the striping rule (gunrock/app/problem_base.cuh:186-210) and leaves
+the multi-GPU path as a TODO (:336-338); this module is the host loop of that path.  The
+device side of every step is libgunrock.so (grb_mgbfs_*, include/gunrock_b200.h,
+csrc/gunrock/app/bfs/mgbfs_enactor.cuh) behind the small `engine` interface below; the test
+suite drives the same loop with a numpy stand-in engine over gloo.
+
+Per level (all bitmaps are global, 1 bit / vertex, owner-major so a device's bits are one
+contiguous segment):
+
+  push   engine.push -> all_to_all_single(next map -> recv map) -> engine.absorb
+  pull   all_gather_into_tensor(frontier map, in place) -> engine.merge_visited -> engine.pull
+  both   all_gather of every device's 64-byte counter block -> one host read: global frontier
+         length, its degree sum (Beamer's direction rule, as in bfs_enactor.cuh), edges inspected
+
+Payloads: push n/8 bytes per device per level (each device sends (P-1)/P of its next map),
+pull n/8 bytes gathered per device, counters 64 B.  Exchange and compute are timed per level
+with events on the stream the steps run on.
+"""
+import ctypes as C
+import time
+
+import numpy as np
+import torch
+import torch.distributed as dist
+
+from . import _capi
+
+CTR_WORDS = 8           # uint64 words of oprtr::LevelCounters
+CTR_FRONTIER, CTR_DEGREE, CTR_EDGES, CTR_CANDS, CTR_OVERFLOW = 0, 1, 2, 4, 6
+
+
+class _RawCuda:
+    """wraps a raw device pointer so torch can view it (no copy, no ownership)"""
+
+    def __init__(self, ptr, count, typestr):
+        self.__cuda_array_interface__ = {"shape": (int(count),), "typestr": typestr,
+                                         "data": (int(ptr), False), "version": 2}
+
+
+class DeviceEngine:
+    """The per-level device steps of one rank, over the C ABI (no CPU path)."""
+
+    def __init__(self, graph):
+        self.graph = graph
+        L = _capi.lib()
+        self._h = C.c_void_p()
+        _capi.check(L.grb_mgbfs_create(graph._h, C.byref(self._h)), "grb_mgbfs_create")
+        info = graph.info
+        self.parts = 1 << info.log_parts
+        self.rank = int(info.rank)
+        self.nodes = int(info.nodes)
+        self.local_nodes = int(info.local_nodes)
+        self.local_edges = int(info.edges)
+        self.seg_words = self.local_nodes // 32
+        self.device = torch.device("cuda", int(info.device))
+        s = C.c_void_p()
+        _capi.check(L.grb_mgbfs_stream(self._h, C.byref(s)), "grb_mgbfs_stream")
+        self.stream = torch.cuda.ExternalStream(s.value or 0, device=self.device)
+        words = self.seg_words * self.parts
+        self.maps = [self._tensor(1, words, "<i4"), self._tensor(2, words, "<i4")]
+        self.visited = self._tensor(0, words, "<i4")
+        self.next = self._tensor(3, words, "<i4")
+        self.recv = self._tensor(4, words, "<i4")
+        self.counters = self._tensor(6, CTR_WORDS, "<i8")
+
+    def _tensor(self, which, count, typestr):
+        p, b = C.c_void_p(), C.c_uint64()
+        _capi.check(_capi.lib().grb_mgbfs_buffer(self._h, which, C.byref(p), C.byref(b)), "grb_mgbfs_buffer")
+        assert b.value >= count * int(typestr[2:]), (which, b.value, count)
+        return torch.as_tensor(_RawCuda(p.value, count, typestr), device=self.device)
+
+    def reset(self, src):
+        d = C.c_uint64()
+        _capi.check(_capi.lib().grb_mgbfs_reset(self._h, int(src), C.byref(d)), "grb_mgbfs_reset")
+        return int(d.value)
+
+    def push(self, level, queue_len, edges_hint):
+        _capi.check(_capi.lib().grb_mgbfs_push(self._h, level, int(queue_len), int(edges_hint)), "grb_mgbfs_push")
+
+    def absorb(self, level, cur_out):
+        _capi.check(_capi.lib().grb_mgbfs_absorb(self._h, level, cur_out), "grb_mgbfs_absorb")
+
+    def pull(self, level, cur):
+        _capi.check(_capi.lib().grb_mgbfs_pull(self._h, level, cur), "grb_mgbfs_pull")
+
+    def merge_visited(self, cur):
+        _capi.check(_capi.lib().grb_mgbfs_merge_visited(self._h, cur), "grb_mgbfs_merge_visited")
+
+    def queue_to_map(self, cur, queue_len):
+        _capi.check(_capi.lib().grb_mgbfs_queue_to_map(self._h, cur, int(queue_len)), "grb_mgbfs_queue_to_map")
+
+    def map_to_queue(self, cur):
+        _capi.check(_capi.lib().grb_mgbfs_map_to_queue(self._h, cur), "grb_mgbfs_map_to_queue")
+
+    def launches(self):
+        lv = _capi.MgLevel()
+        _capi.check(_capi.lib().grb_mgbfs_counters(self._h, C.byref(lv)), "grb_mgbfs_counters")
+        return int(lv.gpu_launches)
+
+    def labels(self):
+        out = np.empty(self.local_nodes, dtype=np.int32)
+        _capi.check(_capi.lib().grb_mgbfs_labels(self._h, out.ctypes.data_as(C.c_void_p)), "grb_mgbfs_labels")
+        return out
+
+    # timing hooks (CUDA events on the stream every step and collective is ordered on)
+    def stream_context(self):
+        return torch.cuda.stream(self.stream)
+
+    def mark(self):
+        e = torch.cuda.Event(enable_timing=True)
+        e.record(self.stream)
+        return e
+
+    @staticmethod
+    def elapsed_ms(a, b):
+        return a.elapsed_time(b)
+
+    def synchronize(self):
+        self.stream.synchronize()
+
+    def close(self):
+        if self._h:
+            _capi.lib().grb_mgbfs_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+def owner_of(v, log_parts):
+    """the partition rule of csrc/gunrock/graph/csr.cuh (Partition::Owner), on the host"""
+    if log_parts == 0:
+        return 0
+    local = (int(v) >> log_parts) & 0xFFFFFFFF
+    mix = ((local * 0x9E3779B1) & 0xFFFFFFFF) >> (32 - log_parts)
+    return (int(v) & ((1 << log_parts) - 1)) ^ mix
+
+
+def global_ids(local_nodes, log_parts, rank):
+    """global vertex id of every local row of `rank` (Partition::Global), vectorised"""
+    local = np.arange(local_nodes, dtype=np.uint64)
+    if log_parts == 0:
+        return local.astype(np.int64)
+    mix = ((local * np.uint64(0x9E3779B1)) & np.uint64(0xFFFFFFFF)) >> np.uint64(32 - log_parts)
+    return ((local << np.uint64(log_parts)) | (np.uint64(rank) ^ mix)).astype(np.int64)
+
+
+class PartitionedBfs:
+    """Host loop of the partitioned DOBFS.  `engine` supplies the device steps and the tensors
+    the collectives move; `group` is the torch.distributed process group (None = default)."""
+
+    def __init__(self, engine, group=None, direction_optimized=True, alpha=14.0, beta=24.0, record_levels=True):
+        self.e = engine
+        self.group = group
+        self.dopt = direction_optimized
+        self.alpha, self.beta = alpha, beta
+        self.record_levels = record_levels
+        self.world = dist.get_world_size(group) if dist.is_initialized() else 1
+        if self.world != engine.parts:
+            raise ValueError("graph is partitioned %d ways but the group has %d ranks" % (engine.parts, self.world))
+        self.all_counters = torch.zeros(self.world * CTR_WORDS, dtype=torch.int64, device=engine.counters.device)
+        self.setup = torch.zeros(2, dtype=torch.int64, device=engine.counters.device)
+
+    # ---- collectives ------------------------------------------------------------------------
+    def _exchange_next(self):
+        e = self.e
+        if self.world == 1:
+            e.recv.copy_(e.next)
+        else:
+            dist.all_to_all_single(e.recv, e.next, group=self.group)
+        return e.next.numel() * 4 * (self.world - 1) // self.world
+
+    def _gather_map(self, cur):
+        e = self.e
+        if self.world > 1:
+            m = e.maps[cur]
+            own = m[e.rank * e.seg_words:(e.rank + 1) * e.seg_words]
+            dist.all_gather_into_tensor(m, own, group=self.group)
+        return e.seg_words * 4 * (self.world - 1)
+
+    def _gather_counters(self):
+        e = self.e
+        if self.world == 1:
+            self.all_counters.copy_(e.counters)
+        else:
+            dist.all_gather_into_tensor(self.all_counters, e.counters, group=self.group)
+        return self.all_counters.cpu().numpy().reshape(self.world, CTR_WORDS)     # the one host read of a level
+
+    # ---- the search -------------------------------------------------------------------------------
+    def run(self, src):
+        """-> stats dict; labels stay on the devices (engine.labels())."""
+        e = self.e
+        with e.stream_context():
+            src_degree = e.reset(src)
+            self.setup[0] = src_degree
+            self.setup[1] = e.local_edges
+            if self.world > 1:
+                dist.all_reduce(self.setup, group=self.group)
+            src_degree, m_global = (int(x) for x in self.setup.cpu())
+            n = e.nodes
+            local_q = 1 if (0 <= src < n and owner_of(src, e.parts.bit_length() - 1) == e.rank) else 0
+            local_hint = src_degree if local_q else 0
+            frontier, frontier_edges = (1 if 0 <= src < n else 0), src_degree
+            unexplored = m_global - frontier_edges
+            edges_visited = frontier_edges
+            prev_len = 0
+            pull = False
+            cur, map_valid, gathered, queue_valid = 0, False, False, True
+            level = 0
+            levels, marks = [], []
+            exch_bytes = inspected = 0
+            t_wall = time.perf_counter()
+            ev_start = e.mark()
+            while frontier > 0:
+                if self.dopt:
+                    if not pull and frontier_edges > unexplored / self.alpha:
+                        pull = True
+                    elif pull and frontier < prev_len and frontier < n / self.beta:
+                        pull = False
+                m0 = e.mark() if self.record_levels else None
+                lvl_bytes = 0
+                if pull:
+                    if not map_valid:
+                        e.queue_to_map(cur, local_q)
+                        map_valid = True
+                    m1 = e.mark() if self.record_levels else None
+                    if not gathered:
+                        lvl_bytes += self._gather_map(cur)
+                    m2 = e.mark() if self.record_levels else None
+                    e.merge_visited(cur)
+                    e.pull(level, cur)
+                    cur ^= 1
+                    queue_valid = False
+                else:
+                    if not queue_valid:
+                        e.map_to_queue(cur)
+                        queue_valid = True
+                    e.push(level, local_q, local_hint)
+                    m1 = e.mark() if self.record_levels else None
+                    lvl_bytes += self._exchange_next()
+                    m2 = e.mark() if self.record_levels else None
+                    e.absorb(level, cur ^ 1)
+                    cur ^= 1
+                map_valid, gathered = True, False
+                m3 = e.mark() if self.record_levels else None
+                c = self._gather_counters()
+                if int(c[:, CTR_OVERFLOW].sum()):
+                    raise _capi.GunrockError("frontier queue overflow on a partitioned level")
+                prev_len = frontier
+                frontier = int(c[:, CTR_FRONTIER].sum())
+                frontier_edges = int(c[:, CTR_DEGREE].sum())
+                local_q = int(c[e.rank, CTR_FRONTIER])
+                local_hint = int(c[e.rank, CTR_DEGREE])
+                lvl_inspected = int(c[:, CTR_EDGES].sum())
+                inspected += lvl_inspected
+                unexplored = max(unexplored - frontier_edges, 0)
+                edges_visited += frontier_edges
+                exch_bytes += lvl_bytes
+                if self.record_levels:
+                    marks.append((m0, m1, m2, m3))
+                    levels.append(dict(level=level, kind="pull" if pull else "push", frontier=prev_len,
+                                       discovered=frontier, edges=lvl_inspected, exchange_bytes=lvl_bytes,
+                                       local_max_edges=int(c[:, CTR_EDGES].max())))
+                level += 1
+            ev_end = e.mark()
+            e.synchronize()
+            wall_ms = (time.perf_counter() - t_wall) * 1e3
+        for rec, (m0, m1, m2, m3) in zip(levels, marks):
+            rec["exchange_ms"] = e.elapsed_ms(m1, m2)
+            rec["compute_ms"] = e.elapsed_ms(m0, m1) + e.elapsed_ms(m2, m3)
+        return dict(elapsed_ms=e.elapsed_ms(ev_start, ev_end), wall_ms=wall_ms, iterations=level,
+                    edges_visited=edges_visited, edges_inspected=inspected, exchange_bytes=exch_bytes,
+                    levels=levels, m_global=m_global)
+
+
+def gather_labels(engine, group=None):
+    """all ranks' labels -> one global int32[n] array in vertex order (on every rank); for tests"""
+    world = dist.get_world_size(group) if dist.is_initialized() else 1
+    mine = engine.labels()
+    log_parts = engine.parts.bit_length() - 1
+    out = np.empty(engine.nodes, dtype=np.int32)
+    if world == 1:
+        out[global_ids(engine.local_nodes, log_parts, 0)] = mine
+        return out
+    parts = [None] * world
+    dist.all_gather_object(parts, mine, group=group)
+    for r, lab in enumerate(parts):
+        out[global_ids(engine.local_nodes, log_parts, r)] = lab
+    return out

@@ -156,37 +156,53 @@ int grb_test_filter(int device, int64_t nodes, int compact,
 
 /* ---- 1D-partitioned BFS, one device per process -----------------------------------
  * No reference counterpart (the reference's multi-GPU path is a TODO,
- * gunrock/app/problem_base.cuh:336-338); the striping rule is the reference's.
- * The harness owns the communicator (torch.distributed / NCCL) and moves the
- * buffers exposed here between levels. */
+ * gunrock/app/problem_base.cuh:336-338); the striping rule is the reference's
+ * (:186-210).  The harness owns the communicator (torch.distributed / NCCL) and runs
+ * its collectives on the context's stream between the steps below; every step is
+ * asynchronous on that stream.
+ *
+ * All bitmaps are GLOBAL, one bit per vertex, laid out owner-major: device r's bits
+ * are words [r * seg_words, (r + 1) * seg_words), seg_words = local_nodes / 32.
+ *   push level : grb_mgbfs_push -> all-to-all(next map -> recv map, seg_words words per
+ *                peer) -> grb_mgbfs_absorb
+ *   pull level : all-gather(frontier map `cur`, own segment in place) -> grb_mgbfs_pull
+ * After either, the 64-byte counter block (buffer 6) holds, as 8 uint64:
+ *   [0] vertices this device added to the next frontier   [1] their out-degree sum
+ *   [2] neighbour entries inspected  [4] pull: unvisited candidates  [6] overflow flag  */
 typedef struct grb_mgbfs_s *grb_mgbfs_t;
 typedef struct {
     uint64_t frontier_local;     /* owned vertices in the next frontier            */
     uint64_t frontier_edges;     /* their out-degree sum                           */
     uint64_t edges_inspected;
     uint64_t candidates;
-    uint64_t outbox_len[16];     /* push-sparse: ids queued for each peer          */
+    uint64_t overflow;
+    uint64_t gpu_launches;       /* kernels launched by this context so far        */
 } grb_mg_level;
 
-int  grb_mgbfs_create(grb_graph_t g, uint64_t outbox_cap, grb_mgbfs_t *out);
+int  grb_mgbfs_create(grb_graph_t g, grb_mgbfs_t *out);
+/* labels <- -1, bitmaps <- 0, source marked visited everywhere, queued on its owner;
+ * src_degree is the source's out-degree on the owner, 0 elsewhere (synchronises) */
 int  grb_mgbfs_reset(grb_mgbfs_t ctx, int32_t src, uint64_t *src_degree);
 /* device pointers the harness hands to the collectives:
- * which: 0 visited bitmap, 1 frontier map A, 2 frontier map B, 3 outbox ids,
- *        4 inbox ids, 5 labels (local), 6 next bitmap (push-dense scratch) */
+ * which: 0 visited map, 1 frontier map 0, 2 frontier map 1, 3 next map, 4 recv map,
+ *        5 labels (int32, local rows), 6 counter block */
 int  grb_mgbfs_buffer(grb_mgbfs_t ctx, int which, void **dev_ptr, uint64_t *bytes);
-/* pull level: reads frontier map `cur`, writes OWN segment of map cur^1 */
-int  grb_mgbfs_pull(grb_mgbfs_t ctx, int32_t level, int cur, grb_mg_level *out);
-/* push level over the local queue; remote discoveries are set in the dense
- * `next` bitmap (dense != 0) or appended to the per-peer outboxes (dense == 0) */
-int  grb_mgbfs_push(grb_mgbfs_t ctx, int32_t level, int dense, grb_mg_level *out);
-/* after the exchange: absorb ids received in the inbox (sparse) ...            */
-int  grb_mgbfs_absorb_inbox(grb_mgbfs_t ctx, int32_t level, uint64_t inbox_len, grb_mg_level *out);
-/* ... or OR together `parts` received segments of the next bitmap (dense)      */
-int  grb_mgbfs_absorb_dense(grb_mgbfs_t ctx, int32_t level, grb_mg_level *out);
-/* local queue <-> own segment of frontier map `cur`; visited |= map (all words) */
-int  grb_mgbfs_queue_to_map(grb_mgbfs_t ctx, int cur);
-int  grb_mgbfs_map_to_queue(grb_mgbfs_t ctx, int cur, grb_mg_level *out);
+/* push level, part 1: clears the counters and the next map, expands the local queue of
+ * `queue_len` vertices; every unvisited neighbour sets its bit in the next map */
+int  grb_mgbfs_push(grb_mgbfs_t ctx, int32_t level, uint64_t queue_len, uint64_t edges_hint);
+/* push level, part 2 (after the all-to-all): OR of the received segments & ~visited ->
+ * labels level+1, own segment of frontier map `cur_out`, new local queue, counters */
+int  grb_mgbfs_absorb(grb_mgbfs_t ctx, int32_t level, int cur_out);
+/* pull level: clears the counters, reads frontier map `cur` (all segments), writes the
+ * OWN segment of map cur^1, labels level+1, updates the own visited segment */
+int  grb_mgbfs_pull(grb_mgbfs_t ctx, int32_t level, int cur);
+/* visited |= frontier map `cur`, all segments (refreshes the remote cull hints) */
 int  grb_mgbfs_merge_visited(grb_mgbfs_t ctx, int cur);
+/* local queue -> own segment of map `cur` (map cleared first); and back */
+int  grb_mgbfs_queue_to_map(grb_mgbfs_t ctx, int cur, uint64_t queue_len);
+int  grb_mgbfs_map_to_queue(grb_mgbfs_t ctx, int cur);
+/* host copy of this device's counter block (synchronises the stream) */
+int  grb_mgbfs_counters(grb_mgbfs_t ctx, grb_mg_level *out);
 int  grb_mgbfs_sync(grb_mgbfs_t ctx);
 int  grb_mgbfs_stream(grb_mgbfs_t ctx, void **cuda_stream);
 int  grb_mgbfs_labels(grb_mgbfs_t ctx, int32_t *labels_host);

@@ -1,0 +1,115 @@
+"""GPU: the advance and filter operators on their own (grb_test_advance / grb_test_filter) against
+a plain numpy restatement of the operator contract: which
+(source, destination, CSR entry, input position) tuples the functor sees, what is emitted in
+which output mode, and the counters."""
+import ctypes as C
+
+import numpy as np
+import pytest
+
+from conftest import rmat_graph
+
+pytestmark = pytest.mark.gpu
+
+
+def run_advance(gr, g, mode, output, queue, out_cap, n, m):
+    L = gr._capi.lib()
+    q = np.ascontiguousarray(queue, dtype=np.int32) if queue is not None else None
+    out = np.full(max(out_cap, 1), -7, dtype=np.int32)
+    eh = np.zeros(max(m, 1), np.int32); ss = np.zeros(max(n, 1), np.int64); dh = np.zeros(max(n, 1), np.int32)
+    out_len, insp = C.c_int64(), C.c_uint64()
+    p = lambda a: a.ctypes.data_as(C.c_void_p) if a is not None else None
+    rc = L.grb_test_advance(g._h, mode, output, p(q), (q.size if q is not None else n), p(out), out_cap,
+                            C.byref(out_len), p(eh), p(ss), p(dh), C.byref(insp))
+    assert rc == 0
+    return out[:max(out_len.value, 0)], out_len.value, eh[:m], ss[:n], dh[:n], insp.value
+
+
+def expect_advance(ro, co, queue, n):
+    m = co.size
+    eh = np.zeros(m, np.int64); ss = np.zeros(n, np.int64); dh = np.zeros(n, np.int64)
+    slots = []
+    for s in queue:
+        if s < 0 or s >= n:
+            continue
+        for e in range(ro[s], ro[s + 1]):
+            d = co[e]
+            eh[e] += 1; ss[d] += s
+            ok = (s + d) % 3 != 0
+            if ok:
+                dh[d] += 1
+            slots.append(d if ok else -1)
+    return eh, ss, dh, np.array(slots, dtype=np.int64)
+
+
+@pytest.mark.parametrize("mode", [0, 1], ids=["twc", "lb"])
+@pytest.mark.parametrize("scale", [8, 12])
+def test_advance_contract(gr, orc, mode, scale):
+    ro, co = rmat_graph(orc, scale, 8)
+    n, m = ro.size - 1, co.size
+    g = gr.Graph.from_csr(ro, co)
+    rng = np.random.RandomState(scale)
+    queues = [np.array([0]), np.arange(n), rng.randint(0, n, 300), np.array([], dtype=np.int64),
+              np.array([5, -1, 5, n + 3, 0, -1]),                  # holes, duplicates, out-of-range ids are skipped
+              None]                                               # NULL queue = identity frontier
+    for q in queues:
+        qq = np.arange(n) if q is None else q
+        eh, ss, dh, slots = expect_advance(ro, co, qq, n)
+        outputs = [0, 1] + ([2] if mode == 1 else [])
+        for output in outputs:
+            out, out_len, geh, gss, gdh, insp = run_advance(gr, g, mode, output, q, slots.size + 8, n, m)
+            assert np.array_equal(geh, eh) and np.array_equal(gss, ss) and np.array_equal(gdh, dh)
+            assert insp == slots.size
+            if output == 1:                                      # compact: the passing destinations, any order
+                assert out_len == int((slots >= 0).sum())
+                assert np.array_equal(np.sort(out), np.sort(slots[slots >= 0]))
+            elif output == 2:                                    # tombstone: one slot per edge, frontier order
+                assert out_len == slots.size
+                assert np.array_equal(out, slots)
+    g.close()
+
+
+def test_advance_reports_overflow(gr, orc):
+    ro, co = rmat_graph(orc, 10, 8)
+    n, m = ro.size - 1, co.size
+    g = gr.Graph.from_csr(ro, co)
+    for mode in (0, 1):
+        _, out_len, *_ = run_advance(gr, g, mode, 1, np.arange(n), 10, n, m)
+        assert out_len == -1
+
+
+def run_filter(gr, n, compact, queue, out_cap):
+    L = gr._capi.lib()
+    q = np.ascontiguousarray(queue, dtype=np.int32) if queue is not None else None
+    out = np.full(max(out_cap, 1), -7, dtype=np.int32)
+    dh = np.zeros(max(n, 1), np.int32)
+    out_len = C.c_int64()
+    p = lambda a: a.ctypes.data_as(C.c_void_p) if a is not None else None
+    rc = L.grb_test_filter(0, n, compact, p(q), (q.size if q is not None else n), p(out), out_cap,
+                           C.byref(out_len), p(dh))
+    assert rc == 0
+    return out[:max(out_len.value, 0)], out_len.value, dh[:n]
+
+
+@pytest.mark.parametrize("size", [0, 1, 1000, 1024, 100001])
+def test_filter_contract(gr, size):
+    n = 5000
+    rng = np.random.RandomState(size)
+    q = rng.randint(-1, n, size)                                 # -1 = tombstones left by the advance
+    keep = q[(q >= 0) & (q % 2 == 0)]
+    want_hits = np.bincount(keep, minlength=n)
+    out, out_len, dh = run_filter(gr, n, 1, q, size + 4)
+    assert out_len == keep.size
+    assert np.array_equal(out, keep)                             # compaction preserves the input order within...
+    assert np.array_equal(dh, want_hits)
+    # apply-only map (reference Kernel2): out = in, functor applied to the passing items
+    out, out_len, dh = run_filter(gr, n, 0, q, size + 4)
+    assert out_len == size and np.array_equal(out, q) and np.array_equal(dh, want_hits)
+
+
+def test_filter_identity_frontier_and_overflow(gr):
+    n = 3000
+    out, out_len, dh = run_filter(gr, n, 1, None, n)
+    assert np.array_equal(np.sort(out), np.arange(0, n, 2)) and dh.sum() == n // 2
+    _, out_len, _ = run_filter(gr, n, 1, np.arange(n), 10)
+    assert out_len == -1

@@ -1,0 +1,84 @@
+"""CPU: the host loop of the 1D-partitioned BFS (gunrockinst_b200/partitioned.py) run at
+world_size 1, 2 and 4 over gloo with a numpy stand-in for the device steps (tests/mg_sim.py);
+depths must equal the oracle's serial BFS.  Also the host copy of the partition rule."""
+import os
+import socket
+import sys
+
+import numpy as np
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+from conftest import ROOT
+
+
+def _free_port():
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    p = s.getsockname()[1]
+    s.close()
+    return p
+
+
+def _worker(rank, world, port, scale, sources, dopt, alpha, q):
+    sys.path.insert(0, ROOT)
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import oracle
+    from gunrockinst_b200 import partitioned as pt
+    from mg_sim import NumpyEngine
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        ro, co = oracle.rmat_csr(scale, 8)
+        eng = NumpyEngine(ro, co, world.bit_length() - 1, rank)
+        bfs = pt.PartitionedBfs(eng, direction_optimized=dopt, alpha=alpha)
+        out = []
+        for src in sources:
+            st = bfs.run(src)
+            labels = pt.gather_labels(eng)
+            want = oracle.bfs(ro, co, src)
+            kinds = "".join("P" if lv["kind"] == "pull" else "p" for lv in st["levels"])
+            out.append((bool(np.array_equal(labels, want)), st["iterations"], int(want.max()) + 1, kinds,
+                        st["edges_visited"], oracle.edges_visited(ro, want)))
+        if rank == 0:
+            q.put(out)
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("world", [1, 2, 4])
+@pytest.mark.parametrize("dopt", [False, True])
+def test_partitioned_loop_matches_oracle(world, dopt):
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    sources = [0, 5, 1023]
+    procs = [ctx.Process(target=_worker, args=(r, world, port, 10, sources, dopt, 4.0, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    res = q.get(timeout=240)
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    saw_pull = False
+    for ok, iters, depth, kinds, ev, ev_want in res:
+        assert ok
+        assert ev == ev_want                                   # the GTEPS numerator (bfs_app.cu:82-91)
+        assert iters in (depth, depth - 1) or depth == 0       # last level may or may not discover nothing
+        saw_pull |= "P" in kinds
+    assert saw_pull == dopt
+
+
+def test_partition_rule_is_a_bijection():
+    from gunrockinst_b200.partitioned import owner_of, global_ids
+    for lp in (0, 1, 2, 3):
+        n = 1 << 12
+        seen = np.zeros(n, dtype=np.int32)
+        for r in range(1 << lp):
+            g = global_ids(n >> lp, lp, r)
+            seen[g] += 1
+            assert all(owner_of(int(v), lp) == r for v in g[:64])
+        assert np.all(seen == 1)

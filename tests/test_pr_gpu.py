@@ -1,0 +1,67 @@
+"""GPU: PageRank through the C ABI against the oracle's fp64 restatement of the reference's
+functor semantics.  Tolerance (BASELINE.json north_star): 1e-6 per vertex, absolute, on the
+un-normalised ranks; the same number of power iterations must be executed."""
+import numpy as np
+import pytest
+
+from conftest import load_golden, rmat_graph
+
+pytestmark = pytest.mark.gpu
+TOL = 1e-6
+
+
+def _check(gr, orc, ro, co, symmetric, **kw):
+    src = kw.get("src", -1)
+    want, it = orc.pagerank(ro, co, kw.get("delta", 0.85), kw.get("threshold", 1e-6), kw.get("max_iter", 1000), src)
+    g = gr.Graph.from_csr(ro, co, symmetric=symmetric)
+    ranks, srt, st = gr.pagerank(g, src=src, delta=kw.get("delta", 0.85), threshold=kw.get("threshold", 1e-6),
+                                 max_iter=kw.get("max_iter", 1000), want_sorted=True)
+    assert st["iterations"] == it
+    scale = max(1.0, float(np.abs(want).max()))
+    assert np.max(np.abs(ranks - want)) <= TOL * scale, np.max(np.abs(ranks - want))
+    ids, sr = srt
+    assert sorted(ids.tolist()) == list(range(ro.size - 1))
+    assert np.all(np.diff(sr) <= 0)                                    # descending
+    assert np.array_equal(sr, ranks[ids].astype(np.float32))
+    ties = np.nonzero(np.diff(sr) == 0)[0]
+    assert np.all(ids[ties] < ids[ties + 1])                           # stable: ties by ascending id
+    g.close()
+    return ranks, st
+
+
+@pytest.mark.parametrize("name", ["bips98_606", "chesapeake", "test_cc", "test_pr", "test_pr_dir", "test_bc_dir",
+                                  "bips98_606_dir"])
+def test_fixtures(gr, orc, name):
+    n, ro, co, _ = load_golden(name)
+    sym = not name.endswith("_dir")
+    _check(gr, orc, ro, co, sym)
+    _check(gr, orc, ro, co, False, src=0, threshold=0.01, max_iter=20)      # test_pr.c's configuration
+    _check(gr, orc, ro, co, False, max_iter=3)                               # stops on the iteration cap
+
+
+def test_shared_lib_fixture_through_reference_api(gr, orc, shared_lib):
+    """shared_lib_tests/test_pr.c: personalised (src 0), delta .85, error .01, max_iter 20, top 10"""
+    ro, co = shared_lib["row_offsets"], shared_lib["col_indices"]
+    want, _ = orc.pagerank(np.array(ro), np.array(co), 0.85, 0.01, 20, 0)
+    ids, ranks = gr.gunrock_pr_func(ro, co, src_node=0, delta=0.85, error=0.01, max_iter=20, top_nodes=10)
+    assert ids.size == 7                                               # min(n, top_nodes)
+    order = np.lexsort((np.arange(7), -want.astype(np.float32)))
+    assert ids.tolist() == order.tolist()
+    assert np.allclose(ranks, want[order], atol=1e-6)
+    ids3, _ = gr.gunrock_pr_func(ro, co, src_node=0, delta=0.85, error=0.01, max_iter=20, top_nodes=3)
+    assert ids3.tolist() == order[:3].tolist()
+
+
+@pytest.mark.parametrize("scale,ef,undirected", [(10, 16, True), (16, 16, True), (14, 4, False), (18, 8, True)])
+def test_rmat(gr, orc, scale, ef, undirected):
+    ro, co = rmat_graph(orc, scale, ef, undirected)
+    ranks, st = _check(gr, orc, ro, co, undirected)
+    assert st["iterations"] > 3
+    if not undirected:
+        assert st["pull_levels"] > 2                                   # pruning cascaded over several sweeps
+
+
+def test_edge_cases(gr, orc):
+    for ro, co in [([0, 0], []), ([0, 0, 0, 0], []), ([0, 1, 2, 2], [1, 0]), ([0, 1, 1], [1])]:
+        ro, co = np.array(ro), np.array(co, dtype=np.int32)
+        _check(gr, orc, ro, co, False)

@@ -114,9 +114,9 @@ class BFSEnactor : public EnactorBase {
     // sm_100a policies: 256-thread CTAs, 4 neighbour entries per thread per tile,
     // grids of 148 x MIN_CTAS persistent CTAs; operator-level bitmask pre-cull on,
     // degree tracking on for the fused (non-idempotent) mode
-    typedef oprtr::advance::KernelPolicy<Problem, 256, 4, 6, true, true>   AdvancePolicy;
-    typedef oprtr::advance::KernelPolicy<Problem, 256, 4, 6, true, false>  IdemAdvancePolicy;
-    typedef oprtr::advance::KernelPolicy<Problem, 256, 4, 8, false, false> PullPolicy;
+    typedef oprtr::advance::KernelPolicy<Problem, 256, 4, 5, true, true>   AdvancePolicy;
+    typedef oprtr::advance::KernelPolicy<Problem, 256, 4, 5, true, false>  IdemAdvancePolicy;
+    typedef oprtr::advance::KernelPolicy<Problem, 256, 4, 4, false, false> PullPolicy;
     // reference: END_BITMASK_CULL = 5 (bfs_enactor.cuh:594); the word-atomic mask stays exact, so keep it on
     typedef oprtr::filter::KernelPolicy<Problem, 256, 4, 6, -1>            FilterPolicy;
 

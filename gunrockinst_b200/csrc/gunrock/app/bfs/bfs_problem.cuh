@@ -62,6 +62,7 @@ struct BFSProblem : ProblemBase<_VertexId, _SizeT> {
 
         __host__ __device__ __forceinline__ unsigned long long BitPos(VertexId v) const
         {
+            if (part.log_parts == 0) return (unsigned long long)(unsigned)v;
             return (unsigned long long)part.Owner(v) * (unsigned long long)local_nodes + (unsigned long long)part.Local(v);
         }
         __host__ __device__ __forceinline__ long long LocalRow(VertexId v) const { return part.Local(v); }

@@ -31,7 +31,7 @@ class CCEnactor : public EnactorBase {
     typedef typename Problem::DataSlice DataSlice;
     typedef HookFunctor<VertexId, SizeT, Value, Problem>    HookFn;
     typedef PtrJumpFunctor<VertexId, SizeT, Value, Problem> JumpFn;
-    typedef oprtr::advance::KernelPolicy<Problem, 256, 4, 6, false, false> AdvancePolicy;
+    typedef oprtr::advance::KernelPolicy<Problem, 256, 4, 5, false, false> AdvancePolicy;
     typedef oprtr::filter::KernelPolicy<Problem, 256, 4, 6, 0>             FilterPolicy;
 
     oprtr::advance::LbScratch<SizeT> lb_scratch;

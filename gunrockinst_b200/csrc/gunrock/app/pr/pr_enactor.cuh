@@ -32,7 +32,7 @@ class PREnactor : public EnactorBase {
     typedef typename Problem::DataSlice DataSlice;
     typedef PRFunctor<VertexId, SizeT, Value, Problem>                   PrFunctor;
     typedef RemoveZeroDegreeNodeFunctor<VertexId, SizeT, Value, Problem> RemoveZeroFunctor;
-    typedef oprtr::advance::KernelPolicy<Problem, 256, 4, 6, false, false> AdvancePolicy;
+    typedef oprtr::advance::KernelPolicy<Problem, 256, 4, 5, false, false> AdvancePolicy;
     typedef oprtr::filter::KernelPolicy<Problem, 256, 4, 6, 0>             FilterPolicy;
 
     oprtr::advance::LbScratch<SizeT> lb_scratch;

@@ -29,7 +29,7 @@ class SSSPEnactor : public EnactorBase {
     typedef PQFunctor<VertexId, SizeT, Problem>   PqFunctor;
     // no bitmask pre-cull (a visited vertex can still improve); out-degree of the emitted
     // vertices is tracked to size the next grid
-    typedef oprtr::advance::KernelPolicy<Problem, 256, 4, 6, false, true> AdvancePolicy;
+    typedef oprtr::advance::KernelPolicy<Problem, 256, 4, 5, false, true> AdvancePolicy;
 
     oprtr::advance::LbScratch<SizeT> lb_scratch;
     bool set_up = false;

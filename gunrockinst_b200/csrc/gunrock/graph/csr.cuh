@@ -36,14 +36,18 @@ struct Partition {
     {
         return log_parts ? (((unsigned)local * 0x9E3779B1u) >> (32 - log_parts)) : 0u;
     }
+    // (log_parts is warp-uniform: the single-device tests below cost one uniform branch and
+    //  spare the per-edge hash arithmetic on the path every headline number is measured on)
     __host__ __device__ __forceinline__ int  Owner(long long v) const
     {
+        if (log_parts == 0) return 0;
         return (int)(((unsigned)v & (unsigned)(Parts() - 1)) ^ Mix(v >> log_parts));
     }
-    __host__ __device__ __forceinline__ bool Mine(long long v) const { return Owner(v) == rank; }
+    __host__ __device__ __forceinline__ bool Mine(long long v) const { return log_parts == 0 || Owner(v) == rank; }
     __host__ __device__ __forceinline__ long long Local(long long v) const { return v >> log_parts; }
     __host__ __device__ __forceinline__ long long Global(long long local) const
     {
+        if (log_parts == 0) return local;
         return (local << log_parts) | (long long)((unsigned)rank ^ Mix(local));
     }
 };

@@ -85,6 +85,13 @@ struct Stager {
         }
     }
 
+    // as FlushIfNeeded, for a caller that has just passed a __syncthreads() and does not Push
+    // again before its next one (the count is then stable without two more barriers)
+    __device__ __forceinline__ void FlushIfNeededSynced(unsigned incoming)
+    {
+        if (sm.count + incoming > (unsigned)Policy::STAGE_CAP) Flush();
+    }
+
     // CTA-convergent: flush only if another `incoming` entries might not fit
     __device__ __forceinline__ void FlushIfNeeded(unsigned incoming)
     {

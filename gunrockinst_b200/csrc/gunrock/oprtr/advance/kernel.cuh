@@ -84,7 +84,8 @@ cudaError_t LaunchPullKernel(
 {
     const unsigned long long resident = (unsigned long long)dev.sm_count * Policy::MIN_CTAS;
     unsigned long long words = (unsigned long long)((args.g.local_nodes + 31) >> 5);
-    unsigned long long ctas = (words + Policy::WARPS - 1) / Policy::WARPS;
+    unsigned long long chunks = (words + pull::kChunkWords - 1) / pull::kChunkWords;
+    unsigned long long ctas = (chunks + Policy::WARPS - 1) / Policy::WARPS;
     unsigned grid = (unsigned)(ctas < 1 ? 1 : (ctas < resident ? ctas : resident));
     pull::Kernel<Policy, Problem, Functor><<<grid, Policy::THREADS, 0, stream>>>(ds, args);
     return util::GRError(cudaGetLastError(), "advance pull::Kernel launch failed", __FILE__, __LINE__);

@@ -14,10 +14,13 @@
 //     item that owns it (the merge-path split points; the reference finds them
 //     with a separate sorted search).
 //  2. ExpandKernel: persistent CTAs (a multiple of the SM count) take
-//     equal-sized tiles of the *edge* space.  A tile stages the scanned degrees
-//     of the items it overlaps in shared memory; thread t handles edges
+//     equal-sized tiles of the *edge* space.  The items a tile overlaps drop
+//     their window index at the tile slot where their list starts and set that
+//     slot's bit in a start-flag bitmap (shared memory); thread t handles slots
 //     t, t+THREADS, ... so that a warp reads 128 contiguous bytes of a neighbour
-//     list; each edge finds its item by binary search in shared memory.
+//     list, and finds its item with one masked count-leading-zeros on the flag
+//     word of its 32 slots (plus a per-word carry every warp derives with one
+//     shuffle max-scan) -- no per-edge binary search, 32-bit arithmetic only.
 //     Column loads of a whole tile are issued before any of them is consumed,
 //     then the optional visited-bitmask probes are issued as a batch, and only
 //     survivors reach Functor::CondEdge / ApplyEdge.  Survivors are staged in
@@ -168,94 +171,132 @@ ScanKernel(Args<typename Policy::VertexId, typename Policy::SizeT> args,
 // ---------------------------------------------------------------------------------
 // kernel 2: tile-wise expansion
 // ---------------------------------------------------------------------------------
+template <typename Policy, bool NEED_SRC>
+struct ExpandStorage {
+    typedef typename Policy::VertexId VertexId;
+    typedef typename Policy::SizeT    SizeT;
+    static const int WORDS = Policy::TILE_EDGES / 32;
+    int       own[Policy::TILE_EDGES];          // window index of the item whose list starts at this slot
+    SizeT     base[Policy::WINDOW];             // CSR position of tile slot y of item j = base[j] + y
+    VertexId  src[NEED_SRC ? Policy::WINDOW : 1];
+    unsigned  bits[2][WORDS];                   // start-of-list flags, double buffered by tile parity
+    StagerStorage<Policy> stager;
+    unsigned long long red[Policy::THREADS / 32 + 1];
+};
+
+// Expands tiles cta, cta + num_ctas, ... of the scanned frontier.  Callable from any kernel whose
+// CTAs have Policy::THREADS threads (the stand-alone ExpandKernel below, the persistent BFS kernel).
 template <typename Policy, typename Problem, typename Functor>
-__global__ void __launch_bounds__(Policy::THREADS, Policy::MIN_CTAS)
-ExpandKernel(const __grid_constant__ typename Problem::DataSlice ds,
-             const __grid_constant__ Args<typename Policy::VertexId, typename Policy::SizeT> args,
-             const __grid_constant__ LbScratchView<typename Policy::SizeT> scratch)
+__device__ __forceinline__ void ExpandTiles(
+    const typename Problem::DataSlice &ds,
+    const Args<typename Policy::VertexId, typename Policy::SizeT> &args,
+    const LbScratchView<typename Policy::SizeT> &scratch,
+    ExpandStorage<Policy, Problem::MARK_PREDECESSORS> &sm,
+    unsigned long long in_len, LevelCounters *slot_out, unsigned cta, unsigned num_ctas)
 {
     typedef typename Policy::VertexId VertexId;
     typedef typename Policy::SizeT    SizeT;
     typedef unsigned long long        ScanT;
     constexpr int THREADS = Policy::THREADS, EPT = Policy::EDGES_PER_THREAD;
-    constexpr int TILE_E = Policy::TILE_EDGES, WINDOW = Policy::WINDOW, STAGE_CAP = Policy::STAGE_CAP;
+    constexpr int TILE_E = Policy::TILE_EDGES, WINDOW = Policy::WINDOW;
+    constexpr int WORDS = TILE_E / 32;
     constexpr bool NEED_SRC = Problem::MARK_PREDECESSORS;
+    static_assert(32 % (THREADS / 32) == 0, "warps per CTA must divide 32");
 
-    __shared__ int        s_rel[WINDOW];        // scanned degree of item j minus tile start
-    __shared__ long long  s_base[WINDOW];       // CSR position of edge y of item j = s_base[j] + y
-    __shared__ VertexId   s_src[NEED_SRC ? WINDOW : 1];
-    __shared__ StagerStorage<Policy> s_stager;
-    __shared__ unsigned long long s_red[THREADS / 32 + 1];
-
-    const unsigned long long in_len = args.d_in_len ? *args.d_in_len : args.in_len;
-    LevelCounters *slot_out = args.slots + ((args.queue_index + 1) & 3);
-    if (blockIdx.x == 0 && threadIdx.x == 0) {
-        ClearFutureSlot(args.slots, args.queue_index);
-        *scratch.ticket = 0;            // the scan of this call is complete (stream order)
-    }
-
+    const int lane = util::LaneId();
     const ScanT total = scratch.scanned[in_len];
     unsigned long long num_tiles = (total + TILE_E - 1) / TILE_E;
     if (num_tiles > scratch.part_cap) {     // a frontier with duplicates expanded past the scratch
         num_tiles = scratch.part_cap;
         if (threadIdx.x == 0) slot_out->overflow = 1;
     }
-    Stager<Policy> stager(s_stager, args, slot_out);
+    Stager<Policy> stager(sm.stager, args, slot_out);
     stager.Init();
-    unsigned long long my_edges = 0;
+    for (int x = threadIdx.x; x < 2 * WORDS; x += THREADS) (&sm.bits[0][0])[x] = 0;
+    unsigned my_edges = 0;                  // flushed into a 64-bit sum every tile
+    unsigned long long my_edges_total = 0;
+    int parity = 0;
 
-    for (unsigned long long tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+    for (unsigned long long tile = cta; tile < num_tiles; tile += num_ctas, parity ^= 1) {
         const ScanT tile_start = tile * TILE_E;
         const int tile_edges = (int)((total - tile_start < (ScanT)TILE_E) ? (total - tile_start) : (ScanT)TILE_E);
         const long long i0 = scratch.part_start[tile];
         const long long i1 = (tile + 1 < num_tiles) ? scratch.part_start[tile + 1] : (long long)in_len - 1;
-        const long long cnt = i1 - i0 + 1;
+        const int cnt = (int)((i1 - i0 + 1 < (long long)WINDOW + 1) ? (i1 - i0 + 1) : (long long)WINDOW + 1);
         const bool windowed = cnt <= WINDOW;
 
-        __syncthreads();                // previous tile's readers of s_rel/s_base are done
+        __syncthreads();                // previous tile's readers of own/base/src are done; stager count is stable
+        if (args.output == OUT_COMPACT) stager.FlushIfNeededSynced(TILE_E);
+        unsigned *bits = sm.bits[parity];
         if (windowed) {
-            for (int j = threadIdx.x; j < (int)cnt; j += THREADS) {
-                ScanT s = scratch.scanned[i0 + j];
-                long long rel = (long long)s - (long long)tile_start;
-                s_rel[j]  = rel < -1 ? -1 : (int)rel;
-                s_base[j] = (long long)scratch.row_start[i0 + j] - (long long)s;
-                if constexpr (NEED_SRC) s_src[j] = args.in_queue ? args.in_queue[i0 + j] : (VertexId)args.g.part.Global(i0 + j);
+            for (int j = threadIdx.x; j < cnt; j += THREADS) {
+                const ScanT s = scratch.scanned[i0 + j], e = scratch.scanned[i0 + j + 1];
+                const long long rel = (long long)s - (long long)tile_start;     // < 0 only for j == 0
+                sm.base[j] = (SizeT)((long long)scratch.row_start[i0 + j] - rel);
+                if constexpr (NEED_SRC) sm.src[j] = args.in_queue ? args.in_queue[i0 + j] : (VertexId)args.g.part.Global(i0 + j);
+                const int slot = rel < 0 ? 0 : (int)rel;
+                if (e > s && slot < TILE_E) {       // unique: the lists that start inside a tile start at distinct slots
+                    sm.own[slot] = j;
+                    atomicOr(bits + (slot >> 5), 1u << (slot & 31));
+                }
             }
         }
         __syncthreads();
+        // item covering the first slot of every 32-slot word: each warp derives all of them with
+        // one max-scan (lane L <-> word L of a pass) instead of a CTA-wide step and another barrier
+        int carry_reg[(WORDS + 31) / 32];
+        if (windowed) {
+            int running = 0;
+#pragma unroll
+            for (int p = 0; p < (WORDS + 31) / 32; ++p) {
+                const int wd = p * 32 + lane;
+                const unsigned b = (wd < WORDS) ? bits[wd] : 0u;
+                int last = b ? sm.own[(wd << 5) + 31 - __clz(b)] : 0;
+                last = last > running ? last : running;
+#pragma unroll
+                for (int o = 1; o < 32; o <<= 1) {
+                    const int t = __shfl_up_sync(util::kFullMask, last, o);
+                    if (lane >= o && t > last) last = t;
+                }
+                int excl = __shfl_up_sync(util::kFullMask, last, 1);
+                if (lane == 0) excl = running;
+                carry_reg[p] = excl;
+                running = __shfl_sync(util::kFullMask, last, 31);
+            }
+        }
+        // the other flag buffer is free (its readers passed the barrier above): clear it for the next tile
+        for (int x = threadIdx.x; x < WORDS; x += THREADS) sm.bits[parity ^ 1][x] = 0;
 
-        long long pos[EPT];             // CSR entry index, -1 = no edge for this slot
-        int       item[EPT];
+        SizeT pos[EPT];
+        int   item[EPT];
+        bool  live[EPT];
 #pragma unroll
         for (int r = 0; r < EPT; ++r) {
             const int ly = r * THREADS + threadIdx.x;
-            pos[r] = -1; item[r] = 0;
-            if (ly < tile_edges) {
-                if (windowed) {
-                    int lo = 0, hi = (int)cnt;          // first j with s_rel[j] > ly
-                    while (lo < hi) { int mid = (lo + hi) >> 1; if (s_rel[mid] <= ly) lo = mid + 1; else hi = mid; }
-                    item[r] = lo - 1;
-                    pos[r]  = s_base[lo - 1] + (long long)(tile_start + ly);
-                } else {                                 // rare: > WINDOW (mostly empty) items in one tile
-                    const ScanT y = tile_start + ly;
-                    long long lo = i0, hi = i1 + 1;
-                    while (lo < hi) { long long mid = (lo + hi) >> 1; if (scratch.scanned[mid] <= y) lo = mid + 1; else hi = mid; }
-                    item[r] = (int)(lo - 1 - i0);
-                    pos[r]  = (long long)scratch.row_start[lo - 1] + (long long)(y - scratch.scanned[lo - 1]);
-                }
+            live[r] = ly < tile_edges;
+            pos[r] = 0; item[r] = 0;
+            if (windowed) {
+                const int wd = ly >> 5;                                 // warp-uniform
+                const unsigned m = bits[wd] & (0xffffffffu >> (31 - lane));   // starts at or before my slot
+                // (wd >> 5 is the same for every warp of the CTA in round r: a compile-time index)
+                const int carried = __shfl_sync(util::kFullMask, carry_reg[(r * (THREADS / 32)) >> 5], wd & 31);
+                item[r] = m ? sm.own[(wd << 5) + 31 - __clz(m)] : carried;
+                pos[r]  = sm.base[item[r]] + (SizeT)ly;
+            } else if (live[r]) {                                       // rare: > WINDOW (mostly empty) items in one tile
+                const ScanT y = tile_start + ly;
+                long long lo = i0, hi = i1 + 1;
+                while (lo < hi) { long long mid = (lo + hi) >> 1; if (scratch.scanned[mid] <= y) lo = mid + 1; else hi = mid; }
+                item[r] = (int)(lo - 1 - i0);
+                pos[r]  = (SizeT)((long long)scratch.row_start[lo - 1] + (long long)(y - scratch.scanned[lo - 1]));
             }
         }
         VertexId nbr[EPT];
 #pragma unroll
         for (int r = 0; r < EPT; ++r)
-            nbr[r] = (pos[r] >= 0) ? util::LoadStream(args.g.col_indices + pos[r]) : (VertexId)-1;
-
-        bool live[EPT];
+            nbr[r] = live[r] ? util::LoadStream(args.g.col_indices + pos[r]) : (VertexId)-1;
 #pragma unroll
-        for (int r = 0; r < EPT; ++r) {
-            live[r] = pos[r] >= 0;
-            if (live[r]) ++my_edges;
-        }
+        for (int r = 0; r < EPT; ++r) my_edges += live[r] ? 1u : 0u;
+
         if constexpr (Policy::PRE_CULL) {   // batched visited-bitmask probes (L2 resident)
             unsigned word[EPT];
 #pragma unroll
@@ -263,17 +304,17 @@ ExpandKernel(const __grid_constant__ typename Problem::DataSlice ds,
                 word[r] = live[r] ? util::LoadCA(ds.d_visited_mask + (ds.BitPos(nbr[r]) >> 5)) : 0u;
 #pragma unroll
             for (int r = 0; r < EPT; ++r)
-                if (live[r] && ((word[r] >> (ds.BitPos(nbr[r]) & 31)) & 1u)) live[r] = false;
+                if ((word[r] >> (ds.BitPos(nbr[r]) & 31)) & 1u) live[r] = false;
         }
 #pragma unroll
         for (int r = 0; r < EPT; ++r) {
             bool ok = false;
             if (live[r]) {
                 VertexId s_id;
-                if constexpr (NEED_SRC) s_id = windowed ? s_src[item[r]]
+                if constexpr (NEED_SRC) s_id = windowed ? sm.src[item[r]]
                                       : (args.in_queue ? args.in_queue[i0 + item[r]] : (VertexId)args.g.part.Global(i0 + item[r]));
                 else                    s_id = (VertexId)args.iteration;
-                ok = VisitEdge<Policy, Problem, Functor>(&ds, s_id, nbr[r], (SizeT)pos[r], (SizeT)(i0 + item[r]));
+                ok = VisitEdge<Policy, Problem, Functor>(&ds, s_id, nbr[r], pos[r], (SizeT)(i0 + item[r]));
             }
             if (args.output == OUT_COMPACT) {
                 stager.Push(ok, nbr[r]);
@@ -286,14 +327,30 @@ ExpandKernel(const __grid_constant__ typename Problem::DataSlice ds,
                 }
             }
         }
-        if (args.output == OUT_COMPACT) stager.FlushIfNeeded(TILE_E);
+        my_edges_total += my_edges; my_edges = 0;
     }
     if (args.output == OUT_COMPACT) stager.Flush();
-    else if (args.output == OUT_TOMBSTONE && blockIdx.x == 0 && threadIdx.x == 0) slot_out->out_len = total;
+    else if (args.output == OUT_TOMBSTONE && cta == 0 && threadIdx.x == 0) slot_out->out_len = total;
 
     // per-CTA statistics: one atomic each
-    BlockAccumulate<THREADS>(my_edges, s_red, &slot_out->edges);
-    if constexpr (Policy::TRACK_OUT_DEGREE) BlockAccumulate<THREADS>(stager.out_degree, s_red, &slot_out->out_degree);
+    BlockAccumulate<THREADS>(my_edges_total, sm.red, &slot_out->edges);
+    if constexpr (Policy::TRACK_OUT_DEGREE) BlockAccumulate<THREADS>(stager.out_degree, sm.red, &slot_out->out_degree);
+}
+
+template <typename Policy, typename Problem, typename Functor>
+__global__ void __launch_bounds__(Policy::THREADS, Policy::MIN_CTAS)
+ExpandKernel(const __grid_constant__ typename Problem::DataSlice ds,
+             const __grid_constant__ Args<typename Policy::VertexId, typename Policy::SizeT> args,
+             const __grid_constant__ LbScratchView<typename Policy::SizeT> scratch)
+{
+    __shared__ ExpandStorage<Policy, Problem::MARK_PREDECESSORS> s_expand;
+    const unsigned long long in_len = args.d_in_len ? *args.d_in_len : args.in_len;
+    LevelCounters *slot_out = args.slots + ((args.queue_index + 1) & 3);
+    if (blockIdx.x == 0 && threadIdx.x == 0) {
+        ClearFutureSlot(args.slots, args.queue_index);
+        *scratch.ticket = 0;            // the scan of this call is complete (stream order)
+    }
+    ExpandTiles<Policy, Problem, Functor>(ds, args, scratch, s_expand, in_len, slot_out, blockIdx.x, gridDim.x);
 }
 
 }  // namespace lb

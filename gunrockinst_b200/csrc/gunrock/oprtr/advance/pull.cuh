@@ -12,12 +12,25 @@
 //     visited        read+written, only the words of the rows this device owns
 //     frontier_in    read-only (probed through the non-coherent path)
 //     frontier_out   written whole words, no atomics, no prior memset
-// and the kernel SWEEPS the owned rows: one warp per 32-vertex word, one lane
-// per vertex.  A word whose vertices are all visited (or edgeless: `candidates`)
-// costs one 4-byte load.  An unvisited lane walks its in-neighbour list with
-// early exit; lists longer than SERIAL_LIMIT are finished by the whole warp with
-// 128-byte coalesced reads and a ballot early exit, so a straggler list cannot
-// serialise a warp.  Newly found vertices are published as one word store.
+// and the kernel SWEEPS the owned rows in chunks of CHUNK_WORDS bitmap words
+// (256 vertices) per warp:
+//   1. scan    -- the warp reads the chunk's visited / candidate words and packs the
+//                 positions of the vertices still to do into a shared-memory list
+//                 (byte offsets), so that the walk below runs with dense lanes
+//                 whatever fraction of the chunk is left (late pull levels leave < 1 %);
+//                 a chunk with nothing to do costs two coalesced loads per word;
+//   2. probe   -- every lane takes UNROLL listed vertices at once and issues, for all
+//                 of them, the row-offset pairs, then the first two neighbour ids,
+//                 then the two frontier-bit probes: the dependent chain
+//                 offsets -> neighbour -> bit is three loads deep with 2*UNROLL probes
+//                 in flight per lane (an R-MAT list is sorted, hubs first, so ~90 % of
+//                 the vertices find their parent here);
+//   3. walk    -- the few that did not continue lane-serially with early exit up to
+//                 SERIAL_LIMIT entries; what is left of long lists is finished by the
+//                 whole warp with 128-byte coalesced reads and a ballot early exit, so
+//                 a straggler list cannot serialise a warp;
+//   4. publish -- found vertices are OR-ed into a per-warp word buffer in shared memory
+//                 and leave as whole-word stores (frontier_out, visited), no global atomics.
 //
 // Algorithmic HBM bytes per call: n/8 (visited) [+ n/8 candidates] + n/8
 // (frontier_out) for the sweep, 2*sizeof(SizeT) per unvisited candidate, 4 + 1
@@ -46,122 +59,209 @@ struct PullArgs {
     long long       iteration;
 };
 
+
+constexpr int kChunkWords = 8;                  // bitmap words a warp sweeps at a time
+constexpr int kChunkVerts = kChunkWords * 32;   // ... = 256 vertices, so list entries fit a byte
+
+template <int WARPS>
+struct SweepStorage {
+    unsigned char      cand[WARPS][kChunkVerts];    // per warp: positions of the chunk's vertices still to do
+    unsigned           found[WARPS][kChunkWords];   // per warp: discoveries of the chunk, one bit each
+    unsigned long long red[WARPS + 1];
+};
+
+// The sweep itself, callable from any kernel whose CTAs have Policy::THREADS threads:
+// warp `first_chunk` of `chunk_stride` warps takes chunks first_chunk, first_chunk + chunk_stride, ...
+// Accumulates edges / out_degree / aux0 (= vertices examined) / out_len into `slot_out`.
+template <typename Policy, typename Problem, typename Functor>
+__device__ __forceinline__ void Sweep(
+    const typename Problem::DataSlice &ds,
+    const PullArgs<typename Policy::VertexId, typename Policy::SizeT> &args,
+    SweepStorage<Policy::WARPS> &sm, LevelCounters *slot_out,
+    long long first_chunk, long long chunk_stride)
+{
+    typedef typename Policy::VertexId VertexId;
+    typedef typename Policy::SizeT    SizeT;
+    constexpr int THREADS = Policy::THREADS;
+    constexpr int SERIAL_LIMIT = 8, U = 2;
+    constexpr bool NEED_SRC = Problem::MARK_PREDECESSORS;
+
+    const int lane = util::LaneId();
+    const long long local_nodes = args.g.local_nodes;
+    const long long num_words  = (local_nodes + 31) >> 5;
+    const long long num_chunks = (num_words + kChunkWords - 1) / kChunkWords;
+    // first word of this device's segment inside the global bitmaps
+    const long long seg = ((long long)args.g.part.rank * local_nodes) >> 5;
+    unsigned char *s_cand  = sm.cand[util::WarpId()];
+    unsigned      *s_found = sm.found[util::WarpId()];
+    const int my_word = lane >> 2, my_shift = (lane & 3) << 3;     // lane -> byte (lane & 3) of word (lane >> 2)
+
+    unsigned long long my_edges = 0, my_found = 0, my_degree = 0, my_cands = 0;
+
+    for (long long c = first_chunk; c < num_chunks; c += chunk_stride) {
+        // ---- 1. scan ---------------------------------------------------------------------------
+        const long long w0 = c * kChunkWords, w = w0 + my_word;
+        unsigned vis = 0xffffffffu, todo = 0;
+        if (w < num_words) {
+            vis  = util::LoadCG(args.visited + seg + w);
+            todo = ~vis;
+            if (args.candidates) todo &= util::LoadStream(args.candidates + w);
+            if (w == num_words - 1 && (local_nodes & 31)) todo &= (1u << (local_nodes & 31)) - 1;
+        }
+        const unsigned mine = (todo >> my_shift) & 0xffu;
+        const unsigned cnt  = (unsigned)__popc(mine);
+        const unsigned incl = util::WarpInclusiveSum(cnt);
+        const unsigned total = __shfl_sync(util::kFullMask, incl, 31);
+        if (total == 0) {                                       // uniform across the warp
+            if ((lane & 3) == 0 && w < num_words) args.frontier_out[seg + w] = 0;
+            continue;
+        }
+        {
+            unsigned at = incl - cnt, m = mine;
+            const unsigned pos0 = (unsigned)(my_word * 32 + my_shift);
+            while (m) { const int b = __ffs(m) - 1; m &= m - 1; s_cand[at++] = (unsigned char)(pos0 + b); }
+            if (lane < kChunkWords) s_found[lane] = 0;
+        }
+        __syncwarp();
+        my_cands += cnt;
+
+        for (unsigned k0 = 0; k0 < total; k0 += 32 * U) {
+            // ---- 2. probe: offsets, then two neighbours, then two frontier bits, UNROLL vertices per lane
+            bool      act[U], found[U];
+            unsigned  off[U];
+            long long begin[U], end[U], epos[U];
+            VertexId  parent[U];
+#pragma unroll
+            for (int u = 0; u < U; ++u) {
+                const unsigned idx = k0 + u * 32 + lane;
+                act[u] = idx < total;
+                off[u] = act[u] ? (unsigned)s_cand[idx] : 0u;
+                begin[u] = end[u] = 0;
+                if (act[u]) {
+                    const long long row = (w0 << 5) + off[u];
+                    begin[u] = (long long)args.g.row_offsets[row];
+                    end[u]   = (long long)args.g.row_offsets[row + 1];
+                }
+            }
+            VertexId n0[U], n1[U];
+#pragma unroll
+            for (int u = 0; u < U; ++u) {
+                n0[u] = (begin[u]     < end[u]) ? util::LoadStream(args.g.col_indices + begin[u])     : (VertexId)-1;
+                n1[u] = (begin[u] + 1 < end[u]) ? util::LoadStream(args.g.col_indices + begin[u] + 1) : (VertexId)-1;
+            }
+            bool h0[U], h1[U];
+#pragma unroll
+            for (int u = 0; u < U; ++u) {
+                h0[u] = n0[u] >= 0 && util::BitTest(args.frontier_in, ds.BitPos(n0[u]));
+                h1[u] = n1[u] >= 0 && util::BitTest(args.frontier_in, ds.BitPos(n1[u]));
+            }
+#pragma unroll
+            for (int u = 0; u < U; ++u) {
+                found[u] = h0[u] || h1[u];
+                parent[u] = h0[u] ? n0[u] : n1[u];
+                epos[u] = h0[u] ? begin[u] : begin[u] + 1;
+                // entries an early-exit walk would have looked at
+                my_edges += h0[u] ? 1u : (unsigned)(n0[u] >= 0) + (unsigned)(n1[u] >= 0);
+            }
+            // ---- 3. walk what is left --------------------------------------------------------------
+#pragma unroll
+            for (int u = 0; u < U; ++u) {
+                long long k = begin[u] + 2;
+                if (act[u] && !found[u] && k < end[u]) {
+                    const long long lim = (end[u] - begin[u] > SERIAL_LIMIT) ? begin[u] + SERIAL_LIMIT : end[u];
+                    const long long k_first = k;
+                    while (k < lim) {
+                        const VertexId x = util::LoadStream(args.g.col_indices + k);
+                        if (util::BitTest(args.frontier_in, ds.BitPos(x))) { found[u] = true; parent[u] = x; epos[u] = k; ++k; break; }
+                        ++k;
+                    }
+                    my_edges += (unsigned long long)(k - k_first);
+                }
+                unsigned rest = __ballot_sync(util::kFullMask, act[u] && !found[u] && k < end[u]);
+                while (rest) {
+                    const int leader = __ffs(rest) - 1;
+                    rest &= rest - 1;
+                    const long long wb = __shfl_sync(util::kFullMask, k, leader);
+                    const long long we = __shfl_sync(util::kFullMask, end[u], leader);
+                    for (long long p = wb; p < we; p += 32) {
+                        const long long idx = p + lane;
+                        VertexId x = -1;
+                        bool hit = false;
+                        if (idx < we) {
+                            x = util::LoadStream(args.g.col_indices + idx);
+                            hit = util::BitTest(args.frontier_in, ds.BitPos(x));
+                            ++my_edges;
+                        }
+                        const unsigned hm = __ballot_sync(util::kFullMask, hit);
+                        if (hm) {
+                            const int first = __ffs(hm) - 1;
+                            const VertexId px = __shfl_sync(util::kFullMask, x, first);
+                            if (lane == leader) { found[u] = true; parent[u] = px; epos[u] = p + first; }
+                            break;
+                        }
+                    }
+                }
+            }
+            // ---- 4. functor + publication ----------------------------------------------------------
+#pragma unroll
+            for (int u = 0; u < U; ++u) {
+                const long long row = (w0 << 5) + off[u];
+                const VertexId child = (VertexId)args.g.part.Global(row);
+                if (found[u]) {
+                    const VertexId s_id = NEED_SRC ? parent[u] : (VertexId)args.iteration;
+                    found[u] = VisitEdge<Policy, Problem, Functor>(&ds, s_id, child, (SizeT)epos[u], (SizeT)row);
+                }
+                if (found[u]) {
+                    atomicOr(s_found + (off[u] >> 5), 1u << (off[u] & 31));
+                    if (args.fwd_row_offsets)
+                        my_degree += (unsigned long long)(args.fwd_row_offsets[row + 1] - args.fwd_row_offsets[row]);
+                    else
+                        my_degree += (unsigned long long)(end[u] - begin[u]);
+                }
+                if (args.out_queue) {
+                    const unsigned fm = __ballot_sync(util::kFullMask, found[u]);
+                    if (fm) {
+                        unsigned long long b = 0;
+                        if (lane == 0) b = atomicAdd(&slot_out->out_len, (unsigned long long)__popc(fm));
+                        b = __shfl_sync(util::kFullMask, b, 0);
+                        if (found[u]) {
+                            const unsigned long long at = b + __popc(fm & ((1u << lane) - 1));
+                            if (at < args.out_cap) args.out_queue[at] = child;
+                            else slot_out->overflow = 1;
+                        }
+                    }
+                }
+            }
+        }
+        __syncwarp();
+        // whole-word publication: lane l < CHUNK_WORDS owns word w0 + l (its visited word sits in lane 4l)
+        const unsigned vis_l = __shfl_sync(util::kFullMask, vis, (lane & (kChunkWords - 1)) << 2);
+        if (lane < kChunkWords && w0 + lane < num_words) {
+            const unsigned fm = s_found[lane];
+            args.frontier_out[seg + w0 + lane] = fm;
+            if (fm) args.visited[seg + w0 + lane] = vis_l | fm;
+            my_found += (unsigned)__popc(fm);
+        }
+        __syncwarp();                                           // the lists are rewritten by the next chunk
+    }
+    BlockAccumulate<THREADS>(my_edges,  sm.red, &slot_out->edges);
+    BlockAccumulate<THREADS>(my_degree, sm.red, &slot_out->out_degree);
+    BlockAccumulate<THREADS>(my_cands,  sm.red, &slot_out->aux0);
+    // found vertices are counted in out_len unless the queue path already did
+    if (!args.out_queue) BlockAccumulate<THREADS>(my_found, sm.red, &slot_out->out_len);
+}
+
 template <typename Policy, typename Problem, typename Functor>
 __global__ void __launch_bounds__(Policy::THREADS, Policy::MIN_CTAS)
 Kernel(const __grid_constant__ typename Problem::DataSlice ds,
        const __grid_constant__ PullArgs<typename Policy::VertexId, typename Policy::SizeT> args)
 {
-    typedef typename Policy::VertexId VertexId;
-    typedef typename Policy::SizeT    SizeT;
-    constexpr int THREADS = Policy::THREADS, WARPS = Policy::WARPS;
-    constexpr int SERIAL_LIMIT = 8;
-    constexpr bool NEED_SRC = Problem::MARK_PREDECESSORS;
-
-    __shared__ unsigned long long s_red[THREADS / 32 + 1];
-
+    __shared__ SweepStorage<Policy::WARPS> s_sweep;
     LevelCounters *slot_out = args.slots + ((args.queue_index + 1) & 3);
     if (blockIdx.x == 0 && threadIdx.x == 0) ClearFutureSlot(args.slots, args.queue_index);
-
-    const int lane = util::LaneId();
-    const long long local_nodes = args.g.local_nodes;
-    const long long num_words = (local_nodes + 31) >> 5;
-    // first word of this device's segment inside the global bitmaps
-    const long long seg = ((long long)args.g.part.rank * local_nodes) >> 5;
-    const long long warps_total = (long long)gridDim.x * WARPS;
-
-    unsigned long long my_edges = 0, my_found = 0, my_degree = 0, my_cands = 0;
-
-    for (long long w = (long long)blockIdx.x * WARPS + util::WarpId(); w < num_words; w += warps_total) {
-        const unsigned vis = args.visited[seg + w];
-        unsigned todo = ~vis;
-        if (args.candidates) todo &= util::LoadStream(args.candidates + w);
-        if (w == num_words - 1 && (local_nodes & 31)) todo &= (1u << (local_nodes & 31)) - 1;
-        if (todo == 0) {                                 // uniform across the warp
-            if (lane == 0) args.frontier_out[seg + w] = 0;
-            continue;
-        }
-        const bool active = (todo >> lane) & 1u;
-        const long long row = (w << 5) + lane;
-        long long k = 0, end = 0, begin = 0;
-        if (active) {
-            begin = (long long)args.g.row_offsets[row];
-            end   = (long long)args.g.row_offsets[row + 1];
-            k = begin;
-        }
-        if (active) ++my_cands;
-        bool found = false;
-        VertexId parent = -1;
-        long long epos = 0;
-
-        // ---- lane-serial walk over the head of the list, early exit -----------------------
-        {
-            const long long lim = (end - begin > SERIAL_LIMIT) ? begin + SERIAL_LIMIT : end;
-            while (k < lim) {
-                const VertexId u = util::LoadStream(args.g.col_indices + k);
-                if (util::BitTest(args.frontier_in, ds.BitPos(u))) { found = true; parent = u; epos = k; ++k; break; }
-                ++k;
-            }
-            my_edges += (unsigned long long)(k - begin);
-        }
-        // ---- warp-cooperative walk over what is left of long lists -----------------------------
-        unsigned rest = __ballot_sync(util::kFullMask, active && !found && k < end);
-        while (rest) {
-            const int leader = __ffs(rest) - 1;
-            rest &= rest - 1;
-            const long long wb = __shfl_sync(util::kFullMask, k, leader);
-            const long long we = __shfl_sync(util::kFullMask, end, leader);
-            for (long long p = wb; p < we; p += 32) {
-                const long long idx = p + lane;
-                VertexId u = -1;
-                bool hit = false;
-                if (idx < we) {
-                    u = util::LoadStream(args.g.col_indices + idx);
-                    hit = util::BitTest(args.frontier_in, ds.BitPos(u));
-                    ++my_edges;
-                }
-                const unsigned hm = __ballot_sync(util::kFullMask, hit);
-                if (hm) {
-                    const int first = __ffs(hm) - 1;
-                    const VertexId pu = __shfl_sync(util::kFullMask, u, first);
-                    if (lane == leader) { found = true; parent = pu; epos = p + first; }
-                    break;
-                }
-            }
-        }
-        // ---- functor + publication ----------------------------------------------------------
-        const VertexId child = (VertexId)args.g.part.Global(row);
-        if (found) {
-            const VertexId s_id = NEED_SRC ? parent : (VertexId)args.iteration;
-            found = VisitEdge<Policy, Problem, Functor>(&ds, s_id, child, (SizeT)epos, (SizeT)row);
-        }
-        const unsigned fm = __ballot_sync(util::kFullMask, found);
-        if (lane == 0) {
-            args.frontier_out[seg + w] = fm;
-            if (fm) args.visited[seg + w] = vis | fm;
-            my_found += __popc(fm);
-        }
-        if (found) {
-            if (args.fwd_row_offsets)
-                my_degree += (unsigned long long)(args.fwd_row_offsets[row + 1] - args.fwd_row_offsets[row]);
-            else
-                my_degree += (unsigned long long)(end - begin);
-        }
-        if (args.out_queue && fm) {
-            unsigned long long b = 0;
-            if (lane == 0) b = atomicAdd(&slot_out->out_len, (unsigned long long)__popc(fm));
-            b = __shfl_sync(util::kFullMask, b, 0);
-            if (found) {
-                const unsigned long long at = b + __popc(fm & ((1u << lane) - 1));
-                if (at < args.out_cap) args.out_queue[at] = child;
-                else slot_out->overflow = 1;
-            }
-        }
-    }
-    BlockAccumulate<THREADS>(my_edges, s_red, &slot_out->edges);
-    BlockAccumulate<THREADS>(my_degree, s_red, &slot_out->out_degree);
-    BlockAccumulate<THREADS>(my_cands, s_red, &slot_out->aux0);
-    // found vertices are counted in out_len unless the queue path already did
-    if (!args.out_queue) BlockAccumulate<THREADS>(my_found, s_red, &slot_out->out_len);
+    Sweep<Policy, Problem, Functor>(ds, args, s_sweep, slot_out,
+                                    (long long)blockIdx.x * Policy::WARPS + util::WarpId(),
+                                    (long long)gridDim.x * Policy::WARPS);
 }
 
 }  // namespace pull

@@ -75,7 +75,9 @@ Kernel(const __grid_constant__ typename Problem::DataSlice ds,
     constexpr int THREADS = Policy::THREADS, IPT = Policy::ITEMS_PER_THREAD, TILE = Policy::TILE;
     constexpr bool IDEMPOTENT = Problem::ENABLE_IDEMPOTENCE;
 
-    __shared__ unsigned s_warp[THREADS / 32 + 1];
+    constexpr int WARPS = THREADS / 32;
+    __shared__ unsigned s_cnt[IPT * WARPS];
+    __shared__ unsigned s_total;
     __shared__ unsigned long long s_base;
     __shared__ VertexId s_history[IDEMPOTENT ? Policy::HISTORY_SLOTS : 1];
 
@@ -161,27 +163,44 @@ Kernel(const __grid_constant__ typename Problem::DataSlice ds,
                 if (id[r] >= 0 && (__ffs(peers) - 1) != lane) id[r] = -1;
             }
         }
-        // ---- compaction: flags -> CTA scan -> one atomic -> scatter ---------------------------
-        unsigned flags = 0, cnt = 0;
+        // ---- compaction: ballots -> scan of (round, warp) counts -> one atomic -> scatter -------
+        // Stable: survivors keep their input order inside a tile (as the reference's raking scan
+        // does, filter/cta.cuh:520-544) and each warp writes one contiguous run per round.
+        unsigned bal[IPT];
 #pragma unroll
-        for (int r = 0; r < IPT; ++r) if (id[r] >= 0) { flags |= 1u << r; ++cnt; }
-        unsigned total;
-        unsigned excl = util::BlockExclusiveSum<THREADS>(cnt, s_warp, total);
-        if (total == 0) continue;                               // uniform
-        if (threadIdx.x == 0) s_base = atomicAdd(&slot_out->out_len, (unsigned long long)total);
+        for (int r = 0; r < IPT; ++r) bal[r] = __ballot_sync(util::kFullMask, id[r] >= 0);
+        if (lane == 0) {
+#pragma unroll
+            for (int r = 0; r < IPT; ++r) s_cnt[r * WARPS + util::WarpId()] = (unsigned)__popc(bal[r]);
+        }
         __syncthreads();
-        const unsigned long long ob = s_base;
-        if (args.out_queue) {
+        if (util::WarpId() == 0) {
+            unsigned running = 0;
+            for (int c = 0; c < IPT * WARPS; c += 32) {
+                const unsigned v = (c + lane < IPT * WARPS) ? s_cnt[c + lane] : 0u;
+                const unsigned incl = util::WarpInclusiveSum(v);
+                if (c + lane < IPT * WARPS) s_cnt[c + lane] = running + incl - v;
+                running += __shfl_sync(util::kFullMask, incl, 31);
+            }
+            if (lane == 0) {
+                s_total = running;
+                if (running) s_base = atomicAdd(&slot_out->out_len, (unsigned long long)running);
+            }
+        }
+        __syncthreads();
+        if (s_total != 0 && args.out_queue) {
+            const unsigned long long ob = s_base;
 #pragma unroll
             for (int r = 0; r < IPT; ++r) {
-                if (flags & (1u << r)) {
-                    const unsigned long long at = ob + excl++;
+                if (id[r] >= 0) {
+                    const unsigned long long at = ob + s_cnt[r * WARPS + util::WarpId()]
+                                                + (unsigned)__popc(bal[r] & ((1u << lane) - 1));
                     if (at < args.out_cap) args.out_queue[at] = id[r];
                     else slot_out->overflow = 1;
                 }
             }
         }
-        __syncthreads();                                        // s_base is rewritten next tile
+        __syncthreads();                                        // s_cnt / s_base are rewritten next tile
     }
 }
 

@@ -67,7 +67,7 @@ cudaError_t RunAdvance(gunrock::graph::DeviceCsr<int, SizeT> *g, cudaStream_t s,
     using namespace gunrock;
     typedef ProbeProblem<SizeT> Problem;
     typedef ProbeFunctor<Problem> Functor;
-    typedef oprtr::advance::KernelPolicy<Problem, 256, 4, 6, false, false> Policy;
+    typedef oprtr::advance::KernelPolicy<Problem, 256, 4, 5, false, false> Policy;
     const size_t n = (size_t)g->nodes, m = (size_t)g->edges;
     util::DeviceArray<int> d_in, d_out, d_eh, d_dh;
     util::DeviceArray<long long> d_ss;

@@ -259,7 +259,7 @@ def run_single(args):
     value = edges / (ms * 1e-3) / 1e9
 
     # ---- per-kernel roofline: one traced pass over the same sources (events around every level)
-    tr = gr.Bfs(g, direction_optimized=True, record_levels=True)
+    tr = gr.Bfs(g, direction_optimized=True, record_levels=True, host_loop=True)
     for i in range(3):
         tr.run(sources[i % len(sources)], want_labels=False)
     agg = {}

@@ -125,10 +125,11 @@ class Bfs:
     """
 
     def __init__(self, graph, mark_pred=False, idempotence=False, traversal_mode=0,
-                 direction_optimized=False, alpha=0.0, beta=0.0, queue_sizing=0.0, record_levels=False):
+                 direction_optimized=False, alpha=0.0, beta=0.0, queue_sizing=0.0, record_levels=False,
+                 host_loop=False):
         self.graph = graph
         cfg = BfsConfig(int(mark_pred), int(idempotence), int(traversal_mode), int(direction_optimized),
-                        float(alpha), float(beta), float(queue_sizing), int(record_levels), 0)
+                        float(alpha), float(beta), float(queue_sizing), int(record_levels), int(host_loop))
         self.mark_pred = bool(mark_pred)
         self._h = C.c_void_p()
         _capi.check(_capi.lib().grb_bfs_create(graph._h, C.byref(cfg), C.byref(self._h)), "grb_bfs_create")

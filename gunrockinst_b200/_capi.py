@@ -57,7 +57,7 @@ class LevelRecord(C.Structure):
 class BfsConfig(C.Structure):
     _fields_ = [("mark_pred", C.c_int32), ("idempotence", C.c_int32), ("traversal_mode", C.c_int32),
                 ("direction_optimized", C.c_int32), ("alpha", C.c_double), ("beta", C.c_double),
-                ("queue_sizing", C.c_double), ("record_levels", C.c_int32), ("reserved", C.c_int32)]
+                ("queue_sizing", C.c_double), ("record_levels", C.c_int32), ("host_loop", C.c_int32)]
 
 
 class MgLevel(C.Structure):

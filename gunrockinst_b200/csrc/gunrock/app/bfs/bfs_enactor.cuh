@@ -24,6 +24,7 @@
 #include <vector>
 #include "bfs_functor.cuh"
 #include "../enactor_base.cuh"
+#include "bfs_persistent.cuh"
 
 namespace gunrock {
 namespace app {
@@ -93,6 +94,8 @@ struct BFSOptions {
     double beta                = 24.0;   // pull -> push when frontier < n / beta and shrinking
     unsigned long long lb_min_edges = 1u << 12;   // mode 0: LB from this many frontier edges upward
     bool   record_levels       = false;  // keep a per-level trace (adds two events per level)
+    bool   host_loop           = false;  // drive every level from the host (the reference's structure) instead
+                                         // of the single cooperative kernel of bfs_persistent.cuh
 };
 
 struct LevelRecord {
@@ -125,6 +128,14 @@ class BFSEnactor : public EnactorBase {
     unsigned long long edges_visited = 0;       // sum of out-degrees of visited vertices (reference GTEPS numerator)
     cudaEvent_t ev_a = nullptr, ev_b = nullptr;
     bool set_up = false;
+    // persistent (single cooperative kernel) loop
+    static const int kMaxRecords = 1024;
+    util::DeviceArray<DeviceLevelRecord>  d_records;
+    util::DeviceArray<PersistentSummary>  d_summary;     // [0] summary, [1] reused as the 8-byte queue cursor
+    util::PinnedArray<DeviceLevelRecord>  h_records;
+    util::PinnedArray<PersistentSummary>  h_summary;
+    bool persistent_ok = false;
+    int  persistent_grid = 0;
 
     ~BFSEnactor()
     {
@@ -143,20 +154,34 @@ class BFSEnactor : public EnactorBase {
         GR_TRY(lb_scratch.Allocate(max_items, (size_t)problem->graph->edges + 1, AdvancePolicy::SCAN_TILE,
                                    AdvancePolicy::TILE_EDGES, s));
         if (!ev_a) { GR_TRY(cudaEventCreate(&ev_a)); GR_TRY(cudaEventCreate(&ev_b)); }
+        if constexpr (!Problem::ENABLE_IDEMPOTENCE) GR_TRY(SetupPersistent(problem));
         set_up = true;
         return cudaSuccess;
     }
 
     // reference signature: Enact<BFSProblem>(context, problem, src, max_grid_size, traversal_mode)
-    cudaError_t Enact(Problem *problem, VertexId src, const BFSOptions &opt)
+    // true when Enact will run the whole search, Problem::Reset's device work included, as one
+    // kernel: the caller may then use Problem::Reset(..., on_device = true)
+    bool FusesReset(VertexId src, const Problem *problem, const BFSOptions &opt) const
+    {
+        return set_up && !Problem::ENABLE_IDEMPOTENCE && persistent_ok && !opt.host_loop &&
+               src >= 0 && (long long)src < problem->graph->nodes;
+    }
+
+    cudaError_t Enact(Problem *problem, VertexId src, const BFSOptions &opt, bool reset_on_device = false)
     {
         if (!set_up) return util::GRError(cudaErrorNotReady, "BFSEnactor::Setup not called", __FILE__, __LINE__);
-        GR_TRY(ResetBase());
+        if (reset_on_device && !FusesReset(src, problem, opt))
+            return util::GRError(cudaErrorInvalidValue, "BFSEnactor: device-side reset needs the persistent kernel",
+                                 __FILE__, __LINE__);
+        if (reset_on_device) { enactor_stats = EnactorStats(); frontier_attribute = FrontierAttribute(); }
+        else GR_TRY(ResetBase());
         levels.clear();
         edges_visited = 0;
         if (src < 0 || (long long)src >= problem->graph->nodes) return cudaSuccess;
         if constexpr (Problem::ENABLE_IDEMPOTENCE) return EnactIdempotent(problem, opt);
-        else return EnactFused(problem, opt);
+        else return (opt.host_loop || !persistent_ok) ? EnactFused(problem, opt)
+                                                      : EnactPersistent(problem, opt, reset_on_device);
     }
 
     // recount edges_visited from the labels (idempotent mode cannot track it: duplicates)
@@ -197,6 +222,110 @@ class BFSEnactor : public EnactorBase {
         if (opt.traversal_mode == 1) return oprtr::advance::LB;
         if (opt.traversal_mode == 2) return oprtr::advance::TWC_FORWARD;
         return frontier_edges >= opt.lb_min_edges ? oprtr::advance::LB : oprtr::advance::TWC_FORWARD;
+    }
+
+    // ---- persistent mode: the level loop runs on the device (bfs_persistent.cuh) ------------------
+    typedef PersistentParams<VertexId, SizeT> PParams;
+    typedef void (*PersistentFn)(const DataSlice, const PParams, unsigned long long *, unsigned long long);
+    static PersistentFn PersistentEntry()
+    {
+        return &PersistentKernel<AdvancePolicy, PullPolicy, Problem, BfsFunctor, PullFunctor>;
+    }
+
+    cudaError_t SetupPersistent(Problem *problem)
+    {
+        int coop = 0;
+        GR_TRY(cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, dev.device));
+        int per_sm = 0;
+        GR_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, PersistentEntry(), AdvancePolicy::THREADS, 0));
+        if (per_sm > kPersistentCtasPerSm) per_sm = kPersistentCtasPerSm;
+        persistent_ok = coop != 0 && per_sm > 0;
+        persistent_grid = per_sm * dev.sm_count;
+        GR_TRY(d_records.Allocate(kMaxRecords));
+        GR_TRY(d_summary.Allocate(2));
+        GR_TRY(h_records.Allocate(kMaxRecords));
+        GR_TRY(h_summary.Allocate(1));
+        return cudaSuccess;
+    }
+
+    cudaError_t EnactPersistent(Problem *problem, const BFSOptions &opt, bool reset_on_device)
+    {
+        typename Problem::Base::Graph &g = *problem->graph;
+        const bool can_pull = opt.direction_optimized && g.HasInverse();
+        if (can_pull) GR_TRY(problem->PreparePull());
+
+        PParams P;
+        P.g = g.View();
+        P.ginv = g.InverseView();
+        P.fwd_row_offsets = g.symmetric ? nullptr : g.row_offsets.ptr;
+        for (int i = 0; i < 2; ++i) {
+            P.queues[i] = problem->frontier_queues[i].ptr;
+            P.queue_cap[i] = problem->frontier_elements[i];
+            P.frontier_map[i] = can_pull ? problem->frontier_map[i].ptr : nullptr;
+        }
+        P.visited = problem->visited_mask.ptr;
+        P.candidates = can_pull ? problem->candidates.ptr : nullptr;
+        if (lb_scratch.epoch + 64 >= oprtr::advance::lb::kEpochLimit) {   // keep wraps out of the common case
+            GR_TRY(lb_scratch.tile_desc.Zero(stream));
+            lb_scratch.epoch = 0;
+        }
+        P.scratch.scanned = lb_scratch.scanned.ptr;     P.scratch.row_start = lb_scratch.row_start.ptr;
+        P.scratch.tile_desc = lb_scratch.tile_desc.ptr; P.scratch.part_start = lb_scratch.part_start.ptr;
+        P.scratch.ticket = lb_scratch.ticket.ptr;       P.scratch.part_cap = lb_scratch.part_start.cap;
+        P.scratch.epoch = lb_scratch.epoch;
+        P.slots = work_progress.d_slots.ptr;            // zeroed by ResetBase()
+        P.records = d_records.ptr;
+        P.max_records = opt.record_levels ? kMaxRecords : 0;
+        P.summary = d_summary.ptr;
+        P.src = problem->src;
+        P.do_reset = reset_on_device ? 1 : 0;
+        P.mask_words = (unsigned long long)problem->visited_mask.size;
+        P.src_is_mine = g.part.Mine(problem->src) ? 1 : 0;
+        P.can_pull = can_pull ? 1 : 0;
+        P.traversal_mode = opt.traversal_mode;
+        P.alpha = opt.alpha; P.beta = opt.beta;
+        P.lb_min_edges = opt.lb_min_edges;
+
+        if (!reset_on_device) GR_TRY(d_summary.Zero(stream));
+        DataSlice ds = problem->MakeDataSlice(0);
+        unsigned long long *cursor = reinterpret_cast<unsigned long long *>(d_summary.ptr + 1);
+        unsigned long long desc_words = (unsigned long long)lb_scratch.tile_desc.size;
+        void *kargs[] = {(void *)&ds, (void *)&P, (void *)&cursor, (void *)&desc_words};
+        GR_TRY(cudaLaunchCooperativeKernel((const void *)PersistentEntry(), dim3((unsigned)persistent_grid),
+                                           dim3(AdvancePolicy::THREADS), kargs, 0, stream));
+        enactor_stats.launches = 1;
+        GR_TRY(cudaMemcpyAsync(h_summary.ptr, d_summary.ptr, sizeof(PersistentSummary), cudaMemcpyDeviceToHost, stream));
+        if (opt.record_levels)
+            GR_TRY(cudaMemcpyAsync(h_records.ptr, d_records.ptr, sizeof(DeviceLevelRecord) * kMaxRecords,
+                                   cudaMemcpyDeviceToHost, stream));
+        GR_TRY(cudaStreamSynchronize(stream));
+        const PersistentSummary &sum = h_summary.ptr[0];
+        lb_scratch.epoch += (unsigned)sum.lb_calls;
+        if (lb_scratch.epoch >= oprtr::advance::lb::kEpochLimit) {           // the kernel wrapped on its own
+            GR_TRY(lb_scratch.tile_desc.Zero(stream));
+            lb_scratch.epoch = 0;
+        }
+        enactor_stats.iteration = (long long)sum.levels;
+        enactor_stats.total_queued = sum.total_queued;
+        enactor_stats.edges_inspected = sum.edges_inspected;
+        enactor_stats.algo_bytes = sum.algo_bytes;
+        enactor_stats.push_levels = (int)sum.push_levels;
+        enactor_stats.pull_levels = (int)sum.pull_levels;
+        edges_visited = sum.edges_visited;
+        if (opt.record_levels) {
+            const int cnt = (int)(sum.levels < (unsigned long long)kMaxRecords ? sum.levels : kMaxRecords);
+            for (int i = 0; i < cnt; ++i) {
+                const DeviceLevelRecord &d = h_records.ptr[i];
+                LevelRecord r;
+                r.level = d.level; r.pull = d.kind; r.frontier = d.frontier; r.edges = d.edges;
+                r.discovered = d.discovered; r.candidates = d.candidates; r.ms = (float)((double)d.ns * 1e-6);
+                levels.push_back(r);
+            }
+        }
+        if (sum.overflow)
+            return util::GRError(cudaErrorInvalidConfiguration,
+                                 "frontier queue overflow: increase queue_size", __FILE__, __LINE__);
+        return cudaSuccess;
     }
 
     // ---- normal mode: fused advance + filter, optional direction optimisation -----------------

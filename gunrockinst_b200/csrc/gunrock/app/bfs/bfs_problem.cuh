@@ -133,11 +133,14 @@ struct BFSProblem : ProblemBase<_VertexId, _SizeT> {
 
     // reference: BFSProblem::Reset (bfs_problem.cuh:272-357): labels <- -1, preds <- -2,
     // mask <- 0, queue[0] = {src}, labels[src] = 0, preds[src] = -1
-    cudaError_t Reset(VertexId source, FrontierType ftype, double queue_sizing)
+    // on_device: only size the queues and note the source; the persistent BFS kernel performs the
+    // fills below itself (bfs_persistent.cuh), which spares ~8 API calls and a host sync per search
+    cudaError_t Reset(VertexId source, FrontierType ftype, double queue_sizing, bool on_device = false)
     {
         cudaStream_t s = this->stream;
         GR_TRY(Base::ResetBase(ftype, queue_sizing));
         src = source;
+        if (on_device) { src_degree = 0; return cudaSuccess; }
         const long long ln = this->graph->local_nodes;
         if (ln) GR_TRY(cudaMemsetAsync(labels.ptr, 0xff, sizeof(VertexId) * (size_t)ln, s));
         if (MARK_PREDECESSORS) GR_TRY(util::Fill(preds.ptr, (VertexId)-2, (unsigned long long)ln, s));

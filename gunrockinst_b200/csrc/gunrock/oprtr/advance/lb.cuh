@@ -97,75 +97,94 @@ __device__ __forceinline__ unsigned long long LookbackExclusive(
 // ---------------------------------------------------------------------------------
 // kernel 1: degrees + exclusive scan + merge-path split points
 // ---------------------------------------------------------------------------------
+template <int T>
+struct ScanStorage {
+    unsigned long long warp[T / 32 + 1];
+    unsigned long long prefix;
+    unsigned           ticket;
+};
+
+// Scans tiles of T*R frontier items, handed out by ticket.  `loop` = keep drawing tickets until the
+// frontier is exhausted (persistent callers); otherwise exactly one ticket per CTA (the stand-alone
+// kernel, whose grid is sized from the host-known length).
+template <typename Policy, int T, int R>
+__device__ __forceinline__ void ScanTiles(
+    const Args<typename Policy::VertexId, typename Policy::SizeT> &args,
+    const LbScratchView<typename Policy::SizeT> &scratch,
+    ScanStorage<T> &sm, unsigned long long in_len, LevelCounters *slot_out, bool loop)
+{
+    typedef typename Policy::VertexId VertexId;
+    typedef typename Policy::SizeT    SizeT;
+    typedef unsigned long long        ScanT;
+    constexpr int TILE = T * R;
+    constexpr unsigned long long TILE_EDGES = Policy::TILE_EDGES;
+
+    do {
+        __syncthreads();                    // sm.ticket / sm.prefix of the previous round are consumed
+        if (threadIdx.x == 0) sm.ticket = atomicAdd(scratch.ticket, 1u);
+        __syncthreads();
+        const long long tile = sm.ticket;
+        const unsigned long long base = (unsigned long long)tile * TILE;
+        if (base >= in_len) {
+            // surplus ticket; an empty frontier still has to publish a zero total so that the
+            // expand step sees no work
+            if (in_len == 0 && tile == 0 && threadIdx.x == 0) { scratch.scanned[0] = 0; slot_out->scan_total = 0; }
+            return;
+        }
+
+        ScanT deg[R], excl[R];
+        SizeT first[R];
+        ScanT running = 0;
+#pragma unroll
+        for (int r = 0; r < R; ++r) {
+            unsigned long long i = base + (unsigned long long)r * T + threadIdx.x;
+            deg[r] = 0; first[r] = 0;
+            if (i < in_len) {
+                VertexId v = args.in_queue ? util::LoadCG(args.in_queue + i) : (VertexId)args.g.part.Global((long long)i);
+                if (v >= 0 && (long long)v < args.g.nodes) {
+                    long long row = args.g.part.Local(v);
+                    SizeT a = args.g.row_offsets[row], b = args.g.row_offsets[row + 1];
+                    first[r] = a; deg[r] = (ScanT)(b - a);
+                }
+            }
+            ScanT total;
+            excl[r] = running + util::BlockExclusiveSum<T>(deg[r], sm.warp, total);
+            running += total;
+        }
+        if (util::WarpId() == 0) {
+            ScanT p = LookbackExclusive(scratch.tile_desc, scratch.epoch, tile, running);
+            if (util::LaneId() == 0) sm.prefix = p;
+        }
+        __syncthreads();
+        const ScanT prefix = sm.prefix;
+#pragma unroll
+        for (int r = 0; r < R; ++r) {
+            unsigned long long i = base + (unsigned long long)r * T + threadIdx.x;
+            if (i < in_len) {
+                ScanT b = prefix + excl[r], e = b + deg[r];
+                scratch.scanned[i]   = b;
+                scratch.row_start[i] = first[r];
+                // this item owns every tile boundary that falls inside [b, e)
+                for (ScanT k = (b + TILE_EDGES - 1) / TILE_EDGES; k * TILE_EDGES < e && k < scratch.part_cap; ++k)
+                    scratch.part_start[k] = (long long)i;
+            }
+        }
+        if (base + TILE >= in_len && threadIdx.x == 0) {
+            scratch.scanned[in_len] = prefix + running;
+            slot_out->scan_total = prefix + running;
+        }
+    } while (loop);
+}
+
 template <typename Policy>
 __global__ void __launch_bounds__(Policy::SCAN_THREADS)
 ScanKernel(Args<typename Policy::VertexId, typename Policy::SizeT> args,
            LbScratchView<typename Policy::SizeT> scratch)
 {
-    typedef typename Policy::VertexId VertexId;
-    typedef typename Policy::SizeT    SizeT;
-    typedef unsigned long long        ScanT;
-    constexpr int T = Policy::SCAN_THREADS, R = Policy::SCAN_ROUNDS, TILE = Policy::SCAN_TILE;
-    constexpr unsigned long long TILE_EDGES = Policy::TILE_EDGES;
-
-    __shared__ ScanT s_warp[T / 32 + 1];
-    __shared__ ScanT s_prefix;
-    __shared__ unsigned s_ticket;
-
+    __shared__ ScanStorage<Policy::SCAN_THREADS> s_scan;
     const unsigned long long in_len = args.d_in_len ? *args.d_in_len : args.in_len;
-    if (threadIdx.x == 0) s_ticket = atomicAdd(scratch.ticket, 1u);
-    __syncthreads();
-    const long long tile = s_ticket;
-    const unsigned long long base = (unsigned long long)tile * TILE;
     LevelCounters *slot_out = args.slots + ((args.queue_index + 1) & 3);
-    if (base >= in_len) {
-        // surplus CTA (grid was sized from an upper bound); an empty frontier still
-        // has to publish a zero total so that the expand kernel sees no work
-        if (in_len == 0 && tile == 0 && threadIdx.x == 0) { scratch.scanned[0] = 0; slot_out->scan_total = 0; }
-        return;
-    }
-
-    ScanT deg[R], excl[R];
-    SizeT first[R];
-    ScanT running = 0;
-#pragma unroll
-    for (int r = 0; r < R; ++r) {
-        unsigned long long i = base + (unsigned long long)r * T + threadIdx.x;
-        deg[r] = 0; first[r] = 0;
-        if (i < in_len) {
-            VertexId v = args.in_queue ? util::LoadStream(args.in_queue + i) : (VertexId)args.g.part.Global((long long)i);
-            if (v >= 0 && (long long)v < args.g.nodes) {
-                long long row = args.g.part.Local(v);
-                SizeT a = args.g.row_offsets[row], b = args.g.row_offsets[row + 1];
-                first[r] = a; deg[r] = (ScanT)(b - a);
-            }
-        }
-        ScanT total;
-        excl[r] = running + util::BlockExclusiveSum<T>(deg[r], s_warp, total);
-        running += total;
-    }
-    if (util::WarpId() == 0) {
-        ScanT p = LookbackExclusive(scratch.tile_desc, scratch.epoch, tile, running);
-        if (util::LaneId() == 0) s_prefix = p;
-    }
-    __syncthreads();
-    const ScanT prefix = s_prefix;
-#pragma unroll
-    for (int r = 0; r < R; ++r) {
-        unsigned long long i = base + (unsigned long long)r * T + threadIdx.x;
-        if (i < in_len) {
-            ScanT b = prefix + excl[r], e = b + deg[r];
-            scratch.scanned[i]   = b;
-            scratch.row_start[i] = first[r];
-            // this item owns every tile boundary that falls inside [b, e)
-            for (ScanT k = (b + TILE_EDGES - 1) / TILE_EDGES; k * TILE_EDGES < e && k < scratch.part_cap; ++k)
-                scratch.part_start[k] = (long long)i;
-        }
-    }
-    if (base + TILE >= in_len && threadIdx.x == 0) {
-        scratch.scanned[in_len] = prefix + running;
-        slot_out->scan_total = prefix + running;
-    }
+    ScanTiles<Policy, Policy::SCAN_THREADS, Policy::SCAN_ROUNDS>(args, scratch, s_scan, in_len, slot_out, false);
 }
 
 // ---------------------------------------------------------------------------------
@@ -204,7 +223,10 @@ __device__ __forceinline__ void ExpandTiles(
     static_assert(32 % (THREADS / 32) == 0, "warps per CTA must divide 32");
 
     const int lane = util::LaneId();
-    const ScanT total = scratch.scanned[in_len];
+    // one load per CTA, not per warp: thousands of warps asking one L2 slice for the same word queue up
+    if (threadIdx.x == 0) sm.red[0] = scratch.scanned[in_len];
+    __syncthreads();
+    const ScanT total = sm.red[0];
     unsigned long long num_tiles = (total + TILE_E - 1) / TILE_E;
     if (num_tiles > scratch.part_cap) {     // a frontier with duplicates expanded past the scratch
         num_tiles = scratch.part_cap;

@@ -30,10 +30,28 @@ namespace oprtr {
 namespace advance {
 namespace twc {
 
+template <typename Policy, bool NEED_SRC>
+struct Storage {
+    typedef typename Policy::VertexId VertexId;
+    typedef typename Policy::SizeT    SizeT;
+    SizeT      gather_pos[Policy::TILE_EDGES];                  // fine-grained gather table: CSR position ...
+    VertexId   gather_src[NEED_SRC ? Policy::TILE_EDGES : 1];   // ... source vertex ...
+    int        gather_in[Policy::TILE_EDGES];                   // ... and thread (frontier slot) of each entry
+    unsigned   warp_tot[Policy::THREADS / 32 + 1];
+    unsigned long long red[Policy::THREADS / 32 + 1];
+    int        owner;
+    long long  cta_begin, cta_end, cta_in;
+    VertexId   cta_src;
+};
+
+// Expands frontier tiles cta, cta + num_ctas, ... (THREADS items each).  Callable from any kernel
+// whose CTAs have Policy::THREADS threads.
 template <typename Policy, typename Problem, typename Functor>
-__global__ void __launch_bounds__(Policy::THREADS, Policy::MIN_CTAS)
-Kernel(const __grid_constant__ typename Problem::DataSlice ds,
-       const __grid_constant__ Args<typename Policy::VertexId, typename Policy::SizeT> args)
+__device__ __forceinline__ void ExpandItems(
+    const typename Problem::DataSlice &ds,
+    const Args<typename Policy::VertexId, typename Policy::SizeT> &args,
+    Storage<Policy, Problem::MARK_PREDECESSORS> &sm,
+    unsigned long long in_len, LevelCounters *slot_out, unsigned cta, unsigned num_ctas)
 {
     typedef typename Policy::VertexId VertexId;
     typedef typename Policy::SizeT    SizeT;
@@ -41,20 +59,6 @@ Kernel(const __grid_constant__ typename Problem::DataSlice ds,
     constexpr int GATHER  = Policy::TILE_EDGES;          // slots of the fine-grained gather table
     constexpr int ROUNDS  = GATHER / THREADS;
     constexpr bool NEED_SRC = Problem::MARK_PREDECESSORS;
-
-    __shared__ long long  s_gather_pos[GATHER];
-    __shared__ VertexId   s_gather_src[NEED_SRC ? GATHER : 1];
-    __shared__ int        s_gather_in[GATHER];
-    __shared__ unsigned   s_warp_tot[THREADS / 32 + 1];
-    __shared__ unsigned long long s_red[THREADS / 32 + 1];
-    __shared__ int        s_owner;
-    __shared__ long long  s_cta_begin, s_cta_end;
-    __shared__ VertexId   s_cta_src;
-    __shared__ long long  s_cta_in;
-
-    const unsigned long long in_len = args.d_in_len ? *args.d_in_len : args.in_len;
-    LevelCounters *slot_out = args.slots + ((args.queue_index + 1) & 3);
-    if (blockIdx.x == 0 && threadIdx.x == 0) ClearFutureSlot(args.slots, args.queue_index);
 
     unsigned long long my_edges = 0, my_out_degree = 0;
     const int lane = util::LaneId();
@@ -97,12 +101,12 @@ Kernel(const __grid_constant__ typename Problem::DataSlice ds,
     };
 
     const unsigned long long num_tiles = (in_len + THREADS - 1) / THREADS;
-    for (unsigned long long tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+    for (unsigned long long tile = cta; tile < num_tiles; tile += num_ctas) {
         const unsigned long long i = tile * THREADS + threadIdx.x;
         VertexId v = -1;
         long long begin = 0, end = 0;
         if (i < in_len) {
-            v = args.in_queue ? util::LoadStream(args.in_queue + i) : (VertexId)args.g.part.Global((long long)i);
+            v = args.in_queue ? util::LoadCG(args.in_queue + i) : (VertexId)args.g.part.Global((long long)i);
             if (v >= 0 && (long long)v < args.g.nodes) {
                 long long row = args.g.part.Local(v);
                 begin = (long long)args.g.row_offsets[row];
@@ -114,20 +118,20 @@ Kernel(const __grid_constant__ typename Problem::DataSlice ds,
         // ---- CTA-cooperative: one long list at a time -------------------------------
         for (;;) {
             __syncthreads();
-            if (threadIdx.x == 0) s_owner = -1;
+            if (threadIdx.x == 0) sm.owner = -1;
             __syncthreads();
-            if (len >= Policy::CTA_THRESHOLD) s_owner = threadIdx.x;
+            if (len >= Policy::CTA_THRESHOLD) sm.owner = threadIdx.x;
             __syncthreads();
-            const int owner = s_owner;
+            const int owner = sm.owner;
             if (owner < 0) break;
             if (owner == (int)threadIdx.x) {
-                s_cta_begin = begin; s_cta_end = end; s_cta_src = v; s_cta_in = (long long)i;
+                sm.cta_begin = begin; sm.cta_end = end; sm.cta_src = v; sm.cta_in = (long long)i;
                 len = 0;
             }
             __syncthreads();
-            const long long cb = s_cta_begin, ce = s_cta_end;
-            const VertexId  cs = s_cta_src;
-            const long long ci = s_cta_in;
+            const long long cb = sm.cta_begin, ce = sm.cta_end;
+            const VertexId  cs = sm.cta_src;
+            const long long ci = sm.cta_in;
             for (long long p = cb; p < ce; p += THREADS)       // uniform trip count
                 visit(p + threadIdx.x < ce, p + threadIdx.x, cs, ci);
         }
@@ -150,14 +154,14 @@ Kernel(const __grid_constant__ typename Problem::DataSlice ds,
         // ---- thread-level: short lists packed through the gather table --------------------
         {
             unsigned total;
-            unsigned excl = util::BlockExclusiveSum<THREADS>((unsigned)len, s_warp_tot, total);
+            unsigned excl = util::BlockExclusiveSum<THREADS>((unsigned)len, sm.warp_tot, total);
             for (unsigned round_base = 0; round_base < total; round_base += GATHER) {
                 for (unsigned k = 0; k < (unsigned)len; ++k) {
                     unsigned slot = excl + k - round_base;         // wraps to huge if below the window
                     if (slot < (unsigned)GATHER) {
-                        s_gather_pos[slot] = begin + k;
-                        s_gather_in[slot]  = threadIdx.x;
-                        if constexpr (NEED_SRC) s_gather_src[slot] = v;
+                        sm.gather_pos[slot] = (SizeT)(begin + k);
+                        sm.gather_in[slot]  = threadIdx.x;
+                        if constexpr (NEED_SRC) sm.gather_src[slot] = v;
                     }
                 }
                 __syncthreads();
@@ -166,17 +170,29 @@ Kernel(const __grid_constant__ typename Problem::DataSlice ds,
                 for (int r = 0; r < ROUNDS; ++r) {
                     const unsigned slot = r * THREADS + threadIdx.x;
                     const bool live = slot < n_round;
-                    long long pos = live ? s_gather_pos[slot] : 0;
-                    VertexId  src = (NEED_SRC && live) ? s_gather_src[slot] : (VertexId)0;
-                    long long in_idx = live ? (long long)(tile * THREADS + s_gather_in[slot]) : 0;
+                    long long pos = live ? (long long)sm.gather_pos[slot] : 0;
+                    VertexId  src = (NEED_SRC && live) ? sm.gather_src[slot] : (VertexId)0;
+                    long long in_idx = live ? (long long)(tile * THREADS + sm.gather_in[slot]) : 0;
                     visit(live, pos, src, in_idx);
                 }
                 __syncthreads();                                // table is rewritten next round
             }
         }
     }
-    BlockAccumulate<THREADS>(my_edges, s_red, &slot_out->edges);
-    if constexpr (Policy::TRACK_OUT_DEGREE) BlockAccumulate<THREADS>(my_out_degree, s_red, &slot_out->out_degree);
+    BlockAccumulate<THREADS>(my_edges, sm.red, &slot_out->edges);
+    if constexpr (Policy::TRACK_OUT_DEGREE) BlockAccumulate<THREADS>(my_out_degree, sm.red, &slot_out->out_degree);
+}
+
+template <typename Policy, typename Problem, typename Functor>
+__global__ void __launch_bounds__(Policy::THREADS, Policy::MIN_CTAS)
+Kernel(const __grid_constant__ typename Problem::DataSlice ds,
+       const __grid_constant__ Args<typename Policy::VertexId, typename Policy::SizeT> args)
+{
+    __shared__ Storage<Policy, Problem::MARK_PREDECESSORS> s_twc;
+    const unsigned long long in_len = args.d_in_len ? *args.d_in_len : args.in_len;
+    LevelCounters *slot_out = args.slots + ((args.queue_index + 1) & 3);
+    if (blockIdx.x == 0 && threadIdx.x == 0) ClearFutureSlot(args.slots, args.queue_index);
+    ExpandItems<Policy, Problem, Functor>(ds, args, s_twc, in_len, slot_out, blockIdx.x, gridDim.x);
 }
 
 }  // namespace twc

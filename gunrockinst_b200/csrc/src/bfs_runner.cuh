@@ -43,6 +43,7 @@ struct BfsRunner : BfsRunnerBase {
             if (cfg->beta > 0) opt.beta = cfg->beta;
             if (cfg->queue_sizing > 0) queue_sizing = cfg->queue_sizing;
             opt.record_levels = cfg->record_levels != 0;
+            opt.host_loop = cfg->host_loop != 0;
         }
         GR_TRY(problem.Init(g, s));
         GR_TRY(cudaEventCreate(&e0)); GR_TRY(cudaEventCreate(&e1)); GR_TRY(cudaEventCreate(&e2));
@@ -54,10 +55,11 @@ struct BfsRunner : BfsRunnerBase {
         using gunrock::app::VERTEX_FRONTIERS;
         using gunrock::app::EDGE_FRONTIERS;
         GR_TRY(cudaEventRecord(e0, stream));
-        GR_TRY(problem.Reset(src, IDEM ? EDGE_FRONTIERS : VERTEX_FRONTIERS, queue_sizing));
+        const bool fused_reset = ready && enactor.FusesReset(src, &problem, opt);
+        GR_TRY(problem.Reset(src, IDEM ? EDGE_FRONTIERS : VERTEX_FRONTIERS, queue_sizing, fused_reset));
         if (!ready) { GR_TRY(enactor.Setup(&problem, stream)); ready = true; }
         GR_TRY(cudaEventRecord(e1, stream));
-        GR_TRY(enactor.Enact(&problem, src, opt));
+        GR_TRY(enactor.Enact(&problem, src, opt, fused_reset));
         GR_TRY(cudaEventRecord(e2, stream));
         GR_TRY(cudaEventSynchronize(e2));
         if (IDEM) GR_TRY(enactor.RecountEdgesVisited(&problem));

@@ -113,7 +113,8 @@ typedef struct {
     double  alpha, beta;          /* <= 0: library defaults                           */
     double  queue_sizing;         /* <= 0: 1.0                                        */
     int32_t record_levels;
-    int32_t reserved;
+    int32_t host_loop;            /* 0: whole level loop in one cooperative kernel; 1: one
+                                     launch set + counter fetch per level, driven by the host */
 } grb_bfs_config;
 
 typedef struct grb_bfs_s *grb_bfs_t;

@@ -66,6 +66,9 @@ MODES = [
     dict(mark_pred=True, direction_optimized=True),
     dict(mark_pred=True, traversal_mode=2),
 ]
+# the non-idempotent modes run as one cooperative kernel by default; the host-driven loop
+# (one launch set + counter fetch per level, the reference's structure) must agree
+MODES += [dict(m, host_loop=True) for m in MODES if not m.get("idempotence")]
 
 
 @pytest.mark.parametrize("mode", MODES, ids=lambda m: ",".join("%s=%s" % kv for kv in m.items()) or "default")
@@ -93,10 +96,12 @@ def test_rmat_scale18_dobfs_and_64bit_offsets(gr, orc):
     for fob in (4, 8):
         g = gr.Graph.from_csr(ro, co, symmetric=True, force_offset_bytes=fob)
         assert g.info.offset_bytes == fob
-        for mode in (dict(direction_optimized=True, record_levels=True), dict(traversal_mode=1), dict()):
+        for mode in (dict(direction_optimized=True, record_levels=True), dict(traversal_mode=1), dict(),
+                     dict(direction_optimized=True, record_levels=True, host_loop=True), dict(host_loop=True)):
             bfs = gr.Bfs(g, **mode)
             labels, _, st = bfs.run(0)
             assert np.array_equal(labels, want)
+            assert st["gpu_launches"] == 1 or mode.get("host_loop")
             if mode.get("direction_optimized"):
                 assert st["pull_levels"] > 0
                 lv = bfs.levels()
@@ -114,7 +119,7 @@ def test_edge_cases(gr, orc):
     n = 3000
     rows = np.arange(n - 1)
     ro, co, _ = orc.coo_to_csr(n, np.concatenate([rows, rows + 1]), np.concatenate([rows + 1, rows]))
-    for mode in (dict(), dict(direction_optimized=True), dict(idempotence=True)):
+    for mode in (dict(), dict(direction_optimized=True), dict(idempotence=True), dict(host_loop=True)):
         g = gr.Graph.from_csr(ro, co, symmetric=True)
         labels, _, st = gr.Bfs(g, **mode).run(0)
         assert np.array_equal(labels, np.arange(n))

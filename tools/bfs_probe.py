@@ -23,7 +23,9 @@ else:
     g = gr.Graph.rmat(scale)
 print("graph: n=%d m=%d built in %.1fs" % (g.nodes, g.edges, time.time() - t0), flush=True)
 PEAK = 6539.5
-for name, mode in [("dobfs", dict(direction_optimized=True)), ("push-auto", dict()), ("push-lb", dict(traversal_mode=1)),
+for name, mode in [("warmup", dict(direction_optimized=True)),
+                   ("dobfs", dict(direction_optimized=True)), ("dobfs-host", dict(direction_optimized=True, host_loop=True)),
+                   ("push-auto", dict()), ("push-host", dict(host_loop=True)), ("push-lb", dict(traversal_mode=1)),
                    ("idempotent", dict(idempotence=True))]:
     bfs = gr.Bfs(g, record_levels=True, **mode)
     best = None
@@ -36,6 +38,6 @@ for name, mode in [("dobfs", dict(direction_optimized=True)), ("push-auto", dict
     print("%-10s %.3f ms  %.2f GTEPS  algo %.1f GB/s (%.1f%% of %.0f)  launches=%d levels=%d/%d inspected=%d" % (
         name, best["elapsed_ms"], gteps, gbs, 100 * gbs / PEAK, PEAK, best["gpu_launches"],
         best["push_levels"], best["pull_levels"], best["edges_inspected"]), flush=True)
-    for lv in bfs.levels():
+    for lv in bfs.levels() if name != "warmup" else []:
         print("   ", json.dumps(lv))
     bfs.close()

@@ -246,15 +246,20 @@ def run_single(args):
     torch.cuda.synchronize()
     clocks.start()
     edges = launches = algo_bytes = 0
+    # the K searches run back to back inside the library (grb_bfs_run_many): every search still
+    # ends with its own stream synchronisation (its summary is read on the host), but no Python
+    # bookkeeping sits between two searches
+    order = [sources[i % len(sources)] for i in range(args.steps)]
     e0.record(stream)
-    for i in range(args.steps):
-        _, _, st = bfs.run(sources[i % len(sources)], want_labels=False)
-        edges += st["edges_visited"]
-        launches += st["gpu_launches"]
-        algo_bytes += st["algo_bytes"]
+    stats = bfs.run_many(order)
     e1.record(stream)
     torch.cuda.synchronize()
     clocks.stop()
+    enact_ms = sum(st["elapsed_ms"] + st["reset_ms"] for st in stats) / max(len(stats), 1)
+    for st in stats:
+        edges += st["edges_visited"]
+        launches += st["gpu_launches"]
+        algo_bytes += st["algo_bytes"]
     ms = e0.elapsed_time(e1)
     value = edges / (ms * 1e-3) / 1e9
 
@@ -333,7 +338,7 @@ def run_single(args):
         "dtype": "int32", "data": "synthetic", "config": workload_config(args, scale, n, m),
         "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": launches,
         "clocks": clocks.summary(), "parity_vs_oracle": parity,
-        "graph500_gteps": value / 2.0, "setup_s": round(time.time() - t_setup, 1),
+        "graph500_gteps": value / 2.0, "device_ms_per_search": enact_ms, "setup_s": round(time.time() - t_setup, 1),
     }
     bfs.close()
     g.close()

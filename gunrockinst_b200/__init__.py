@@ -147,6 +147,13 @@ class Bfs:
                     "grb_bfs_run")
         return labels, preds, st.as_dict()
 
+    def run_many(self, sources):
+        """One search per source, back to back inside the library; -> list of stats dicts."""
+        srcs = np.ascontiguousarray(sources, dtype=np.int32)
+        st = (Stats * max(srcs.size, 1))()
+        _capi.check(_capi.lib().grb_bfs_run_many(self._h, _ptr(srcs), int(srcs.size), st), "grb_bfs_run_many")
+        return [st[i].as_dict() for i in range(srcs.size)]
+
     def device_labels(self):
         p = C.c_void_p()
         _capi.check(_capi.lib().grb_bfs_device_labels(self._h, C.byref(p)), "grb_bfs_device_labels")
@@ -160,7 +167,7 @@ class Bfs:
         _capi.check(L.grb_bfs_levels(self._h, arr, cnt.value, C.byref(cnt)), "grb_bfs_levels")
         kinds = {0: "push-twc", 1: "pull", 2: "push-lb"}
         return [dict(level=r.level, kind=kinds.get(r.kind, str(r.kind)), frontier=r.frontier, edges=r.edges,
-                     discovered=r.discovered, candidates=r.candidates, ms=r.ms) for r in arr[:cnt.value]]
+                     discovered=r.discovered, candidates=r.candidates, ms=r.ms, switch_ms=r.switch_ms) for r in arr[:cnt.value]]
 
     def close(self):
         if self._h:

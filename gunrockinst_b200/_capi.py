@@ -51,7 +51,7 @@ class Stats(C.Structure):
 class LevelRecord(C.Structure):
     _fields_ = [("level", C.c_int32), ("kind", C.c_int32),
                 ("frontier", C.c_uint64), ("edges", C.c_uint64), ("discovered", C.c_uint64),
-                ("candidates", C.c_uint64), ("ms", C.c_float), ("pad", C.c_float)]
+                ("candidates", C.c_uint64), ("ms", C.c_float), ("switch_ms", C.c_float)]
 
 
 class BfsConfig(C.Structure):
@@ -125,6 +125,7 @@ def lib():
     sig("grb_graph_destroy", None, [p])
     sig("grb_bfs_create", C.c_int, [p, C.POINTER(BfsConfig), pp])
     sig("grb_bfs_run", C.c_int, [p, i32, p, p, C.POINTER(Stats)])
+    sig("grb_bfs_run_many", C.c_int, [p, p, i32, C.POINTER(Stats)])
     sig("grb_bfs_device_labels", C.c_int, [p, pp])
     sig("grb_bfs_levels", C.c_int, [p, C.POINTER(LevelRecord), i32, C.POINTER(i32)])
     sig("grb_bfs_destroy", None, [p])

@@ -102,6 +102,7 @@ struct LevelRecord {
     int level; int pull;                 // pull: 0 push-TWC, 1 pull, 2 push-LB
     unsigned long long frontier, edges, discovered, candidates;
     float ms;
+    float switch_ms;                     // part of ms spent converting queue <-> bitmap (persistent loop)
 };
 
 template <typename Problem>
@@ -265,6 +266,7 @@ class BFSEnactor : public EnactorBase {
         }
         P.visited = problem->visited_mask.ptr;
         P.candidates = can_pull ? problem->candidates.ptr : nullptr;
+        P.head = can_pull ? problem->head.ptr : nullptr;
         if (lb_scratch.epoch + 64 >= oprtr::advance::lb::kEpochLimit) {   // keep wraps out of the common case
             GR_TRY(lb_scratch.tile_desc.Zero(stream));
             lb_scratch.epoch = 0;
@@ -319,6 +321,7 @@ class BFSEnactor : public EnactorBase {
                 LevelRecord r;
                 r.level = d.level; r.pull = d.kind; r.frontier = d.frontier; r.edges = d.edges;
                 r.discovered = d.discovered; r.candidates = d.candidates; r.ms = (float)((double)d.ns * 1e-6);
+                r.switch_ms = (float)((double)d.ns_switch * 1e-6);
                 levels.push_back(r);
             }
         }
@@ -391,6 +394,7 @@ class BFSEnactor : public EnactorBase {
                 pa.frontier_out = problem->frontier_map[cur_map ^ 1].ptr;
                 pa.visited      = problem->visited_mask.ptr;
                 pa.candidates   = problem->candidates.ptr;
+                pa.head         = problem->head.ptr;
                 pa.fwd_row_offsets = g.symmetric ? nullptr : g.row_offsets.ptr;
                 pa.out_queue = nullptr; pa.out_cap = 0;
                 pa.slots = work_progress.d_slots.ptr;
@@ -419,6 +423,7 @@ class BFSEnactor : public EnactorBase {
                 LevelRecord r;
                 r.level = level; r.pull = kind; r.frontier = F; r.edges = E; r.discovered = D; r.candidates = c.aux0;
                 GR_TRY(cudaEventElapsedTime(&r.ms, ev_a, ev_b));
+                r.switch_ms = 0;
                 levels.push_back(r);
             }
             prev_len = F;

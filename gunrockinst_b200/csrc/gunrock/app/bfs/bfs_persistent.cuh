@@ -33,6 +33,7 @@ struct DeviceLevelRecord {
     int level, kind;                                // kind: 0 push-TWC, 1 pull, 2 push-LB
     unsigned long long frontier, edges, discovered, candidates;
     unsigned long long ns;                          // globaltimer span of the level, barriers included
+    unsigned long long ns_switch;                   // ... of which queue <-> bitmap conversion (+ its barrier)
 };
 
 struct PersistentSummary {
@@ -53,6 +54,7 @@ struct PersistentParams {
     unsigned    *frontier_map[2];
     unsigned    *visited;
     const unsigned *candidates;
+    const VertexId *head;
     oprtr::advance::LbScratchView<SizeT> scratch;   // .epoch = first epoch this run may use
     oprtr::LevelCounters *slots;                    // zeroed by the host before the launch
     DeviceLevelRecord    *records;                  // optional trace
@@ -80,7 +82,7 @@ union PersistentStorage {
     oprtr::advance::lb::ExpandStorage<PushPolicy, NEED_SRC> expand;
     oprtr::advance::lb::ScanStorage<PushPolicy::THREADS>    scan;
     oprtr::advance::twc::Storage<PushPolicy, NEED_SRC>      twc;
-    oprtr::advance::pull::SweepStorage<PullPolicy::WARPS>   sweep;
+    oprtr::advance::pull::SweepStorage<PullPolicy>          sweep;
     struct { unsigned warp[PushPolicy::THREADS / 32 + 1]; unsigned long long base; } b2q;
 };
 
@@ -236,6 +238,7 @@ PersistentKernel(const __grid_constant__ typename Problem::DataSlice ds0,
                 pull = false;
             }
         }
+        const unsigned long long t1 = leader ? GlobalTimerNs() : 0ull;
         // ---- one level ------------------------------------------------------------------------------
         oprtr::LevelCounters *slot_out = P.slots + ((qi + 1) & 3);
         if (leader) oprtr::ClearFutureSlot(P.slots, qi);
@@ -275,6 +278,7 @@ PersistentKernel(const __grid_constant__ typename Problem::DataSlice ds0,
             pa.frontier_out = P.frontier_map[cur_map ^ 1];
             pa.visited = P.visited;
             pa.candidates = P.candidates;
+            pa.head = P.head;
             pa.fwd_row_offsets = P.fwd_row_offsets;
             pa.out_queue = nullptr; pa.out_cap = 0;
             pa.slots = P.slots; pa.queue_index = qi; pa.iteration = level;
@@ -302,6 +306,7 @@ PersistentKernel(const __grid_constant__ typename Problem::DataSlice ds0,
             DeviceLevelRecord r;
             r.level = level; r.kind = kind; r.frontier = F; r.edges = E; r.discovered = D; r.candidates = cands;
             r.ns = GlobalTimerNs() - t0;
+            r.ns_switch = t1 - t0;
             P.records[sum.levels] = r;
         }
         ++sum.levels;

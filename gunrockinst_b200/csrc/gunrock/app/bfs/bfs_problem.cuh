@@ -39,6 +39,17 @@ __global__ void MarkCandidatesKernel(const void *offsets, int offset_bytes, long
     }
 }
 
+// head[row] = first entry of the row's (inverse) list, -1 if the row is empty
+template <typename VertexId, typename SizeT>
+__global__ void FillHeadKernel(const SizeT *offsets, const VertexId *cols, long long local_nodes, VertexId *head)
+{
+    const long long stride = (long long)gridDim.x * blockDim.x;
+    for (long long row = (long long)blockIdx.x * blockDim.x + threadIdx.x; row < local_nodes; row += stride) {
+        const SizeT b = offsets[row], e = offsets[row + 1];
+        head[row] = e > b ? cols[b] : (VertexId)-1;
+    }
+}
+
 template <typename _VertexId, typename _SizeT, typename _Value, bool _MARK_PREDECESSORS, bool _ENABLE_IDEMPOTENCE>
 struct BFSProblem : ProblemBase<_VertexId, _SizeT> {
     typedef _VertexId VertexId;
@@ -70,6 +81,7 @@ struct BFSProblem : ProblemBase<_VertexId, _SizeT> {
 
     util::DeviceArray<VertexId> labels, preds;
     util::DeviceArray<unsigned> visited_mask, frontier_map[2], candidates;
+    util::DeviceArray<VertexId> head;                   // pull direction: first in-neighbour of every row
     util::DeviceArray<unsigned> next_map, recv_map;     // partitioned runs only (PrepareExchange)
     bool candidates_valid = false;
     unsigned long long src_degree = 0;
@@ -107,6 +119,11 @@ struct BFSProblem : ProblemBase<_VertexId, _SizeT> {
             auto inv = this->graph->InverseView();
             MarkCandidatesKernel<VertexId><<<util::FillGrid(words * 32), 256, 0, this->stream>>>(
                 (const void *)inv.row_offsets, (int)sizeof(SizeT), this->graph->local_nodes, candidates.ptr);
+            GR_TRY(cudaGetLastError());
+            GR_TRY(head.Allocate((size_t)this->graph->local_nodes + 1));
+            FillHeadKernel<VertexId, SizeT><<<util::FillGrid((unsigned long long)this->graph->local_nodes + 1), 256, 0,
+                                               this->stream>>>(inv.row_offsets, inv.col_indices,
+                                                               this->graph->local_nodes, head.ptr);
             GR_TRY(cudaGetLastError());
             candidates_valid = true;
         }

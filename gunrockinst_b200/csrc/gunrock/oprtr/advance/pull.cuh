@@ -19,18 +19,24 @@
 //                 (byte offsets), so that the walk below runs with dense lanes
 //                 whatever fraction of the chunk is left (late pull levels leave < 1 %);
 //                 a chunk with nothing to do costs two coalesced loads per word;
-//   2. probe   -- every lane takes UNROLL listed vertices at once and issues, for all
-//                 of them, the row-offset pairs, then the first two neighbour ids,
-//                 then the two frontier-bit probes: the dependent chain
-//                 offsets -> neighbour -> bit is three loads deep with 2*UNROLL probes
-//                 in flight per lane (an R-MAT list is sorted, hubs first, so ~90 % of
-//                 the vertices find their parent here);
-//   3. walk    -- the few that did not continue lane-serially with early exit up to
-//                 SERIAL_LIMIT entries; what is left of long lists is finished by the
-//                 whole warp with 128-byte coalesced reads and a ballot early exit, so
-//                 a straggler list cannot serialise a warp;
+//   2. probe   -- phase-wise over the WHOLE list (up to 8 vertices per lane): first all
+//                 row-offset pairs, then all first-neighbour ids, then all frontier-bit
+//                 probes, so the dependent chain offsets -> neighbour -> bit is three
+//                 loads deep for the chunk, not per vertex, with up to 8 independent
+//                 loads in flight per lane in every phase (an R-MAT list is sorted, hubs
+//                 first, so ~90 % of the vertices find their parent at their first entry);
+//   3. walk    -- the vertices that did not are packed into a retry list and continue
+//                 lane-serially with early exit up to SERIAL_LIMIT entries; what is left
+//                 of long lists is finished by the whole warp with 128-byte coalesced
+//                 reads and a ballot early exit, so a straggler list cannot serialise a warp;
 //   4. publish -- found vertices are OR-ed into a per-warp word buffer in shared memory
 //                 and leave as whole-word stores (frontier_out, visited), no global atomics.
+//
+// Optional `head` array (first entry of every row, 4 bytes per vertex, built once per graph):
+// a sorted R-MAT list starts with its lowest-numbered, i.e. highest-degree, neighbour, so nine
+// vertices out of ten find their parent there; reading that entry from a dense array instead
+// of col_indices[row_offsets[v]] replaces one 128-byte line (and one 32-byte DRAM sector) per
+// vertex by coalesced reads of consecutive rows.
 //
 // Algorithmic HBM bytes per call: n/8 (visited) [+ n/8 candidates] + n/8
 // (frontier_out) for the sweep, 2*sizeof(SizeT) per unvisited candidate, 4 + 1
@@ -51,6 +57,7 @@ struct PullArgs {
     unsigned       *frontier_out;           // global bitmap; this device writes its own words
     unsigned       *visited;                // global bitmap; this device updates its own words
     const unsigned *candidates;             // optional, local words: 1 = vertex has in-edges
+    const VertexId *head;                   // optional, per local row: first entry of its list (-1: empty)
     const SizeT    *fwd_row_offsets;        // forward (out-edge) offsets for the degree sum; NULL: use g
     VertexId       *out_queue;              // optional: also enqueue found vertices
     unsigned long long out_cap;
@@ -62,12 +69,17 @@ struct PullArgs {
 
 constexpr int kChunkWords = 8;                  // bitmap words a warp sweeps at a time
 constexpr int kChunkVerts = kChunkWords * 32;   // ... = 256 vertices, so list entries fit a byte
+constexpr int kChunkPerLane = kChunkVerts / 32;
 
-template <int WARPS>
+template <typename Policy>
 struct SweepStorage {
-    unsigned char      cand[WARPS][kChunkVerts];    // per warp: positions of the chunk's vertices still to do
-    unsigned           found[WARPS][kChunkWords];   // per warp: discoveries of the chunk, one bit each
-    unsigned long long red[WARPS + 1];
+    typedef typename Policy::SizeT SizeT;
+    SizeT              begin[Policy::WARPS][kChunkVerts];   // per listed vertex: first entry of its list ...
+    unsigned           deg[Policy::WARPS][kChunkVerts];     // ... and its length (clamped to 2^31 - 1)
+    unsigned char      cand[Policy::WARPS][kChunkVerts];    // per warp: positions of the chunk's vertices still to do
+    unsigned char      retry[Policy::WARPS][kChunkVerts];   // list slots whose first entry was not in the frontier
+    unsigned           found[Policy::WARPS][kChunkWords];   // per warp: discoveries of the chunk, one bit each
+    unsigned long long red[Policy::WARPS + 1];
 };
 
 // The sweep itself, callable from any kernel whose CTAs have Policy::THREADS threads:
@@ -77,13 +89,13 @@ template <typename Policy, typename Problem, typename Functor>
 __device__ __forceinline__ void Sweep(
     const typename Problem::DataSlice &ds,
     const PullArgs<typename Policy::VertexId, typename Policy::SizeT> &args,
-    SweepStorage<Policy::WARPS> &sm, LevelCounters *slot_out,
+    SweepStorage<Policy> &sm, LevelCounters *slot_out,
     long long first_chunk, long long chunk_stride)
 {
     typedef typename Policy::VertexId VertexId;
     typedef typename Policy::SizeT    SizeT;
     constexpr int THREADS = Policy::THREADS;
-    constexpr int SERIAL_LIMIT = 8, U = 2;
+    constexpr int SERIAL_LIMIT = 8, U = kChunkPerLane;
     constexpr bool NEED_SRC = Problem::MARK_PREDECESSORS;
 
     const int lane = util::LaneId();
@@ -93,10 +105,32 @@ __device__ __forceinline__ void Sweep(
     // first word of this device's segment inside the global bitmaps
     const long long seg = ((long long)args.g.part.rank * local_nodes) >> 5;
     unsigned char *s_cand  = sm.cand[util::WarpId()];
+    unsigned char *s_retry = sm.retry[util::WarpId()];
+    SizeT         *s_begin = sm.begin[util::WarpId()];
+    unsigned      *s_deg   = sm.deg[util::WarpId()];
     unsigned      *s_found = sm.found[util::WarpId()];
     const int my_word = lane >> 2, my_shift = (lane & 3) << 3;     // lane -> byte (lane & 3) of word (lane >> 2)
 
     unsigned long long my_edges = 0, my_found = 0, my_degree = 0, my_cands = 0;
+
+    // functor + publication of one found vertex (list slot idx of the current chunk)
+    auto publish = [&](long long w0, unsigned idx, VertexId parent, long long epos) {
+        const unsigned off = s_cand[idx];
+        const long long row = (w0 << 5) + off;
+        const VertexId child = (VertexId)args.g.part.Global(row);
+        const VertexId s_id = NEED_SRC ? parent : (VertexId)args.iteration;
+        if (!VisitEdge<Policy, Problem, Functor>(&ds, s_id, child, (SizeT)epos, (SizeT)row)) return;
+        atomicOr(s_found + (off >> 5), 1u << (off & 31));
+        if (args.fwd_row_offsets)
+            my_degree += (unsigned long long)(args.fwd_row_offsets[row + 1] - args.fwd_row_offsets[row]);
+        else
+            my_degree += s_deg[idx];
+        if (args.out_queue) {
+            const unsigned long long at = atomicAdd(&slot_out->out_len, 1ull);
+            if (at < args.out_cap) args.out_queue[at] = child;
+            else slot_out->overflow = 1;
+        }
+    };
 
     for (long long c = first_chunk; c < num_chunks; c += chunk_stride) {
         // ---- 1. scan ---------------------------------------------------------------------------
@@ -125,116 +159,104 @@ __device__ __forceinline__ void Sweep(
         __syncwarp();
         my_cands += cnt;
 
-        for (unsigned k0 = 0; k0 < total; k0 += 32 * U) {
-            // ---- 2. probe: offsets, then two neighbours, then two frontier bits, UNROLL vertices per lane
-            bool      act[U], found[U];
-            unsigned  off[U];
-            long long begin[U], end[U], epos[U];
-            VertexId  parent[U];
+        // ---- 2. probe, phase by phase over the whole list -------------------------------------------
+        // (u * 32 < total is warp-uniform: unused phases of a short list are skipped)
 #pragma unroll
-            for (int u = 0; u < U; ++u) {
-                const unsigned idx = k0 + u * 32 + lane;
-                act[u] = idx < total;
-                off[u] = act[u] ? (unsigned)s_cand[idx] : 0u;
-                begin[u] = end[u] = 0;
-                if (act[u]) {
-                    const long long row = (w0 << 5) + off[u];
-                    begin[u] = (long long)args.g.row_offsets[row];
-                    end[u]   = (long long)args.g.row_offsets[row + 1];
-                }
+        for (int u = 0; u < U; ++u) {
+            const unsigned idx = u * 32 + lane;
+            if (u * 32 < total && idx < total) {
+                const long long row = (w0 << 5) + s_cand[idx];
+                const SizeT b = args.g.row_offsets[row], e = args.g.row_offsets[row + 1];
+                s_begin[idx] = b;
+                const unsigned long long d = (unsigned long long)(e - b);
+                s_deg[idx] = d > 0x7fffffffull ? 0x7fffffffu : (unsigned)d;
             }
-            VertexId n0[U], n1[U];
+        }
+        VertexId n0[U];
 #pragma unroll
-            for (int u = 0; u < U; ++u) {
-                n0[u] = (begin[u]     < end[u]) ? util::LoadStream(args.g.col_indices + begin[u])     : (VertexId)-1;
-                n1[u] = (begin[u] + 1 < end[u]) ? util::LoadStream(args.g.col_indices + begin[u] + 1) : (VertexId)-1;
+        for (int u = 0; u < U; ++u) {
+            const unsigned idx = u * 32 + lane;
+            n0[u] = -1;
+            if (u * 32 < total && idx < total && s_deg[idx] != 0) {
+                // the dense head array turns this gather (one 128-byte line per vertex) into a
+                // coalesced read of consecutive rows
+                if (args.head) n0[u] = util::LoadStream(args.head + ((w0 << 5) + s_cand[idx]));
+                else           n0[u] = util::LoadStream(args.g.col_indices + s_begin[idx]);
             }
-            bool h0[U], h1[U];
+        }
+        unsigned hits = 0;
 #pragma unroll
-            for (int u = 0; u < U; ++u) {
-                h0[u] = n0[u] >= 0 && util::BitTest(args.frontier_in, ds.BitPos(n0[u]));
-                h1[u] = n1[u] >= 0 && util::BitTest(args.frontier_in, ds.BitPos(n1[u]));
+        for (int u = 0; u < U; ++u) {
+            if (u * 32 < total && n0[u] >= 0) {
+                ++my_edges;
+                if (util::BitTest(args.frontier_in, ds.BitPos(n0[u]))) hits |= 1u << u;
             }
+        }
+        unsigned n_retry = 0;
 #pragma unroll
-            for (int u = 0; u < U; ++u) {
-                found[u] = h0[u] || h1[u];
-                parent[u] = h0[u] ? n0[u] : n1[u];
-                epos[u] = h0[u] ? begin[u] : begin[u] + 1;
-                // entries an early-exit walk would have looked at
-                my_edges += h0[u] ? 1u : (unsigned)(n0[u] >= 0) + (unsigned)(n1[u] >= 0);
-            }
-            // ---- 3. walk what is left --------------------------------------------------------------
-#pragma unroll
-            for (int u = 0; u < U; ++u) {
-                long long k = begin[u] + 2;
-                if (act[u] && !found[u] && k < end[u]) {
-                    const long long lim = (end[u] - begin[u] > SERIAL_LIMIT) ? begin[u] + SERIAL_LIMIT : end[u];
-                    const long long k_first = k;
-                    while (k < lim) {
-                        const VertexId x = util::LoadStream(args.g.col_indices + k);
-                        if (util::BitTest(args.frontier_in, ds.BitPos(x))) { found[u] = true; parent[u] = x; epos[u] = k; ++k; break; }
-                        ++k;
-                    }
-                    my_edges += (unsigned long long)(k - k_first);
-                }
-                unsigned rest = __ballot_sync(util::kFullMask, act[u] && !found[u] && k < end[u]);
-                while (rest) {
-                    const int leader = __ffs(rest) - 1;
-                    rest &= rest - 1;
-                    const long long wb = __shfl_sync(util::kFullMask, k, leader);
-                    const long long we = __shfl_sync(util::kFullMask, end[u], leader);
-                    for (long long p = wb; p < we; p += 32) {
-                        const long long idx = p + lane;
-                        VertexId x = -1;
-                        bool hit = false;
-                        if (idx < we) {
-                            x = util::LoadStream(args.g.col_indices + idx);
-                            hit = util::BitTest(args.frontier_in, ds.BitPos(x));
-                            ++my_edges;
-                        }
-                        const unsigned hm = __ballot_sync(util::kFullMask, hit);
-                        if (hm) {
-                            const int first = __ffs(hm) - 1;
-                            const VertexId px = __shfl_sync(util::kFullMask, x, first);
-                            if (lane == leader) { found[u] = true; parent[u] = px; epos[u] = p + first; }
-                            break;
-                        }
-                    }
-                }
-            }
-            // ---- 4. functor + publication ----------------------------------------------------------
-#pragma unroll
-            for (int u = 0; u < U; ++u) {
-                const long long row = (w0 << 5) + off[u];
-                const VertexId child = (VertexId)args.g.part.Global(row);
-                if (found[u]) {
-                    const VertexId s_id = NEED_SRC ? parent[u] : (VertexId)args.iteration;
-                    found[u] = VisitEdge<Policy, Problem, Functor>(&ds, s_id, child, (SizeT)epos[u], (SizeT)row);
-                }
-                if (found[u]) {
-                    atomicOr(s_found + (off[u] >> 5), 1u << (off[u] & 31));
-                    if (args.fwd_row_offsets)
-                        my_degree += (unsigned long long)(args.fwd_row_offsets[row + 1] - args.fwd_row_offsets[row]);
-                    else
-                        my_degree += (unsigned long long)(end[u] - begin[u]);
-                }
-                if (args.out_queue) {
-                    const unsigned fm = __ballot_sync(util::kFullMask, found[u]);
-                    if (fm) {
-                        unsigned long long b = 0;
-                        if (lane == 0) b = atomicAdd(&slot_out->out_len, (unsigned long long)__popc(fm));
-                        b = __shfl_sync(util::kFullMask, b, 0);
-                        if (found[u]) {
-                            const unsigned long long at = b + __popc(fm & ((1u << lane) - 1));
-                            if (at < args.out_cap) args.out_queue[at] = child;
-                            else slot_out->overflow = 1;
-                        }
-                    }
-                }
+        for (int u = 0; u < U; ++u) {
+            if (u * 32 < total) {                               // uniform
+                const unsigned idx = u * 32 + lane;
+                const bool hit = (hits >> u) & 1u;
+                if (hit) publish(w0, idx, n0[u], (long long)s_begin[idx]);
+                const bool again = !hit && idx < total && s_deg[idx] > 1;
+                const unsigned am = __ballot_sync(util::kFullMask, again);
+                if (again) s_retry[n_retry + __popc(am & ((1u << lane) - 1))] = (unsigned char)idx;
+                n_retry += (unsigned)__popc(am);
             }
         }
         __syncwarp();
-        // whole-word publication: lane l < CHUNK_WORDS owns word w0 + l (its visited word sits in lane 4l)
+        // ---- 3. walk what is left ------------------------------------------------------------------
+        for (unsigned k0 = 0; k0 < n_retry; k0 += 32) {
+            const bool act = k0 + lane < n_retry;
+            const unsigned idx = act ? (unsigned)s_retry[k0 + lane] : 0u;
+            long long begin = 0, end = 0, k = 0, epos = 0;
+            bool found = false;
+            VertexId parent = -1;
+            if (act) {
+                begin = (long long)s_begin[idx];
+                end = begin + (long long)s_deg[idx];
+                if (s_deg[idx] == 0x7fffffffu) {                // clamped: re-read the true end
+                    const long long row = (w0 << 5) + s_cand[idx];
+                    end = (long long)args.g.row_offsets[row + 1];
+                }
+                k = begin + 1;
+                const long long lim = (end - begin > SERIAL_LIMIT) ? begin + SERIAL_LIMIT : end;
+                while (k < lim) {
+                    const VertexId x = util::LoadStream(args.g.col_indices + k);
+                    if (util::BitTest(args.frontier_in, ds.BitPos(x))) { found = true; parent = x; epos = k; ++k; break; }
+                    ++k;
+                }
+                my_edges += (unsigned long long)(k - begin - 1);
+            }
+            unsigned rest = __ballot_sync(util::kFullMask, act && !found && k < end);
+            while (rest) {
+                const int leader = __ffs(rest) - 1;
+                rest &= rest - 1;
+                const long long wb = __shfl_sync(util::kFullMask, k, leader);
+                const long long we = __shfl_sync(util::kFullMask, end, leader);
+                for (long long p = wb; p < we; p += 32) {
+                    const long long at = p + lane;
+                    VertexId x = -1;
+                    bool hit = false;
+                    if (at < we) {
+                        x = util::LoadStream(args.g.col_indices + at);
+                        hit = util::BitTest(args.frontier_in, ds.BitPos(x));
+                        ++my_edges;
+                    }
+                    const unsigned hm = __ballot_sync(util::kFullMask, hit);
+                    if (hm) {
+                        const int first = __ffs(hm) - 1;
+                        const VertexId px = __shfl_sync(util::kFullMask, x, first);
+                        if (lane == leader) { found = true; parent = px; epos = p + first; }
+                        break;
+                    }
+                }
+            }
+            if (found) publish(w0, idx, parent, epos);
+        }
+        __syncwarp();
+        // ---- 4. whole-word publication: lane l < CHUNK_WORDS owns word w0 + l (its visited word sits in lane 4l)
         const unsigned vis_l = __shfl_sync(util::kFullMask, vis, (lane & (kChunkWords - 1)) << 2);
         if (lane < kChunkWords && w0 + lane < num_words) {
             const unsigned fm = s_found[lane];
@@ -256,7 +278,7 @@ __global__ void __launch_bounds__(Policy::THREADS, Policy::MIN_CTAS)
 Kernel(const __grid_constant__ typename Problem::DataSlice ds,
        const __grid_constant__ PullArgs<typename Policy::VertexId, typename Policy::SizeT> args)
 {
-    __shared__ SweepStorage<Policy::WARPS> s_sweep;
+    __shared__ SweepStorage<Policy> s_sweep;
     LevelCounters *slot_out = args.slots + ((args.queue_index + 1) & 3);
     if (blockIdx.x == 0 && threadIdx.x == 0) ClearFutureSlot(args.slots, args.queue_index);
     Sweep<Policy, Problem, Functor>(ds, args, s_sweep, slot_out,

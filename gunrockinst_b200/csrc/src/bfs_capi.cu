@@ -35,6 +35,15 @@ extern "C" int grb_bfs_run(grb_bfs_t ctx, int32_t src, int32_t *labels_host, int
     return 0;
 }
 
+extern "C" int grb_bfs_run_many(grb_bfs_t ctx, const int32_t *srcs, int32_t count, grb_stats *stats)
+{
+    if (!ctx || (!srcs && count > 0)) return (int)cudaErrorInvalidValue;
+    GRB_TRY(cudaSetDevice(ctx->graph->device()));
+    for (int32_t i = 0; i < count; ++i)
+        GRB_TRY(ctx->runner->Run(srcs[i], nullptr, nullptr, stats ? stats + i : nullptr));
+    return 0;
+}
+
 extern "C" int grb_bfs_device_labels(grb_bfs_t ctx, void **labels_dev)
 {
     if (!ctx || !labels_dev) return (int)cudaErrorInvalidValue;
@@ -50,7 +59,7 @@ extern "C" int grb_bfs_levels(grb_bfs_t ctx, grb_level_record *out, int32_t cap,
     for (int i = 0; i < (int)lv.size() && i < cap && out; ++i) {
         out[i].level = lv[i].level; out[i].kind = lv[i].pull; out[i].frontier = lv[i].frontier;
         out[i].edges = lv[i].edges; out[i].discovered = lv[i].discovered; out[i].candidates = lv[i].candidates;
-        out[i].ms = lv[i].ms; out[i].pad = 0;
+        out[i].ms = lv[i].ms; out[i].switch_ms = lv[i].switch_ms;
     }
     return 0;
 }

@@ -99,7 +99,7 @@ typedef struct {
     int32_t  kind;              /* 0 push-TWC, 1 pull, 2 push-LB                     */
     uint64_t frontier, edges, discovered, candidates;
     float    ms;
-    float    pad;
+    float    switch_ms;         /* part of ms spent converting queue <-> bitmap        */
 } grb_level_record;
 
 /* ---- BFS ----------------------------------------------------------------------
@@ -122,6 +122,9 @@ typedef struct grb_bfs_s *grb_bfs_t;
 int  grb_bfs_create(grb_graph_t g, const grb_bfs_config *cfg, grb_bfs_t *out);
 /* labels_host / preds_host may be NULL (results stay on the device) */
 int  grb_bfs_run(grb_bfs_t ctx, int32_t src, int32_t *labels_host, int32_t *preds_host, grb_stats *stats);
+/* `count` searches back to back inside the library (no caller code between two searches);
+ * stats[i] (optional) receives the i-th search's statistics, labels stay on the device */
+int  grb_bfs_run_many(grb_bfs_t ctx, const int32_t *srcs, int32_t count, grb_stats *stats);
 int  grb_bfs_device_labels(grb_bfs_t ctx, void **labels_dev);
 int  grb_bfs_levels(grb_bfs_t ctx, grb_level_record *out, int32_t cap, int32_t *count);
 void grb_bfs_destroy(grb_bfs_t ctx);

@@ -213,6 +213,29 @@ def pagerank(graph, src=-1, delta=0.85, threshold=1e-6, max_iter=1000, want_sort
     return ranks, ((ids, sr) if want_sorted else None), st.as_dict()
 
 
+def bc(graph, src=-1, want_sigmas=False):
+    """Betweenness centrality -> (bc float32[n] (x0.5; src < 0: every source), sigmas or None, stats)."""
+    n = graph.local_nodes
+    vals = np.empty(max(n, 1), dtype=np.float32)
+    sig = np.empty(max(n, 1), dtype=np.float32) if want_sigmas else None
+    st = Stats()
+    _capi.check(_capi.lib().grb_bc(graph._h, int(src), _ptr(vals), _ptr(sig), None, C.byref(st)), "grb_bc")
+    return vals[:n], (sig[:n] if want_sigmas else None), st.as_dict()
+
+
+def topk(row_offsets, col_offsets, top_nodes, device=0):
+    """Top-k degree centrality from the offsets of a graph and of its transpose
+    -> (node_ids, in_degrees, out_degrees), int32[min(k, n)] each."""
+    ro = np.ascontiguousarray(row_offsets, dtype=np.int32)
+    ci = np.ascontiguousarray(col_offsets, dtype=np.int32)
+    n = ro.size - 1
+    k = max(min(int(top_nodes), n), 0)
+    ids, ind, outd = (np.empty(max(k, 1), dtype=np.int32) for _ in range(3))
+    _capi.check(_capi.lib().grb_topk(device, n, _ptr(ro), _ptr(ci), int(top_nodes), _ptr(ids), _ptr(ind),
+                                     _ptr(outd), None), "grb_topk")
+    return ids[:k], ind[:k], outd[:k]
+
+
 # ---- the reference's C API, argument for argument ---------------------------------------
 def _gunrock_graph(row_offsets, col_indices, edge_values=None):
     ro = np.ascontiguousarray(row_offsets, dtype=np.int32)
@@ -267,6 +290,38 @@ def gunrock_cc_func(row_offsets, col_indices, **cfg):
     dt = _capi.GunrockDataType(_capi.VTXID_INT, _capi.SIZET_INT, _capi.VALUE_INT)
     _capi.lib().gunrock_cc_func(C.byref(out), C.byref(g), _config(**cfg), dt)
     return _take_node_values(out, int(g.num_nodes), np.int32)
+
+
+def gunrock_bc_func(row_offsets, col_indices, **cfg):
+    """-> (bc float32[n], ebc float32[m]) (gunrock.h:112-116); src_node defaults to -1 = every source."""
+    g, keep = _gunrock_graph(row_offsets, col_indices)
+    out = _capi.GunrockGraph()
+    dt = _capi.GunrockDataType(_capi.VTXID_INT, _capi.SIZET_INT, _capi.VALUE_FLOAT)
+    cfg.setdefault("src_node", -1)
+    _capi.lib().gunrock_bc_func(C.byref(out), C.byref(g), _config(**cfg), dt)
+    m = int(g.num_edges)
+    if not out.edge_values:
+        raise GunrockError("library returned no edge_values (see stderr)")
+    ebc = np.ctypeslib.as_array(C.cast(out.edge_values, C.POINTER(C.c_float)), shape=(max(m, 1),))[:m].copy()
+    _capi.free_host(out.edge_values)
+    return _take_node_values(out, int(g.num_nodes), np.float32), ebc
+
+
+def gunrock_topk_func(row_offsets, col_indices, col_offsets, row_indices, top_nodes, **cfg):
+    """-> (node_ids, in_degrees, out_degrees) int32[top_nodes] (gunrock.h:133-141)."""
+    g, keep = _gunrock_graph(row_offsets, col_indices)
+    ci = np.ascontiguousarray(col_offsets, dtype=np.int32)
+    ri = np.ascontiguousarray(row_indices, dtype=np.int32)
+    g.col_offsets = ci.ctypes.data
+    g.row_indices = ri.ctypes.data
+    n = int(g.num_nodes)
+    k = max(min(int(top_nodes), n), 0)
+    ids, ind, outd = (np.full(max(int(top_nodes), 1), -1, dtype=np.int32) for _ in range(3))
+    out = _capi.GunrockGraph()
+    dt = _capi.GunrockDataType(_capi.VTXID_INT, _capi.SIZET_INT, _capi.VALUE_INT)
+    _capi.lib().gunrock_topk_func(C.byref(out), _ptr(ids), _ptr(ind), _ptr(outd), C.byref(g),
+                                  _config(top_nodes=int(top_nodes), **cfg), dt)
+    return ids[:k], ind[:k], outd[:k]
 
 
 def gunrock_sssp_func(row_offsets, col_indices, edge_values, **cfg):

@@ -132,6 +132,8 @@ def lib():
     sig("grb_sssp", C.c_int, [p, i32, i32, i32, p, p, C.POINTER(Stats)])
     sig("grb_cc", C.c_int, [p, p, C.POINTER(i64), C.POINTER(Stats)])
     sig("grb_pagerank", C.c_int, [p, i32, dbl, dbl, i32, p, p, p, C.POINTER(Stats)])
+    sig("grb_bc", C.c_int, [p, i32, p, p, p, C.POINTER(Stats)])
+    sig("grb_topk", C.c_int, [C.c_int, i64, p, p, i32, p, p, p, C.POINTER(Stats)])
     sig("grb_test_advance", C.c_int, [p, C.c_int, C.c_int, p, i64, p, i64, C.POINTER(i64), p, p, p,
                                       C.POINTER(u64)])
     sig("grb_test_filter", C.c_int, [C.c_int, i64, C.c_int, p, i64, p, i64, C.POINTER(i64), p])

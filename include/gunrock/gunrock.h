@@ -107,7 +107,8 @@ void gunrock_bfs_func(
     struct GunrockConfig       configs,
     struct GunrockDataType     data_type);
 
-/* betweenness centrality (outside the accelerated path: reports and returns) */
+/* betweenness centrality: node_values = malloc'ed float[n] (x0.5, summed over every source when
+ * src_node == -1), edge_values = malloc'ed float[m] of zeros (the reference never accumulates it) */
 void gunrock_bc_func(
     struct GunrockGraph       *graph_out,
     const struct GunrockGraph *graph_in,
@@ -139,7 +140,8 @@ void gunrock_pr_func(
     struct GunrockConfig       configs,
     struct GunrockDataType     data_type);
 
-/* degree-centrality top-k (outside the accelerated path: reports and returns) */
+/* degree-centrality top-k: caller-allocated int[top_nodes] outputs, ordered by in+out degree
+ * (descending, ties by ascending vertex id); graph_in needs col_offsets as well */
 void gunrock_topk_func(
     struct GunrockGraph       *graph_out,
     void                      *node_ids,

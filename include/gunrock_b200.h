@@ -140,6 +140,16 @@ int grb_pagerank(grb_graph_t g, int32_t src, double delta, double threshold, int
                  double *ranks64_host, int32_t *sorted_ids_host, float *sorted_ranks_host,
                  grb_stats *stats);
 
+/* ---- BC / top-k --------------------------------------------------------------------
+ * stand in for gunrock_bc_func (app/bc/bc_app.cu:252) and gunrock_topk_func
+ * (app/topk/topk_app.cu:336).  grb_bc: src < 0 accumulates over every source; values are
+ * halved as the reference does; any host output may be NULL. */
+int grb_bc(grb_graph_t g, int32_t src, float *bc_host, float *sigmas_host, int32_t *labels_host,
+           grb_stats *stats);
+int grb_topk(int device, int64_t nodes, const int32_t *row_offsets_host, const int32_t *col_offsets_host,
+             int32_t top_nodes, int32_t *node_ids_host, int32_t *in_degrees_host, int32_t *out_degrees_host,
+             grb_stats *stats);
+
 /* ---- operators, stand-alone (parity tests of the operators themselves) ------------
  * stand in for advance::LaunchKernel (gunrock/oprtr/advance/kernel.cuh:101-129) and
  * filter::Kernel (gunrock/oprtr/filter/kernel.cuh:738-757) run with a probe functor:

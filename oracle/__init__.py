@@ -55,6 +55,10 @@ def lib():
         L.orc_cc.argtypes = [i64, p, p, p]
         L.orc_pagerank.restype = C.c_int
         L.orc_pagerank.argtypes = [i64, p, p, dbl, dbl, C.c_int, i32, p]
+        L.orc_bc.restype = None
+        L.orc_bc.argtypes = [i64, p, p, i32, p, p, p]
+        L.orc_topk.restype = None
+        L.orc_topk.argtypes = [i64, p, p, i64, p, p, p]
         L.orc_rmat_draw.restype = u64
         L.orc_rmat_draw.argtypes = [u64, u64, C.c_uint32, C.c_uint32]
         L.orc_rmat_edges.restype = None
@@ -199,6 +203,28 @@ def pagerank(row_offsets, col, delta=0.85, threshold=0.01, max_iter=20, src=-1):
     it = lib().orc_pagerank(n, _ptr(ro), _ptr(co), float(delta), float(threshold),
                             int(max_iter), int(src), _ptr(rank))
     return rank, int(it)
+
+
+def bc(row_offsets, col, src=-1):
+    """-> (bc float64[n] (x0.5; src < 0: summed over every source), sigmas float64[n], depths int32[n]
+    of the last source)."""
+    ro, co = _offs(row_offsets), _cols(col)
+    n = ro.size - 1
+    out = np.empty(max(n, 1), dtype=np.float64)
+    sig = np.empty(max(n, 1), dtype=np.float64)
+    lab = np.empty(max(n, 1), dtype=np.int32)
+    lib().orc_bc(n, _ptr(ro), _ptr(co), int(src), _ptr(out), _ptr(sig), _ptr(lab))
+    return out[:n], sig[:n], lab[:n]
+
+
+def topk(out_offsets, in_offsets, k):
+    """-> (node_ids, in_degrees, out_degrees), int32[min(k, n)] each."""
+    oo, io = _offs(out_offsets), _offs(in_offsets)
+    n = oo.size - 1
+    k = min(int(k), n)
+    ids, ind, outd = (np.empty(max(k, 1), dtype=np.int32) for _ in range(3))
+    lib().orc_topk(n, _ptr(oo), _ptr(io), k, _ptr(ids), _ptr(ind), _ptr(outd))
+    return ids[:k], ind[:k], outd[:k]
 
 
 def rmat_edges(scale, seed, e0, e1, abcd=RMAT_ABCD):

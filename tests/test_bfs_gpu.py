@@ -23,6 +23,9 @@ def check_preds(ro, co, labels, preds, src):
 
 def test_shared_lib_fixture_through_reference_api(gr, shared_lib):
     """shared_lib_tests/test_bfs.c: 7-vertex graph, src_mode randomize (first draw = 0)"""
+    # the C program is a fresh process: libc rand() in its initial state (= srand(1)), first draw -> vertex 0
+    import ctypes
+    ctypes.CDLL(None).srand(1)
     labels = gr.gunrock_bfs_func(shared_lib["row_offsets"], shared_lib["col_indices"],
                                  src_mode=gr._capi.SRC_RANDOMIZE)
     assert labels.tolist() == shared_lib["bfs_labels"]

@@ -175,3 +175,25 @@ def test_rmat_is_deterministic_and_canonical(orc):
     assert (A != A.T).nnz == 0                          # undirected => symmetric
     # skew like the reference's generator (a = 0.55): vertex 0 is a hub
     assert np.diff(ro)[0] == np.diff(ro).max()
+
+
+def test_bc_and_topk_goldens():
+    """CMakeLists.txt:219-221 (test_bc.c graph: node 0 -> 0.5) and :235-237 (test_topk.c graph:
+    node 2 -> in 3 / out 3, first of the top 3)"""
+    import oracle
+    ro = [0, 3, 6, 11, 15, 19, 23, 26]
+    co = [1, 2, 3, 0, 2, 4, 0, 1, 3, 4, 5, 0, 2, 5, 6, 1, 2, 5, 6, 2, 3, 4, 6, 3, 4, 5]
+    bc, _, _ = oracle.bc(ro, co, -1)
+    assert np.allclose(bc, [0.5, 0.5, 7 / 3, 11 / 6, 11 / 6, 2 / 3, 1 / 3])
+    # summing single-source runs reproduces the all-source value; the source itself gets nothing
+    acc = np.zeros(7)
+    for s in range(7):
+        one, sig, depth = oracle.bc(ro, co, s)
+        assert one[s] == 0 and sig[s] == 1 and depth[s] == 0
+        acc += one
+    assert np.allclose(acc, bc)
+    # a path 0-1-2-3-4: interior vertices lie on (i)(4-i) pairs
+    pro, pco = [0, 1, 3, 5, 7, 8], [1, 0, 2, 1, 3, 2, 4, 3]
+    assert np.allclose(oracle.bc(pro, pco, -1)[0], [0, 3, 4, 3, 0])
+    ids, ind, outd = oracle.topk([0, 3, 6, 9, 11, 14, 15, 15], [0, 1, 2, 5, 7, 9, 12, 15], 3)
+    assert ids.tolist() == [2, 4, 0] and ind.tolist() == [3, 2, 1] and outd.tolist() == [3, 3, 3]

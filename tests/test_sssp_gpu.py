@@ -27,6 +27,9 @@ def check_preds(ro, co, w, dist, preds, src):
 
 def test_shared_lib_fixture_through_reference_api(gr, shared_lib):
     """shared_lib_tests/test_sssp.c; golden CMakeLists.txt:227-229: node 1 -> 39, predecessor 0"""
+    # the C program is a fresh process: libc rand() in its initial state (= srand(1)), first draw -> vertex 0
+    import ctypes
+    ctypes.CDLL(None).srand(1)
     dist, preds = gr.gunrock_sssp_func(shared_lib["row_offsets"], shared_lib["col_indices"],
                                        shared_lib["edge_values"], src_mode=gr._capi.SRC_RANDOMIZE,
                                        mark_pred=True, delta_factor=1)

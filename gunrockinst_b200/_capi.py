@@ -45,7 +45,7 @@ class Stats(C.Structure):
                 ("gpu_launches", C.c_int32), ("reserved", C.c_int32)]
 
     def as_dict(self):
-        return {k: getattr(self, k) for k, _ in self._fields_ if k != "reserved"}
+        return {k: getattr(self, k) for k, _ in self._fields_}
 
 
 class LevelRecord(C.Structure):
@@ -115,6 +115,7 @@ def lib():
 
     sig("grb_version", C.c_char_p, [])
     sig("grb_device_count", C.c_int, [])
+    sig("grb_release_cached_memory", None, [])
     sig("grb_graph_from_host", C.c_int, [C.c_int, i64, i64, p, C.c_int, p, p, C.c_int, C.c_int, pp])
     sig("grb_graph_rmat", C.c_int, [C.c_int, C.c_int, i64, u64, C.c_int, dbl, dbl, dbl, dbl,
                                     C.c_int, C.c_int, u64, C.c_int, pp])

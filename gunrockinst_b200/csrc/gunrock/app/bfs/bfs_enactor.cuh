@@ -90,8 +90,8 @@ __global__ void EdgesVisitedKernel(const VertexId *labels, const SizeT *row_offs
 struct BFSOptions {
     int    traversal_mode      = 0;      // 0: choose per level, 1: always LB, 2: always TWC (reference: --traversal-mode)
     bool   direction_optimized = false;  // allow the pull direction (needs an inverse graph)
-    double alpha               = 14.0;   // push -> pull when frontier_edges > unexplored_edges / alpha
-    double beta                = 24.0;   // pull -> push when frontier < n / beta and shrinking
+    double alpha               = 8.0;    // push -> pull when frontier_edges > unexplored_edges / alpha
+    double beta                = 72.0;   // pull -> push when frontier < n / beta and shrinking (swept on B200: tools/sweep_alpha.py)
     unsigned long long lb_min_edges = 1u << 12;   // mode 0: LB from this many frontier edges upward
     bool   record_levels       = false;  // keep a per-level trace (adds two events per level)
     bool   host_loop           = false;  // drive every level from the host (the reference's structure) instead
@@ -135,7 +135,11 @@ class BFSEnactor : public EnactorBase {
     util::DeviceArray<PersistentSummary>  d_summary;     // [0] summary, [1] reused as the 8-byte queue cursor
     util::PinnedArray<DeviceLevelRecord>  h_records;
     util::PinnedArray<PersistentSummary>  h_summary;
+    util::DeviceArray<VertexId>           d_sources;     // run-many: the batch of sources
+    util::PinnedArray<VertexId>           h_sources;
+    int many_count = 0;
     bool persistent_ok = false;
+    int  kernel_us = 0, reset_us = 0;     // device-side span of the last persistent search / of its reset phase
     int  persistent_grid = 0;
 
     ~BFSEnactor()
@@ -169,7 +173,10 @@ class BFSEnactor : public EnactorBase {
                src >= 0 && (long long)src < problem->graph->nodes;
     }
 
-    cudaError_t Enact(Problem *problem, VertexId src, const BFSOptions &opt, bool reset_on_device = false)
+    // sources / count / summaries: a batch of searches in one launch (needs reset_on_device; `src` is
+    // then the last source of the batch, whose labels are the ones left on the device)
+    cudaError_t Enact(Problem *problem, VertexId src, const BFSOptions &opt, bool reset_on_device = false,
+                      const VertexId *sources = nullptr, int count = 0, PersistentSummary *summaries = nullptr)
     {
         if (!set_up) return util::GRError(cudaErrorNotReady, "BFSEnactor::Setup not called", __FILE__, __LINE__);
         if (reset_on_device && !FusesReset(src, problem, opt))
@@ -181,8 +188,16 @@ class BFSEnactor : public EnactorBase {
         edges_visited = 0;
         if (src < 0 || (long long)src >= problem->graph->nodes) return cudaSuccess;
         if constexpr (Problem::ENABLE_IDEMPOTENCE) return EnactIdempotent(problem, opt);
-        else return (opt.host_loop || !persistent_ok) ? EnactFused(problem, opt)
-                                                      : EnactPersistent(problem, opt, reset_on_device);
+        else {
+            if (sources && count > 0) {
+                if (!reset_on_device)
+                    return util::GRError(cudaErrorInvalidValue, "BFSEnactor: a batch needs the device-side reset",
+                                         __FILE__, __LINE__);
+                return EnactPersistentMany(problem, sources, count, opt, summaries);
+            }
+            return (opt.host_loop || !persistent_ok) ? EnactFused(problem, opt)
+                                                     : EnactPersistent(problem, opt, reset_on_device);
+        }
     }
 
     // recount edges_visited from the labels (idempotent mode cannot track it: duplicates)
@@ -249,6 +264,26 @@ class BFSEnactor : public EnactorBase {
         return cudaSuccess;
     }
 
+    // `count` searches in one launch (sources on the host; needs the device-side reset); summaries[i]
+    // receives the i-th search's summary
+    cudaError_t EnactPersistentMany(Problem *problem, const VertexId *sources, int count, const BFSOptions &opt,
+                                    PersistentSummary *summaries)
+    {
+        if (count <= 0) return cudaSuccess;
+        GR_TRY(d_sources.Allocate((size_t)count));
+        GR_TRY(h_sources.Allocate((size_t)count));
+        GR_TRY(d_summary.Allocate((size_t)count + 1));
+        GR_TRY(h_summary.Allocate((size_t)count + 1));
+        for (int i = 0; i < count; ++i) h_sources.ptr[i] = sources[i];
+        GR_TRY(cudaMemcpyAsync(d_sources.ptr, h_sources.ptr, sizeof(VertexId) * (size_t)count, cudaMemcpyHostToDevice, stream));
+        problem->src = sources[count - 1];
+        many_count = count;
+        cudaError_t e = EnactPersistent(problem, opt, true);
+        many_count = 0;
+        for (int i = 0; i < count; ++i) summaries[i] = h_summary.ptr[i];
+        return e;
+    }
+
     cudaError_t EnactPersistent(Problem *problem, const BFSOptions &opt, bool reset_on_device)
     {
         typename Problem::Base::Graph &g = *problem->graph;
@@ -267,6 +302,8 @@ class BFSEnactor : public EnactorBase {
         P.visited = problem->visited_mask.ptr;
         P.candidates = can_pull ? problem->candidates.ptr : nullptr;
         P.head = can_pull ? problem->head.ptr : nullptr;
+        P.tickets = work_progress.d_tickets.ptr;
+        GR_TRY(work_progress.d_tickets.Zero(stream));
         if (lb_scratch.epoch + 64 >= oprtr::advance::lb::kEpochLimit) {   // keep wraps out of the common case
             GR_TRY(lb_scratch.tile_desc.Zero(stream));
             lb_scratch.epoch = 0;
@@ -280,33 +317,32 @@ class BFSEnactor : public EnactorBase {
         P.max_records = opt.record_levels ? kMaxRecords : 0;
         P.summary = d_summary.ptr;
         P.src = problem->src;
+        P.sources = many_count ? d_sources.ptr : nullptr;
+        P.num_sources = many_count;
         P.do_reset = reset_on_device ? 1 : 0;
         P.mask_words = (unsigned long long)problem->visited_mask.size;
-        P.src_is_mine = g.part.Mine(problem->src) ? 1 : 0;
         P.can_pull = can_pull ? 1 : 0;
         P.traversal_mode = opt.traversal_mode;
         P.alpha = opt.alpha; P.beta = opt.beta;
         P.lb_min_edges = opt.lb_min_edges;
 
-        if (!reset_on_device) GR_TRY(d_summary.Zero(stream));
+        if (!reset_on_device || many_count) GR_TRY(d_summary.Zero(stream));
         DataSlice ds = problem->MakeDataSlice(0);
-        unsigned long long *cursor = reinterpret_cast<unsigned long long *>(d_summary.ptr + 1);
+        const int searches = many_count ? many_count : 1;
+        unsigned long long *cursor = reinterpret_cast<unsigned long long *>(d_summary.ptr + searches);
         unsigned long long desc_words = (unsigned long long)lb_scratch.tile_desc.size;
         void *kargs[] = {(void *)&ds, (void *)&P, (void *)&cursor, (void *)&desc_words};
         GR_TRY(cudaLaunchCooperativeKernel((const void *)PersistentEntry(), dim3((unsigned)persistent_grid),
                                            dim3(AdvancePolicy::THREADS), kargs, 0, stream));
         enactor_stats.launches = 1;
-        GR_TRY(cudaMemcpyAsync(h_summary.ptr, d_summary.ptr, sizeof(PersistentSummary), cudaMemcpyDeviceToHost, stream));
+        GR_TRY(cudaMemcpyAsync(h_summary.ptr, d_summary.ptr, sizeof(PersistentSummary) * (size_t)searches,
+                               cudaMemcpyDeviceToHost, stream));
         if (opt.record_levels)
             GR_TRY(cudaMemcpyAsync(h_records.ptr, d_records.ptr, sizeof(DeviceLevelRecord) * kMaxRecords,
                                    cudaMemcpyDeviceToHost, stream));
         GR_TRY(cudaStreamSynchronize(stream));
-        const PersistentSummary &sum = h_summary.ptr[0];
-        lb_scratch.epoch += (unsigned)sum.lb_calls;
-        if (lb_scratch.epoch >= oprtr::advance::lb::kEpochLimit) {           // the kernel wrapped on its own
-            GR_TRY(lb_scratch.tile_desc.Zero(stream));
-            lb_scratch.epoch = 0;
-        }
+        const PersistentSummary &sum = h_summary.ptr[searches - 1];      // stats of the (last) search
+        lb_scratch.epoch = (unsigned)sum.epoch_end;        // the kernel wraps (and re-zeroes) on its own
         enactor_stats.iteration = (long long)sum.levels;
         enactor_stats.total_queued = sum.total_queued;
         enactor_stats.edges_inspected = sum.edges_inspected;
@@ -314,6 +350,7 @@ class BFSEnactor : public EnactorBase {
         enactor_stats.push_levels = (int)sum.push_levels;
         enactor_stats.pull_levels = (int)sum.pull_levels;
         edges_visited = sum.edges_visited;
+        kernel_us = (int)(sum.ns_kernel / 1000); reset_us = (int)(sum.ns_reset / 1000);
         if (opt.record_levels) {
             const int cnt = (int)(sum.levels < (unsigned long long)kMaxRecords ? sum.levels : kMaxRecords);
             for (int i = 0; i < cnt; ++i) {
@@ -395,6 +432,8 @@ class BFSEnactor : public EnactorBase {
                 pa.visited      = problem->visited_mask.ptr;
                 pa.candidates   = problem->candidates.ptr;
                 pa.head         = problem->head.ptr;
+                pa.tickets      = work_progress.Tickets(level);
+                GR_TRY(cudaMemsetAsync(pa.tickets, 0, sizeof(unsigned long long) * oprtr::WorkProgress::kTicketWords, stream));
                 pa.fwd_row_offsets = g.symmetric ? nullptr : g.row_offsets.ptr;
                 pa.out_queue = nullptr; pa.out_cap = 0;
                 pa.slots = work_progress.d_slots.ptr;

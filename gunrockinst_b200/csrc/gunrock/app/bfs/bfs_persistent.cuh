@@ -30,7 +30,7 @@ namespace bfs {
 
 // what one level did (device-written; the host turns it into LevelRecord / EnactorStats)
 struct DeviceLevelRecord {
-    int level, kind;                                // kind: 0 push-TWC, 1 pull, 2 push-LB
+    int level, kind;                                // kind: 0 push-TWC, 1 pull, 2 push-LB, 3 push-LB on a CTA-private scan
     unsigned long long frontier, edges, discovered, candidates;
     unsigned long long ns;                          // globaltimer span of the level, barriers included
     unsigned long long ns_switch;                   // ... of which queue <-> bitmap conversion (+ its barrier)
@@ -39,9 +39,12 @@ struct DeviceLevelRecord {
 struct PersistentSummary {
     unsigned long long levels, push_levels, pull_levels;
     unsigned long long total_queued, edges_inspected, edges_visited, algo_bytes;
-    unsigned long long lb_calls;                    // epochs consumed from the LB scratch
+    unsigned long long lb_calls;                    // LB scans of this search
+    unsigned long long epoch_end;                   // look-back epoch of the LB scratch after this search
     unsigned long long overflow;
     unsigned long long grid_syncs;
+    unsigned long long ns_kernel;                   // globaltimer span of the whole kernel as seen by its first thread
+    unsigned long long ns_reset;                    // ... of which the in-kernel Problem::Reset
 };
 
 template <typename VertexId, typename SizeT>
@@ -55,15 +58,17 @@ struct PersistentParams {
     unsigned    *visited;
     const unsigned *candidates;
     const VertexId *head;
+    unsigned long long *tickets;                    // 2 sets of pull-sweep chunk counters (zeroed by the host)
     oprtr::advance::LbScratchView<SizeT> scratch;   // .epoch = first epoch this run may use
     oprtr::LevelCounters *slots;                    // zeroed by the host before the launch
     DeviceLevelRecord    *records;                  // optional trace
     int                   max_records;
     PersistentSummary    *summary;
-    VertexId src;
+    VertexId src;                                   // the source, or ...
+    const VertexId *sources;                        // ... num_sources of them, searched one after the other by ONE
+    int      num_sources;                           //     launch (needs do_reset); summary[i] describes search i
     int      do_reset;                              // 1: the kernel also does Problem::Reset's device work
     unsigned long long mask_words;                  // words of the visited bitmap (do_reset)
-    int      src_is_mine;
     int      can_pull;
     int      traversal_mode;
     double   alpha, beta;
@@ -152,29 +157,36 @@ PersistentKernel(const __grid_constant__ typename Problem::DataSlice ds0,
 
     __shared__ PersistentStorage<PushPolicy, PullPolicy, Problem::MARK_PREDECESSORS> sm;
     __shared__ unsigned long long s_level[5];           // the level's counters: one L2 read per CTA, not per warp
+    __shared__ oprtr::advance::lb::SmallScanStorage<PushPolicy> s_small;
     cg::grid_group grid = cg::this_grid();
     const unsigned cta = blockIdx.x, num_ctas = gridDim.x;
     const bool leader = cta == 0 && threadIdx.x == 0;
     const unsigned long long gtid = (unsigned long long)cta * THREADS + threadIdx.x;
     const unsigned long long gthreads = (unsigned long long)num_ctas * THREADS;
 
-    // ---- loop state: identical in every thread of the grid ------------------------------------
+    const unsigned long long n = (unsigned long long)P.g.nodes;
+    const unsigned osz = (unsigned)sizeof(SizeT);
+    unsigned epoch = P.scratch.epoch;
     DataSlice ds = ds0;
-    unsigned long long F = P.src_is_mine ? 1ull : 0ull;
+    const int num_searches = P.sources ? P.num_sources : 1;
+
+  for (int si = 0; si < num_searches; ++si) {
+    const unsigned long long t_start = leader ? GlobalTimerNs() : 0ull;
+    // ---- loop state: identical in every thread of the grid ------------------------------------
+    const VertexId src = P.sources ? P.sources[si] : P.src;
+    const bool src_is_mine = P.g.part.Mine(src);
+    unsigned long long F = src_is_mine ? 1ull : 0ull;
     unsigned long long frontier_edges = 0;
-    if (P.src_is_mine) {
-        const long long row = P.g.part.Local(P.src);
+    if (src_is_mine) {
+        const long long row = P.g.part.Local(src);
         frontier_edges = (unsigned long long)(P.g.row_offsets[row + 1] - P.g.row_offsets[row]);
     }
     unsigned long long unexplored = (unsigned long long)P.g.edges - frontier_edges;
     unsigned long long prev_len = 0;
-    const unsigned long long n = (unsigned long long)P.g.nodes;
-    const unsigned osz = (unsigned)sizeof(SizeT);
-    bool pull = false;
+    bool pull = false, aborted = false;
     int  cur_map = 0, sel = 0;
     long long qi = 0;
     VertexId level = 0;
-    unsigned epoch = P.scratch.epoch;
     PersistentSummary sum;
     sum.levels = sum.push_levels = sum.pull_levels = 0;
     sum.total_queued = sum.edges_inspected = sum.algo_bytes = 0;
@@ -191,7 +203,7 @@ PersistentKernel(const __grid_constant__ typename Problem::DataSlice ds0,
     // is written once, by the thread that owns it, so no ordering between the fills is needed
     if (P.do_reset) {
         const long long ln = ds.local_nodes;
-        const long long src_row = P.src_is_mine ? (long long)P.g.part.Local(P.src) : -1;
+        const long long src_row = src_is_mine ? (long long)P.g.part.Local(src) : -1;
         const long long quads = ln >> 2;
         int4 *labels4 = reinterpret_cast<int4 *>(ds.d_labels);
         for (long long q = (long long)gtid; q < quads; q += (long long)gthreads) {
@@ -208,19 +220,22 @@ PersistentKernel(const __grid_constant__ typename Problem::DataSlice ds0,
             for (long long i = (long long)gtid; i < ln; i += (long long)gthreads)
                 ds.d_preds[i] = (i == src_row) ? -1 : -2;
         }
-        const unsigned long long src_pos = ds.BitPos(P.src);
+        const unsigned long long src_pos = ds.BitPos(src);
         for (unsigned long long w = gtid; w < P.mask_words; w += gthreads)
             P.visited[w] = (w == (src_pos >> 5)) ? (1u << (src_pos & 31)) : 0u;
         if (leader) {
-            if (P.src_is_mine) P.queues[0][0] = P.src;
+            if (src_is_mine) P.queues[0][0] = src;
             unsigned long long *z = reinterpret_cast<unsigned long long *>(P.slots);
             for (int i = 0; i < (int)(4 * sizeof(oprtr::LevelCounters) / 8); ++i) z[i] = 0;
-            P.summary->overflow = 0;
+            P.summary[si].overflow = 0;
             *cursor = 0;
         }
+        if (cta == 0 && P.tickets)          // both sets of pull-sweep chunk counters
+            for (int x = threadIdx.x; x < 2 * oprtr::WorkProgress::kTicketWords; x += THREADS) P.tickets[x] = 0;
         grid.sync(); ++sum.grid_syncs;
     }
 
+    sum.ns_reset = leader ? GlobalTimerNs() - t_start : 0ull;
     while (F > 0) {
         const unsigned long long t0 = leader ? GlobalTimerNs() : 0ull;
         ds.level = level;
@@ -232,7 +247,7 @@ PersistentKernel(const __grid_constant__ typename Problem::DataSlice ds0,
                 pull = true;
             } else if (pull && F < prev_len && (double)F < (double)n / P.beta) {
                 BitmapToQueue<THREADS>(P.frontier_map[cur_map], P.queues[sel], P.queue_cap[sel], cursor,
-                                       &P.summary->overflow, ds, sm.b2q, cta, num_ctas);
+                                       &P.summary[si].overflow, ds, sm.b2q, cta, num_ctas);
                 grid.sync(); ++sum.grid_syncs;
                 if (leader) *cursor = 0;
                 pull = false;
@@ -242,6 +257,10 @@ PersistentKernel(const __grid_constant__ typename Problem::DataSlice ds0,
         // ---- one level ------------------------------------------------------------------------------
         oprtr::LevelCounters *slot_out = P.slots + ((qi + 1) & 3);
         if (leader) oprtr::ClearFutureSlot(P.slots, qi);
+        // chunk-ticket counters of the pull sweep: a level uses set (level & 1); every level clears the
+        // other set, so whichever level pulls next finds its set zeroed
+        if (cta == 0 && P.tickets && threadIdx.x < oprtr::WorkProgress::kTicketWords)
+            P.tickets[((level + 1) & 1) * oprtr::WorkProgress::kTicketWords + threadIdx.x] = 0;
         int kind;
         if (!pull) {
             adv::Args<VertexId, SizeT> a;
@@ -252,7 +271,13 @@ PersistentKernel(const __grid_constant__ typename Problem::DataSlice ds0,
             a.slots = P.slots; a.queue_index = qi; a.iteration = level;
             a.output = adv::OUT_COMPACT;
             const bool lb = P.traversal_mode == 1 || (P.traversal_mode != 2 && frontier_edges >= P.lb_min_edges);
-            if (!lb) {
+            if (P.traversal_mode == 0 && F <= (unsigned long long)adv::lb::SmallScanStorage<PushPolicy>::SMALL_ITEMS) {
+                // short frontier (first / last levels, a hub on its own): every CTA scans it privately
+                // and expands its share of the edge tiles -- one pass, all SMs, no extra barrier
+                kind = 3;
+                adv::lb::ExpandSmall<PushPolicy, Problem, PushFunctor>(ds, a, s_small, sm.expand, F, frontier_edges,
+                                                                       slot_out, cta, num_ctas);
+            } else if (!lb) {
                 kind = 0;
                 adv::twc::ExpandItems<PushPolicy, Problem, PushFunctor>(ds, a, sm.twc, F, slot_out, cta, num_ctas);
             } else {
@@ -279,6 +304,7 @@ PersistentKernel(const __grid_constant__ typename Problem::DataSlice ds0,
             pa.visited = P.visited;
             pa.candidates = P.candidates;
             pa.head = P.head;
+            pa.tickets = P.tickets + (level & 1) * oprtr::WorkProgress::kTicketWords;
             pa.fwd_row_offsets = P.fwd_row_offsets;
             pa.out_queue = nullptr; pa.out_cap = 0;
             pa.slots = P.slots; pa.queue_index = qi; pa.iteration = level;
@@ -310,7 +336,7 @@ PersistentKernel(const __grid_constant__ typename Problem::DataSlice ds0,
             P.records[sum.levels] = r;
         }
         ++sum.levels;
-        if (ovf) { sum.overflow = 1; break; }
+        if (ovf) { sum.overflow = 1; aborted = true; break; }
         prev_len = F;
         F = D;
         frontier_edges = deg;
@@ -321,9 +347,15 @@ PersistentKernel(const __grid_constant__ typename Problem::DataSlice ds0,
         ++level;
     }
     if (leader) {
-        if (P.summary->overflow) sum.overflow = 1;     // raised by the bitmap -> queue conversion
-        *P.summary = sum;
+        if (P.summary[si].overflow) sum.overflow = 1;  // raised by the bitmap -> queue conversion
+        sum.ns_kernel = GlobalTimerNs() - t_start;
+        sum.epoch_end = epoch;
+        P.summary[si] = sum;
     }
+    if (aborted) break;                                 // uniform: every thread saw the same counter
+    // the next search resets the counters every CTA has just read: everybody must be past that read
+    if (si + 1 < num_searches) grid.sync();
+  }
 }
 
 }  // namespace bfs

@@ -187,6 +187,7 @@ class MGBFSEnactor : public EnactorBase {
         pa.visited      = problem->visited_mask.ptr;
         pa.candidates   = problem->candidates.ptr;
         pa.head         = problem->head.ptr;
+        pa.tickets      = nullptr;
         pa.fwd_row_offsets = g.symmetric ? nullptr : g.row_offsets.ptr;
         pa.out_queue = nullptr; pa.out_cap = 0;
         pa.slots = work_progress.d_slots.ptr; pa.queue_index = 0; pa.iteration = level;

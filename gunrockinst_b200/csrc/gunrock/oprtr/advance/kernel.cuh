@@ -22,10 +22,8 @@ struct DeviceInfo {
     cudaError_t Query(int dev)
     {
         device = dev;
-        cudaDeviceProp p;
-        GR_TRY(cudaGetDeviceProperties(&p, dev));
-        sm_count = p.multiProcessorCount;
-        return cudaSuccess;
+        // one attribute, not cudaGetDeviceProperties (which costs ~1 ms and sat in every one-shot call)
+        return cudaDeviceGetAttribute(&sm_count, cudaDevAttrMultiProcessorCount, dev);
     }
 };
 

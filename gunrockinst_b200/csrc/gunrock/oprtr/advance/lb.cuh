@@ -135,18 +135,26 @@ __device__ __forceinline__ void ScanTiles(
         ScanT deg[R], excl[R];
         SizeT first[R];
         ScanT running = 0;
+        // all loads of the tile first (queue, then offsets): the scans below are full of barriers and
+        // would otherwise serialise R dependent round trips to memory
+        VertexId item[R];
 #pragma unroll
         for (int r = 0; r < R; ++r) {
             unsigned long long i = base + (unsigned long long)r * T + threadIdx.x;
+            item[r] = -1;
+            if (i < in_len) item[r] = args.in_queue ? util::LoadCG(args.in_queue + i) : (VertexId)args.g.part.Global((long long)i);
+        }
+#pragma unroll
+        for (int r = 0; r < R; ++r) {
             deg[r] = 0; first[r] = 0;
-            if (i < in_len) {
-                VertexId v = args.in_queue ? util::LoadCG(args.in_queue + i) : (VertexId)args.g.part.Global((long long)i);
-                if (v >= 0 && (long long)v < args.g.nodes) {
-                    long long row = args.g.part.Local(v);
-                    SizeT a = args.g.row_offsets[row], b = args.g.row_offsets[row + 1];
-                    first[r] = a; deg[r] = (ScanT)(b - a);
-                }
+            if (item[r] >= 0 && (long long)item[r] < args.g.nodes) {
+                long long row = args.g.part.Local(item[r]);
+                SizeT a = args.g.row_offsets[row], b = args.g.row_offsets[row + 1];
+                first[r] = a; deg[r] = (ScanT)(b - a);
             }
+        }
+#pragma unroll
+        for (int r = 0; r < R; ++r) {
             ScanT total;
             excl[r] = running + util::BlockExclusiveSum<T>(deg[r], sm.warp, total);
             running += total;
@@ -203,13 +211,41 @@ struct ExpandStorage {
     unsigned long long red[Policy::THREADS / 32 + 1];
 };
 
+// where ExpandTiles finds the scanned frontier: the global scratch ScanKernel filled ...
+template <typename SizeT>
+struct GlobalScan {
+    const LbScratchView<SizeT> &s;
+    __device__ __forceinline__ unsigned long long Scanned(long long i) const { return s.scanned[i]; }
+    __device__ __forceinline__ SizeT RowStart(long long i) const { return s.row_start[i]; }
+    __device__ __forceinline__ long long FirstItem(unsigned long long tile, unsigned long long) const { return s.part_start[tile]; }
+    __device__ __forceinline__ unsigned long long TileCap() const { return s.part_cap; }
+};
+// ... or a CTA-private copy in shared memory (small frontiers: every CTA scans the whole frontier
+// itself, which spares the scan pass, its scratch traffic and a grid-wide barrier)
+template <typename SizeT>
+struct LocalScan {
+    const unsigned long long *scanned;      // [in_len + 1]
+    const SizeT              *row_start;    // [in_len]
+    long long                 in_len;
+    __device__ __forceinline__ unsigned long long Scanned(long long i) const { return scanned[i]; }
+    __device__ __forceinline__ SizeT RowStart(long long i) const { return row_start[i]; }
+    // the item that owns edge tile_start: last i with scanned[i] <= tile_start (it has edges: scanned[i+1] > tile_start)
+    __device__ __forceinline__ long long FirstItem(unsigned long long, unsigned long long tile_start) const
+    {
+        long long lo = 0, hi = in_len + 1;
+        while (lo < hi) { const long long mid = (lo + hi) >> 1; if (scanned[mid] <= tile_start) lo = mid + 1; else hi = mid; }
+        return lo - 1;
+    }
+    __device__ __forceinline__ unsigned long long TileCap() const { return ~0ull; }
+};
+
 // Expands tiles cta, cta + num_ctas, ... of the scanned frontier.  Callable from any kernel whose
 // CTAs have Policy::THREADS threads (the stand-alone ExpandKernel below, the persistent BFS kernel).
-template <typename Policy, typename Problem, typename Functor>
-__device__ __forceinline__ void ExpandTiles(
+template <typename Policy, typename Problem, typename Functor, typename Scan>
+__device__ __forceinline__ void ExpandTilesFrom(
     const typename Problem::DataSlice &ds,
     const Args<typename Policy::VertexId, typename Policy::SizeT> &args,
-    const LbScratchView<typename Policy::SizeT> &scratch,
+    const Scan &scan, const unsigned long long total,
     ExpandStorage<Policy, Problem::MARK_PREDECESSORS> &sm,
     unsigned long long in_len, LevelCounters *slot_out, unsigned cta, unsigned num_ctas)
 {
@@ -223,13 +259,9 @@ __device__ __forceinline__ void ExpandTiles(
     static_assert(32 % (THREADS / 32) == 0, "warps per CTA must divide 32");
 
     const int lane = util::LaneId();
-    // one load per CTA, not per warp: thousands of warps asking one L2 slice for the same word queue up
-    if (threadIdx.x == 0) sm.red[0] = scratch.scanned[in_len];
-    __syncthreads();
-    const ScanT total = sm.red[0];
     unsigned long long num_tiles = (total + TILE_E - 1) / TILE_E;
-    if (num_tiles > scratch.part_cap) {     // a frontier with duplicates expanded past the scratch
-        num_tiles = scratch.part_cap;
+    if (num_tiles > scan.TileCap()) {       // a frontier with duplicates expanded past the scratch
+        num_tiles = scan.TileCap();
         if (threadIdx.x == 0) slot_out->overflow = 1;
     }
     Stager<Policy> stager(sm.stager, args, slot_out);
@@ -242,8 +274,8 @@ __device__ __forceinline__ void ExpandTiles(
     for (unsigned long long tile = cta; tile < num_tiles; tile += num_ctas, parity ^= 1) {
         const ScanT tile_start = tile * TILE_E;
         const int tile_edges = (int)((total - tile_start < (ScanT)TILE_E) ? (total - tile_start) : (ScanT)TILE_E);
-        const long long i0 = scratch.part_start[tile];
-        const long long i1 = (tile + 1 < num_tiles) ? scratch.part_start[tile + 1] : (long long)in_len - 1;
+        const long long i0 = scan.FirstItem(tile, tile_start);
+        const long long i1 = (tile + 1 < num_tiles) ? scan.FirstItem(tile + 1, tile_start + TILE_E) : (long long)in_len - 1;
         const int cnt = (int)((i1 - i0 + 1 < (long long)WINDOW + 1) ? (i1 - i0 + 1) : (long long)WINDOW + 1);
         const bool windowed = cnt <= WINDOW;
 
@@ -252,9 +284,9 @@ __device__ __forceinline__ void ExpandTiles(
         unsigned *bits = sm.bits[parity];
         if (windowed) {
             for (int j = threadIdx.x; j < cnt; j += THREADS) {
-                const ScanT s = scratch.scanned[i0 + j], e = scratch.scanned[i0 + j + 1];
+                const ScanT s = scan.Scanned(i0 + j), e = scan.Scanned(i0 + j + 1);
                 const long long rel = (long long)s - (long long)tile_start;     // < 0 only for j == 0
-                sm.base[j] = (SizeT)((long long)scratch.row_start[i0 + j] - rel);
+                sm.base[j] = (SizeT)((long long)scan.RowStart(i0 + j) - rel);
                 if constexpr (NEED_SRC) sm.src[j] = args.in_queue ? args.in_queue[i0 + j] : (VertexId)args.g.part.Global(i0 + j);
                 const int slot = rel < 0 ? 0 : (int)rel;
                 if (e > s && slot < TILE_E) {       // unique: the lists that start inside a tile start at distinct slots
@@ -307,9 +339,9 @@ __device__ __forceinline__ void ExpandTiles(
             } else if (live[r]) {                                       // rare: > WINDOW (mostly empty) items in one tile
                 const ScanT y = tile_start + ly;
                 long long lo = i0, hi = i1 + 1;
-                while (lo < hi) { long long mid = (lo + hi) >> 1; if (scratch.scanned[mid] <= y) lo = mid + 1; else hi = mid; }
+                while (lo < hi) { long long mid = (lo + hi) >> 1; if (scan.Scanned(mid) <= y) lo = mid + 1; else hi = mid; }
                 item[r] = (int)(lo - 1 - i0);
-                pos[r]  = (SizeT)((long long)scratch.row_start[lo - 1] + (long long)(y - scratch.scanned[lo - 1]));
+                pos[r]  = (SizeT)((long long)scan.RowStart(lo - 1) + (long long)(y - scan.Scanned(lo - 1)));
             }
         }
         VertexId nbr[EPT];
@@ -357,6 +389,82 @@ __device__ __forceinline__ void ExpandTiles(
     // per-CTA statistics: one atomic each
     BlockAccumulate<THREADS>(my_edges_total, sm.red, &slot_out->edges);
     if constexpr (Policy::TRACK_OUT_DEGREE) BlockAccumulate<THREADS>(stager.out_degree, sm.red, &slot_out->out_degree);
+}
+
+// the scanned frontier lives in the global scratch (after ScanKernel / ScanTiles)
+template <typename Policy, typename Problem, typename Functor>
+__device__ __forceinline__ void ExpandTiles(
+    const typename Problem::DataSlice &ds,
+    const Args<typename Policy::VertexId, typename Policy::SizeT> &args,
+    const LbScratchView<typename Policy::SizeT> &scratch,
+    ExpandStorage<Policy, Problem::MARK_PREDECESSORS> &sm,
+    unsigned long long in_len, LevelCounters *slot_out, unsigned cta, unsigned num_ctas)
+{
+    // one load per CTA, not per warp: thousands of warps asking one L2 slice for the same word queue up
+    if (threadIdx.x == 0) sm.red[0] = scratch.scanned[in_len];
+    __syncthreads();
+    const unsigned long long total = sm.red[0];
+    GlobalScan<typename Policy::SizeT> scan = {scratch};
+    ExpandTilesFrom<Policy, Problem, Functor>(ds, args, scan, total, sm, in_len, slot_out, cta, num_ctas);
+}
+
+// Small frontiers (in_len <= SMALL_ITEMS): every CTA scans the frontier's degrees itself into shared
+// memory and takes its tiles straight away -- one pass, no scratch, no barrier between scan and
+// expansion, and a single hub's list is still spread over all CTAs.
+template <typename Policy>
+struct SmallScanStorage {
+    static const int SMALL_ITEMS = Policy::THREADS * 4;
+    unsigned long long     scanned[SMALL_ITEMS + 1];
+    typename Policy::SizeT row_start[SMALL_ITEMS];
+    unsigned long long     warp[Policy::THREADS / 32 + 1];
+};
+
+template <typename Policy, typename Problem, typename Functor>
+__device__ __forceinline__ void ExpandSmall(
+    const typename Problem::DataSlice &ds,
+    const Args<typename Policy::VertexId, typename Policy::SizeT> &args,
+    SmallScanStorage<Policy> &ss, ExpandStorage<Policy, Problem::MARK_PREDECESSORS> &sm,
+    unsigned long long in_len, unsigned long long edges_hint, LevelCounters *slot_out, unsigned cta, unsigned num_ctas)
+{
+    typedef typename Policy::VertexId VertexId;
+    typedef typename Policy::SizeT    SizeT;
+    typedef unsigned long long        ScanT;
+    constexpr int T = Policy::THREADS, R = 4;
+    // a CTA beyond the last tile has nothing to do (edges_hint: exact degree sum, or an upper bound)
+    if ((unsigned long long)cta * Policy::TILE_EDGES >= edges_hint && cta != 0) return;
+    ScanT running = 0;
+    VertexId item[R];
+    ScanT    deg[R];
+    SizeT    first[R];
+#pragma unroll
+    for (int r = 0; r < R; ++r) {           // all loads first, scans (barriers) afterwards
+        const unsigned long long i = (unsigned long long)r * T + threadIdx.x;
+        item[r] = -1;
+        if (i < in_len) item[r] = args.in_queue ? util::LoadCG(args.in_queue + i) : (VertexId)args.g.part.Global((long long)i);
+    }
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+        deg[r] = 0; first[r] = 0;
+        if (item[r] >= 0 && (long long)item[r] < args.g.nodes) {
+            const long long row = args.g.part.Local(item[r]);
+            const SizeT a = args.g.row_offsets[row], b = args.g.row_offsets[row + 1];
+            first[r] = a; deg[r] = (ScanT)(b - a);
+        }
+    }
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+        const unsigned long long i = (unsigned long long)r * T + threadIdx.x;
+        if ((unsigned long long)r * T >= in_len) break;         // uniform: no items in this round or later
+        ScanT total;
+        const ScanT excl = running + util::BlockExclusiveSum<T>(deg[r], ss.warp, total);
+        running += total;
+        if (i < in_len) { ss.scanned[i] = excl; ss.row_start[i] = first[r]; }
+    }
+    if (threadIdx.x == 0) ss.scanned[in_len] = running;
+    __syncthreads();
+    if (cta == 0 && threadIdx.x == 0) slot_out->scan_total = running;
+    LocalScan<SizeT> scan = {ss.scanned, ss.row_start, (long long)in_len};
+    ExpandTilesFrom<Policy, Problem, Functor>(ds, args, scan, running, sm, in_len, slot_out, cta, num_ctas);
 }
 
 template <typename Policy, typename Problem, typename Functor>

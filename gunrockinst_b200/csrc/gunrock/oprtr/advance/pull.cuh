@@ -58,6 +58,8 @@ struct PullArgs {
     unsigned       *visited;                // global bitmap; this device updates its own words
     const unsigned *candidates;             // optional, local words: 1 = vertex has in-edges
     const VertexId *head;                   // optional, per local row: first entry of its list (-1: empty)
+    unsigned long long *tickets;            // optional: kTicketCounters zeroed counters, kTicketStride words apart
+                                            // (dynamic chunk hand-out; NULL: static stride)
     const SizeT    *fwd_row_offsets;        // forward (out-edge) offsets for the degree sum; NULL: use g
     VertexId       *out_queue;              // optional: also enqueue found vertices
     unsigned long long out_cap;
@@ -70,6 +72,8 @@ struct PullArgs {
 constexpr int kChunkWords = 8;                  // bitmap words a warp sweeps at a time
 constexpr int kChunkVerts = kChunkWords * 32;   // ... = 256 vertices, so list entries fit a byte
 constexpr int kChunkPerLane = kChunkVerts / 32;
+constexpr int kTicketCounters = 16;             // chunk tickets are drawn from 16 counters on 16 different L2 lines:
+constexpr int kTicketStride   = 16;             // one counter would serialise ~16K atomics per sweep at scale 22
 
 template <typename Policy>
 struct SweepStorage {
@@ -96,6 +100,7 @@ __device__ __forceinline__ void Sweep(
     typedef typename Policy::SizeT    SizeT;
     constexpr int THREADS = Policy::THREADS;
     constexpr int SERIAL_LIMIT = 8, U = kChunkPerLane;
+    static_assert(sizeof(VertexId) == 4, "the sweep fetches neighbour ids as aligned groups of four 32-bit words");
     constexpr bool NEED_SRC = Problem::MARK_PREDECESSORS;
 
     const int lane = util::LaneId();
@@ -132,7 +137,16 @@ __device__ __forceinline__ void Sweep(
         }
     };
 
-    for (long long c = first_chunk; c < num_chunks; c += chunk_stride) {
+    // chunks: the first one by position, the following ones by ticket (chunks differ a lot in cost and
+    // 16384 chunks over 4736 resident warps is 3 or 4 each: a static stride left 15 % of the warp time
+    // waiting at the final barrier); the ticket for the next chunk is drawn before the current one is
+    // processed, so its round trip is hidden
+    long long c = first_chunk;
+    const int my_counter = (int)(first_chunk & (kTicketCounters - 1));
+    unsigned long long *counter = args.tickets ? args.tickets + my_counter * kTicketStride : nullptr;
+    while (c < num_chunks) {
+        unsigned long long ticket = 0;
+        if (lane == 0 && counter) ticket = atomicAdd(counter, 1ull);
         // ---- 1. scan ---------------------------------------------------------------------------
         const long long w0 = c * kChunkWords, w = w0 + my_word;
         unsigned vis = 0xffffffffu, todo = 0;
@@ -148,6 +162,8 @@ __device__ __forceinline__ void Sweep(
         const unsigned total = __shfl_sync(util::kFullMask, incl, 31);
         if (total == 0) {                                       // uniform across the warp
             if ((lane & 3) == 0 && w < num_words) args.frontier_out[seg + w] = 0;
+            c = counter ? chunk_stride + (long long)__shfl_sync(util::kFullMask, ticket, 0) * kTicketCounters + my_counter
+                        : c + chunk_stride;
             continue;
         }
         {
@@ -222,12 +238,14 @@ __device__ __forceinline__ void Sweep(
                 }
                 k = begin + 1;
                 const long long lim = (end - begin > SERIAL_LIMIT) ? begin + SERIAL_LIMIT : end;
+                // (measured: fetching these as aligned groups of four, or four probes per step, is slower --
+                //  the level is bound by L1 wavefronts, one per lane per distinct line, not by latency)
                 while (k < lim) {
                     const VertexId x = util::LoadStream(args.g.col_indices + k);
                     if (util::BitTest(args.frontier_in, ds.BitPos(x))) { found = true; parent = x; epos = k; ++k; break; }
                     ++k;
                 }
-                my_edges += (unsigned long long)(k - begin - 1);
+                my_edges += (unsigned long long)(k - begin - 1);    // entries an early-exit walk looks at
             }
             unsigned rest = __ballot_sync(util::kFullMask, act && !found && k < end);
             while (rest) {
@@ -265,6 +283,8 @@ __device__ __forceinline__ void Sweep(
             my_found += (unsigned)__popc(fm);
         }
         __syncwarp();                                           // the lists are rewritten by the next chunk
+        c = counter ? chunk_stride + (long long)__shfl_sync(util::kFullMask, ticket, 0) * kTicketCounters + my_counter
+                    : c + chunk_stride;
     }
     BlockAccumulate<THREADS>(my_edges,  sm.red, &slot_out->edges);
     BlockAccumulate<THREADS>(my_degree, sm.red, &slot_out->out_degree);

@@ -29,13 +29,19 @@ struct WorkProgress {
     static const int kSlots = 4;
     util::DeviceArray<LevelCounters> d_slots;
     util::PinnedArray<LevelCounters> h_slot;
+    // two sets (by level parity) of chunk-ticket counters for the pull sweep, each counter on its own line
+    static const int kTicketWords = 16 * 16;
+    util::DeviceArray<unsigned long long> d_tickets;
 
     cudaError_t Setup(cudaStream_t s)
     {
         GR_TRY(d_slots.Allocate(kSlots));
         GR_TRY(h_slot.Allocate(kSlots));
+        GR_TRY(d_tickets.Allocate(2 * kTicketWords));
+        GR_TRY(d_tickets.Zero(s));
         return d_slots.Zero(s);
     }
+    unsigned long long *Tickets(long long level) const { return d_tickets.ptr + (level & 1) * kTicketWords; }
     __host__ LevelCounters *Slot(long long queue_index) const { return d_slots.ptr + (queue_index & (kSlots - 1)); }
 
     // host view of the slot a kernel with this queue_index accumulated into

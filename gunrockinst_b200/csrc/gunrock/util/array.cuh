@@ -4,19 +4,135 @@
 // Problem::Init / Enactor::Enact (e.g. app/problem_base.cuh:279-303,
 // app/bfs/bfs_enactor.cuh:254-258): every buffer is allocated once, outside
 // any timed region, and grown geometrically if a later Reset needs more.
+//
+// Behind both sits a block cache: a released buffer is kept (per device, per size class) and
+// handed to the next request of that class, so a caller that goes through the reference's
+// one-shot entry points (gunrock_bfs_func & co.: upload, run, download, tear down -- every
+// call) pays cudaMalloc / cudaFree / cudaHostAlloc once per size, not once per call.  On a
+// scale-22 graph those calls were 9 of the 23 ms of gunrock_bfs_func.  GRB_POOL=0 turns the
+// cache off; grb_release_cached_memory() empties it.
 #pragma once
 #include <cstddef>
 #include <cstdint>
+#include <cstdlib>
+#include <map>
+#include <mutex>
+#include <utility>
+#include <vector>
 #include "error.cuh"
 
 namespace gunrock {
 namespace util {
+
+class BlockCache {
+  public:
+    static BlockCache &Device() { static BlockCache *c = new BlockCache(false); return *c; }   // never destroyed:
+    static BlockCache &Pinned() { static BlockCache *c = new BlockCache(true);  return *c; }   // outlives the runtime
+
+    // bytes -> size class: at most 12.5 % above the request, so few distinct classes exist
+    static size_t Class(size_t bytes)
+    {
+        if (bytes <= 512) return 512;
+        int top = 63;
+        while (!((bytes >> top) & 1)) --top;
+        const size_t step = (size_t)1 << (top - 3);
+        return (bytes + step - 1) & ~(step - 1);
+    }
+
+    cudaError_t Take(size_t bytes, void **out, size_t *got)
+    {
+        const size_t cls = Class(bytes);
+        int dev = 0;
+        if (!pinned_) cudaGetDevice(&dev);
+        if (enabled_) {
+            std::lock_guard<std::mutex> lock(mu_);
+            auto it = free_.find(std::make_pair(dev, cls));
+            if (it != free_.end() && !it->second.empty()) {
+                *out = it->second.back();
+                it->second.pop_back();
+                cached_ -= cls;
+                *got = cls;
+                return cudaSuccess;
+            }
+        }
+        cudaError_t e = Raw(out, cls);
+        if (e == cudaErrorMemoryAllocation) {       // give the cache back to the driver and retry once
+            cudaGetLastError();
+            Trim();
+            e = Raw(out, cls);
+        }
+        *got = cls;
+        return e;
+    }
+
+    void Give(void *p, size_t cls, int dev)
+    {
+        if (!p) return;
+        if (enabled_) {
+            std::lock_guard<std::mutex> lock(mu_);
+            if (cached_ + cls <= Limit()) {
+                free_[std::make_pair(pinned_ ? 0 : dev, cls)].push_back(p);
+                cached_ += cls;
+                return;
+            }
+        }
+        Free(p, dev);
+    }
+
+    void Trim()
+    {
+        std::lock_guard<std::mutex> lock(mu_);
+        for (auto &kv : free_)
+            for (void *p : kv.second) Free(p, kv.first.first);
+        free_.clear();
+        cached_ = 0;
+    }
+    size_t CachedBytes() { std::lock_guard<std::mutex> lock(mu_); return cached_; }
+
+  private:
+    explicit BlockCache(bool pinned) : pinned_(pinned)
+    {
+        const char *e = getenv("GRB_POOL");
+        enabled_ = !(e && e[0] == '0');
+    }
+    cudaError_t Raw(void **out, size_t bytes)
+    {
+        return pinned_ ? cudaHostAlloc(out, bytes, cudaHostAllocDefault) : cudaMalloc(out, bytes);
+    }
+    void Free(void *p, int dev)
+    {
+        if (pinned_) { cudaFreeHost(p); return; }
+        int cur = 0;
+        cudaGetDevice(&cur);
+        if (cur != dev) cudaSetDevice(dev);
+        cudaFree(p);
+        if (cur != dev) cudaSetDevice(cur);
+    }
+    size_t Limit()
+    {
+        if (limit_ == 0) {
+            if (pinned_) limit_ = (size_t)1 << 30;
+            else {
+                size_t free_b = 0, total_b = 0;
+                limit_ = (cudaMemGetInfo(&free_b, &total_b) == cudaSuccess && total_b) ? total_b / 2 : ((size_t)8 << 30);
+            }
+        }
+        return limit_;
+    }
+    bool   pinned_, enabled_ = true;
+    size_t cached_ = 0, limit_ = 0;
+    std::mutex mu_;
+    std::map<std::pair<int, size_t>, std::vector<void *>> free_;
+};
 
 template <typename T>
 struct DeviceArray {
     T     *ptr  = nullptr;
     size_t size = 0;   // elements in use
     size_t cap  = 0;   // elements allocated
+    size_t block_ = 0; // bytes of the cached block behind ptr
+    int    device_ = 0;
+    static const size_t kPad = 16;
 
     DeviceArray() = default;
     DeviceArray(const DeviceArray &) = delete;
@@ -28,17 +144,20 @@ struct DeviceArray {
     {
         if (n > cap) {
             Release();
-            size_t bytes = (n ? n : 1) * sizeof(T);
-            GR_TRY(cudaMalloc((void **)&ptr, bytes));
-            cap = n ? n : 1;
+            // kPad bytes beyond the last element stay readable: kernels fetch aligned 16-byte groups
+            size_t bytes = (n ? n : 1) * sizeof(T) + kPad, got = 0;
+            cudaGetDevice(&device_);
+            GR_TRY(BlockCache::Device().Take(bytes, (void **)&ptr, &got));
+            block_ = got;
+            cap = (got - kPad) / sizeof(T);
         }
         size = n;
         return cudaSuccess;
     }
     void Release()
     {
-        if (ptr) cudaFree(ptr);
-        ptr = nullptr; size = cap = 0;
+        if (ptr) BlockCache::Device().Give(ptr, block_, device_);
+        ptr = nullptr; size = cap = 0; block_ = 0;
     }
     cudaError_t Zero(cudaStream_t s) { return size ? cudaMemsetAsync(ptr, 0, size * sizeof(T), s) : cudaSuccess; }
     cudaError_t FromHost(const T *h, size_t n, cudaStream_t s)
@@ -67,12 +186,15 @@ struct PinnedArray {
     {
         if (n > size) {
             Release();
-            GR_TRY(cudaHostAlloc((void **)&ptr, (n ? n : 1) * sizeof(T), cudaHostAllocDefault));
+            size_t got = 0;
+            GR_TRY(BlockCache::Pinned().Take((n ? n : 1) * sizeof(T), (void **)&ptr, &got));
+            block_ = got;
             size = n;
         }
         return cudaSuccess;
     }
-    void Release() { if (ptr) cudaFreeHost(ptr); ptr = nullptr; size = 0; }
+    void Release() { if (ptr) BlockCache::Pinned().Give(ptr, block_, 0); ptr = nullptr; size = 0; block_ = 0; }
+    size_t block_ = 0;
 };
 
 }  // namespace util

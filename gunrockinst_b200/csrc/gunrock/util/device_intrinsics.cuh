@@ -37,6 +37,15 @@ template <> __device__ __forceinline__ float LoadStream<float>(const float *p)
     float v; asm volatile("ld.global.nc.L1::no_allocate.f32 %0, [%1];" : "=f"(v) : "l"(p)); return v;
 }
 
+// four consecutive ints in one request (p must be 16-byte aligned)
+__device__ __forceinline__ int4 LoadStream4(const int *p)
+{
+    int4 v;
+    asm volatile("ld.global.nc.L1::no_allocate.v4.s32 {%0, %1, %2, %3}, [%4];"
+                 : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p));
+    return v;
+}
+
 // data another SM may be updating in this same launch (labels, bitmaps, ranks):
 // read at L2, never from a stale L1 line
 template <typename T> __device__ __forceinline__ T LoadCG(const T *p) { return __ldcg(p); }

@@ -6,6 +6,12 @@
 #include "../../../include/gunrock/gunrock.h"
 #include "bfs_runner.cuh"
 #include "source_select.h"
+#include <chrono>
+
+static double grb_wall_ms()
+{
+    return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now().time_since_epoch()).count();
+}
 
 struct grb_bfs_s {
     grb_graph_t graph = nullptr;
@@ -39,8 +45,7 @@ extern "C" int grb_bfs_run_many(grb_bfs_t ctx, const int32_t *srcs, int32_t coun
 {
     if (!ctx || (!srcs && count > 0)) return (int)cudaErrorInvalidValue;
     GRB_TRY(cudaSetDevice(ctx->graph->device()));
-    for (int32_t i = 0; i < count; ++i)
-        GRB_TRY(ctx->runner->Run(srcs[i], nullptr, nullptr, stats ? stats + i : nullptr));
+    GRB_TRY(ctx->runner->RunMany(srcs, count, stats));
     return 0;
 }
 
@@ -86,9 +91,13 @@ extern "C" void gunrock_bfs_func(struct GunrockGraph *graph_out, const struct Gu
     const int *h_off = (const int *)graph_in->row_offsets;
     const int src = grb_pick_source(configs.src_mode, configs.src_node, n, h_off);
 
+    // GRB_TRACE=1: wall-clock split of the call on stderr (upload / context / search+download / teardown)
+    const bool trace = getenv("GRB_TRACE") != nullptr;
+    const double t_begin = trace ? grb_wall_ms() : 0.0;
     grb_graph_t g = nullptr;
     if (grb_graph_from_host(configs.device, n, m, h_off, 4, (const int32_t *)graph_in->col_indices, nullptr, 0, 4, &g))
         return;
+    const double t_upload = trace ? grb_wall_ms() : 0.0;
     grb_bfs_config cfg;
     memset(&cfg, 0, sizeof(cfg));
     cfg.mark_pred = configs.mark_pred; cfg.idempotence = configs.idempotence;
@@ -96,6 +105,7 @@ extern "C" void gunrock_bfs_func(struct GunrockGraph *graph_out, const struct Gu
     grb_bfs_t ctx = nullptr;
     if (grb_bfs_create(g, &cfg, &ctx)) { grb_graph_destroy(g); return; }
 
+    const double t_ctx = trace ? grb_wall_ms() : 0.0;
     int *h_labels = (int *)malloc(sizeof(int) * (size_t)(n > 0 ? n : 1));     // caller frees (bfs_app.cu:165,211)
     int *h_preds = configs.mark_pred ? (int *)malloc(sizeof(int) * (size_t)(n > 0 ? n : 1)) : nullptr;
     grb_stats st;
@@ -113,8 +123,13 @@ extern "C" void gunrock_bfs_func(struct GunrockGraph *graph_out, const struct Gu
         free(h_labels);
         graph_out->node_values = nullptr;
     }
+    const double t_run = trace ? grb_wall_ms() : 0.0;
     free(h_preds);                          // the C API never returns BFS predecessors (bfs_app.cu:166-170,227)
     grb_bfs_destroy(ctx);
     grb_graph_destroy(g);
     cudaDeviceSynchronize();                // bfs_app.cu:229
+    if (trace)
+        fprintf(stderr, "[grb trace] gunrock_bfs_func: upload %.3f ms, context %.3f ms, search+download %.3f ms "
+                        "(device %.3f ms), teardown %.3f ms\n", t_upload - t_begin, t_ctx - t_upload, t_run - t_ctx,
+                (double)(st.elapsed_ms + st.reset_ms), grb_wall_ms() - t_run);
 }

@@ -10,6 +10,7 @@
 struct BfsRunnerBase {
     virtual ~BfsRunnerBase() {}
     virtual cudaError_t Run(int src, int *labels_host, int *preds_host, grb_stats *stats) = 0;
+    virtual cudaError_t RunMany(const int *srcs, int count, grb_stats *stats) = 0;
     virtual void *DeviceLabels() = 0;
     virtual const std::vector<gunrock::app::bfs::LevelRecord> &Levels() = 0;
 };
@@ -78,6 +79,48 @@ struct BfsRunner : BfsRunnerBase {
             stats->push_levels = enactor.enactor_stats.push_levels;
             stats->pull_levels = enactor.enactor_stats.pull_levels;
             stats->gpu_launches = enactor.enactor_stats.launches;
+            stats->reserved = enactor.kernel_us;        // persistent loop: microseconds between the kernel's first and last instruction
+        }
+        return cudaSuccess;
+    }
+    // `count` searches; when the persistent kernel can take them, batches of up to kBatch sources run
+    // as ONE launch each (no launch, copy or host synchronisation between two searches)
+    cudaError_t RunMany(const int *srcs, int count, grb_stats *stats) override
+    {
+        using gunrock::app::VERTEX_FRONTIERS;
+        const int kBatch = 256;
+        int done = 0;
+        while (done < count) {
+            bool batch = ready && !IDEM && !opt.record_levels && count - done > 1;
+            int take = count - done < kBatch ? count - done : kBatch;
+            for (int i = 0; batch && i < take; ++i) batch = enactor.FusesReset(srcs[done + i], &problem, opt);
+            if (!batch) {
+                GR_TRY(Run(srcs[done], nullptr, nullptr, stats ? stats + done : nullptr));
+                ++done;
+                continue;
+            }
+            if constexpr (!IDEM) {
+                std::vector<gunrock::app::bfs::PersistentSummary> sums((size_t)take);
+                GR_TRY(problem.Reset(srcs[done + take - 1], VERTEX_FRONTIERS, queue_sizing, true));
+                GR_TRY(enactor.Enact(&problem, srcs[done + take - 1], opt, true, srcs + done, take, sums.data()));
+                for (int i = 0; stats && i < take; ++i) {
+                    grb_stats *st = stats + done + i;
+                    memset(st, 0, sizeof(*st));
+                    st->elapsed_ms = (float)((double)(sums[i].ns_kernel - sums[i].ns_reset) * 1e-6);   // device-side spans
+                    st->reset_ms = (float)((double)sums[i].ns_reset * 1e-6);
+                    st->iterations = (int64_t)sums[i].levels;
+                    st->edges_visited = (int64_t)sums[i].edges_visited;
+                    st->edges_inspected = sums[i].edges_inspected;
+                    st->total_queued = sums[i].total_queued;
+                    st->nodes_visited = (int64_t)sums[i].total_queued;
+                    st->algo_bytes = sums[i].algo_bytes;
+                    st->push_levels = (int32_t)sums[i].push_levels;
+                    st->pull_levels = (int32_t)sums[i].pull_levels;
+                    st->gpu_launches = i == 0 ? 1 : 0;             // one kernel for the whole batch
+                    st->reserved = (int32_t)(sums[i].ns_kernel / 1000);
+                }
+            }
+            done += take;
         }
         return cudaSuccess;
     }

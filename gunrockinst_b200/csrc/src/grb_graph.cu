@@ -7,6 +7,12 @@
 
 extern "C" const char *grb_version(void) { return "gunrockinst_b200 0.1 (sm_100a)"; }
 
+extern "C" void grb_release_cached_memory(void)
+{
+    gunrock::util::BlockCache::Device().Trim();
+    gunrock::util::BlockCache::Pinned().Trim();
+}
+
 extern "C" int grb_device_count(void)
 {
     int count = 0;

@@ -32,6 +32,9 @@ typedef struct grb_graph_s *grb_graph_t;
 /* ---- library / device ----------------------------------------------------- */
 const char *grb_version(void);
 int grb_device_count(void);              /* 0 when no CUDA device is usable */
+/* the library keeps released device / pinned buffers for reuse (GRB_POOL=0 disables that);
+ * this hands everything cached back to the driver */
+void grb_release_cached_memory(void);
 
 /* ---- resident graphs --------------------------------------------------------
  * stands in for ProblemBase::Init's upload (gunrock/app/problem_base.cuh:226-342)
@@ -96,7 +99,7 @@ typedef struct {
 /* per-level trace of the last BFS on a handle (record_levels != 0) */
 typedef struct {
     int32_t  level;
-    int32_t  kind;              /* 0 push-TWC, 1 pull, 2 push-LB                     */
+    int32_t  kind;              /* 0 push-TWC, 1 pull, 2 push-LB, 3 push-LB (private scan) */
     uint64_t frontier, edges, discovered, candidates;
     float    ms;
     float    switch_ms;         /* part of ms spent converting queue <-> bitmap        */

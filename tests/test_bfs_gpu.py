@@ -152,3 +152,34 @@ def test_repeated_runs_reuse_context(gr, orc):
     for src in range(40):
         labels, _, _ = bfs.run(src)
         assert np.array_equal(labels, orc.bfs(ro, co, src))
+
+
+@pytest.mark.parametrize("mode", [dict(direction_optimized=True), dict(), dict(mark_pred=True, direction_optimized=True),
+                                  dict(direction_optimized=True, host_loop=True), dict(idempotence=True)],
+                         ids=["dobfs", "push", "dobfs-pred", "dobfs-host-loop", "idempotent"])
+def test_run_many_batches_match_single_runs(gr, orc, mode):
+    """grb_bfs_run_many: a batch of searches inside one launch (persistent loop) gives, search by
+    search, the statistics of separate runs, and leaves the last search's depths on the device"""
+    import ctypes as C
+    ro, co = rmat_graph(orc, 15)
+    n = ro.size - 1
+    g = gr.Graph.from_csr(ro, co, symmetric=True)
+    bfs = gr.Bfs(g, **mode)
+    bfs.run(0)                                              # first run sets the context up
+    srcs = [0, 7, n - 1, 123, 0, 4242, n + 5, 99]           # one out-of-range source: an empty search
+    many = bfs.run_many(srcs)
+    for s, st in zip(srcs, many):
+        want = orc.bfs(ro, co, s) if s < n else np.full(n, -1, np.int32)
+        assert st["edges_visited"] == orc.edges_visited(ro, want), (s, mode)
+        assert st["iterations"] == (int(want.max()) + 1 if s < n else 0)
+    # depths of the last search are what the device holds
+    labels = np.empty(n, np.int32)
+    import torch
+    ptr = bfs.device_labels()
+    t = torch.as_tensor(gr.partitioned._RawCuda(ptr, n, "<i4"), device="cuda") if hasattr(gr, "partitioned") else None
+    if t is None:
+        from gunrockinst_b200 import partitioned
+        t = torch.as_tensor(partitioned._RawCuda(ptr, n, "<i4"), device="cuda")
+    assert np.array_equal(t.cpu().numpy(), orc.bfs(ro, co, srcs[-1]))
+    bfs.close()
+    g.close()

@@ -356,17 +356,21 @@ def main():
     ap.add_argument("--cpu-seconds", type=float, default=12.0)
     ap.add_argument("--ref-edge-cap", type=int, default=20_000_000)
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--exchange", default="peer", choices=["peer", "nccl"],
+                    help="partitioned runs: peer-memory stores over NVLink (default) or NCCL collectives")
+    ap.add_argument("--partitioned", action="store_true",
+                    help="use the partitioned driver even on one device (the 1-device point of a scale-27 scaling table)")
     args = ap.parse_args()
     world = env_int("WORLD_SIZE", 1)
     rank = env_int("RANK", 0)
     if world > 1:
         args.gpus = world
     if args.scale <= 0:
-        args.scale = 22 if args.gpus == 1 else 27
+        args.scale = 22 if (args.gpus == 1 and not args.partitioned) else 27
     if args.impl == "reference":
         run_reference(args, rank, world)
         return
-    if args.gpus == 1:
+    if args.gpus == 1 and not args.partitioned:
         run_single(args)
     else:
         from gunrockinst_b200 import partitioned

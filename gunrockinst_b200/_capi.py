@@ -66,6 +66,21 @@ class MgLevel(C.Structure):
                 ("overflow", C.c_uint64), ("gpu_launches", C.c_uint64)]
 
 
+class MgStats(C.Structure):
+    _fields_ = [("elapsed_ms", C.c_double), ("iterations", C.c_int64), ("push_levels", C.c_int64),
+                ("pull_levels", C.c_int64), ("gpu_launches", C.c_int64), ("edges_visited", C.c_uint64),
+                ("edges_inspected", C.c_uint64), ("exchange_bytes", C.c_uint64), ("nodes_visited", C.c_uint64)]
+
+
+class MgTrace(C.Structure):
+    _fields_ = [("level", C.c_int32), ("kind", C.c_int32), ("frontier", C.c_uint64), ("discovered", C.c_uint64),
+                ("edges", C.c_uint64), ("max_edges", C.c_uint64), ("exchange_bytes", C.c_uint64),
+                ("compute_ms", C.c_float), ("exchange_ms", C.c_float)]
+
+
+IPC_HANDLE_BYTES, MG_PEER_BUFFERS = 64, 4
+
+
 # gunrock.h (reference ABI, gunrock/gunrock.h:51-99)
 class GunrockGraph(C.Structure):
     _fields_ = [("num_nodes", C.c_size_t), ("num_edges", C.c_size_t),
@@ -152,6 +167,10 @@ def lib():
     sig("grb_mgbfs_stream", C.c_int, [p, pp])
     sig("grb_mgbfs_labels", C.c_int, [p, p])
     sig("grb_mgbfs_destroy", None, [p])
+    sig("grb_mgbfs_peer_export", C.c_int, [p, p])
+    sig("grb_mgbfs_peer_import", C.c_int, [p, C.c_int, p, u64])
+    sig("grb_mgbfs_run_peer", C.c_int, [p, i32, C.c_int, dbl, dbl, C.c_int, C.POINTER(MgStats)])
+    sig("grb_mgbfs_peer_levels", C.c_int, [p, C.POINTER(MgTrace), i32, C.POINTER(i32)])
     for name in ("gunrock_bfs_func", "gunrock_cc_func", "gunrock_bc_func"):
         sig(name, None, [C.POINTER(GunrockGraph), C.POINTER(GunrockGraph), GunrockConfig, GunrockDataType])
     sig("gunrock_topk_func", None, [C.POINTER(GunrockGraph), p, p, p, C.POINTER(GunrockGraph),

@@ -23,7 +23,9 @@
 // harness all-gathers, so one collective + one host read per level carries the frontier
 // length, its degree sum and the edges inspected of every device.
 #pragma once
+#include <vector>
 #include "bfs_enactor.cuh"
+#include "mgbfs_p2p.cuh"
 
 namespace gunrock {
 namespace app {
@@ -52,7 +54,7 @@ struct MgPushFunctor {
 // it as this device's segment of the frontier map and enqueue it (CTA-aggregated)
 template <typename VertexId, typename SizeT, typename DataSlice, int THREADS>
 __global__ void __launch_bounds__(THREADS)
-AbsorbDenseKernel(const unsigned *recv, int parts, unsigned *visited, unsigned *frontier_out, VertexId *queue,
+AbsorbDenseKernel(unsigned *recv, int parts, bool consume, unsigned *visited, unsigned *frontier_out, VertexId *queue,
                   unsigned long long cap, const SizeT *row_offsets, oprtr::LevelCounters *slot, DataSlice ds)
 {
     __shared__ unsigned s_warp[THREADS / 32 + 1];
@@ -67,7 +69,13 @@ AbsorbDenseKernel(const unsigned *recv, int parts, unsigned *visited, unsigned *
         unsigned bits = 0;
         if (w < words) {
             unsigned acc = 0;
-            for (int p = 0; p < parts; ++p) acc |= util::LoadStream(recv + (long long)p * words + w);
+            for (int p = 0; p < parts; ++p) {
+                const unsigned x = util::LoadStream(recv + (long long)p * words + w);
+                // peer-memory exchange: senders only store the lines that hold discoveries, so a
+                // consumed word is cleared here for the next level
+                if (consume && x) recv[(long long)p * words + w] = 0;
+                acc |= x;
+            }
             const unsigned vis = visited[seg + w];
             bits = acc & ~vis;
             frontier_out[seg + w] = bits;
@@ -143,10 +151,11 @@ class MGBFSEnactor : public EnactorBase {
     cudaError_t ZeroCounters() { return cudaMemsetAsync(Counters(), 0, sizeof(oprtr::LevelCounters), stream); }
 
     // push level, part 1: expand the local queue into the dense discovery map
-    cudaError_t Push(Problem *problem, VertexId level, unsigned long long queue_len, unsigned long long edges_hint)
+    cudaError_t Push(Problem *problem, VertexId level, unsigned long long queue_len, unsigned long long edges_hint,
+                     bool clear_next = true)
     {
         GR_TRY(ZeroCounters());
-        GR_TRY(problem->next_map.Zero(stream));
+        if (clear_next) GR_TRY(problem->next_map.Zero(stream));
         if (queue_len == 0) return cudaSuccess;
         DataSlice ds = problem->MakeDataSlice(level);
         oprtr::advance::Args<VertexId, SizeT> a;
@@ -161,12 +170,12 @@ class MGBFSEnactor : public EnactorBase {
                                                                                  edges_hint, stream);
     }
     // push level, part 2 (after the all-to-all of the next map into recv_map)
-    cudaError_t Absorb(Problem *problem, VertexId level, int cur_out)
+    cudaError_t Absorb(Problem *problem, VertexId level, int cur_out, bool consume = false)
     {
         DataSlice ds = problem->MakeDataSlice(level);
         const unsigned long long words = (unsigned long long)((problem->graph->local_nodes + 31) >> 5);
         AbsorbDenseKernel<VertexId, SizeT, DataSlice, 256><<<util::FillGrid(words), 256, 0, stream>>>(
-            problem->recv_map.ptr, problem->graph->part.Parts(), problem->visited_mask.ptr,
+            problem->recv_map.ptr, problem->graph->part.Parts(), consume, problem->visited_mask.ptr,
             problem->frontier_map[cur_out].ptr, problem->frontier_queues[in_sel ^ 1].ptr,
             problem->frontier_elements[in_sel ^ 1], problem->graph->row_offsets.ptr, Counters(), ds);
         GR_TRY(cudaGetLastError());
@@ -175,7 +184,7 @@ class MGBFSEnactor : public EnactorBase {
         return cudaSuccess;
     }
     // pull level: reads the (all-gathered) frontier map `cur`, writes this device's segment of map cur^1
-    cudaError_t Pull(Problem *problem, VertexId level, int cur)
+    cudaError_t Pull(Problem *problem, VertexId level, int cur, const PeerTable *peers = nullptr)
     {
         GR_TRY(ZeroCounters());
         DataSlice ds = problem->MakeDataSlice(level);
@@ -190,6 +199,10 @@ class MGBFSEnactor : public EnactorBase {
         pa.tickets      = nullptr;
         pa.fwd_row_offsets = g.symmetric ? nullptr : g.row_offsets.ptr;
         pa.out_queue = nullptr; pa.out_cap = 0;
+        pa.peers = 0;
+        if (peers)
+            for (int p = 0; p < peers->parts; ++p)
+                if (p != peers->rank) pa.peer_out[pa.peers++] = peers->map[cur ^ 1][p];
         pa.slots = work_progress.d_slots.ptr; pa.queue_index = 0; pa.iteration = level;
         ++enactor_stats.launches;
         return oprtr::advance::LaunchPullKernel<PullPolicy, Problem, PullFunctor>(dev, ds, pa, stream);
@@ -225,6 +238,225 @@ class MGBFSEnactor : public EnactorBase {
             problem->frontier_elements[in_sel], scratch, ds);
         ++enactor_stats.launches;
         return util::GRError(cudaGetLastError(), "BitmapToQueueKernel failed", __FILE__, __LINE__);
+    }
+
+    // ------------------------------------------------------------------------------------------
+    // peer-memory exchange (mgbfs_p2p.cuh): the whole search as one native host loop
+    // ------------------------------------------------------------------------------------------
+    struct LevelTrace {
+        int level, kind;                    // kind: 0 push, 1 pull
+        unsigned long long frontier, discovered, edges, max_edges, exchange_bytes;
+        float compute_ms, exchange_ms;
+    };
+    struct SearchStats {
+        double elapsed_ms = 0;
+        long long iterations = 0, push_levels = 0, pull_levels = 0, launches = 0;
+        unsigned long long edges_visited = 0, edges_inspected = 0, exchange_bytes = 0, nodes_visited = 0;
+    };
+
+    PeerTable peers;
+    util::DeviceArray<Mailbox> mailbox;
+    util::DeviceArray<unsigned long long> sent_words;
+    util::PinnedArray<oprtr::LevelCounters> h_all;
+    util::PinnedArray<unsigned long long> h_status;
+    unsigned long long epoch = 0, bar_count = 0, global_edges = 0;
+    bool p2p_ready = false;
+    std::vector<LevelTrace> trace;
+    std::vector<cudaEvent_t> events;
+
+    unsigned long long SegWords(Problem *problem) const { return (unsigned long long)((problem->graph->local_nodes + 31) >> 5); }
+
+    // own entries of the peer table; the remote ones are filled in by the C layer (IPC mappings)
+    cudaError_t SetupPeers(Problem *problem)
+    {
+        GR_TRY(mailbox.Allocate(1));
+        GR_TRY(mailbox.Zero(stream));
+        GR_TRY(sent_words.Allocate(1));
+        GR_TRY(sent_words.Zero(stream));
+        GR_TRY(h_all.Allocate(kMaxPeers));
+        GR_TRY(h_status.Allocate(1));
+        peers = PeerTable();
+        peers.parts = problem->graph->part.Parts();
+        peers.rank = problem->graph->part.rank;
+        if (peers.parts > kMaxPeers) return util::GRError(cudaErrorInvalidValue, "peer exchange supports up to 8 devices", __FILE__, __LINE__);
+        const int r = peers.rank;
+        peers.mailbox[r] = mailbox.ptr;
+        peers.map[0][r] = problem->frontier_map[0].ptr;
+        peers.map[1][r] = problem->frontier_map[1].ptr;
+        peers.recv[r] = problem->recv_map.ptr;
+        epoch = bar_count = 0;
+        p2p_ready = (peers.parts == 1);
+        return cudaStreamSynchronize(stream);
+    }
+
+    cudaError_t ExchangeCounters()
+    {
+        ++epoch;
+        *h_status.ptr = 0;
+        ExchangeCountersKernel<<<1, 32 * kMaxPeers, 0, stream>>>(peers, Counters(), epoch, h_all.ptr, h_status.ptr);
+        GR_TRY(cudaGetLastError());
+        ++enactor_stats.launches;
+        GR_TRY(cudaStreamSynchronize(stream));
+        if (*h_status.ptr != epoch)
+            return util::GRError(cudaErrorLaunchTimeout, "peer exchange timed out (a peer stopped or the ranks diverged)", __FILE__, __LINE__);
+        return cudaSuccess;
+    }
+    cudaError_t PeerBarrier()
+    {
+        if (peers.parts == 1) return cudaSuccess;
+        ++bar_count;
+        PeerBarrierKernel<<<1, 32 * kMaxPeers, 0, stream>>>(peers, bar_count);
+        ++enactor_stats.launches;
+        return cudaGetLastError();
+    }
+    cudaEvent_t Mark(size_t &used)
+    {
+        if (used == events.size()) { cudaEvent_t e; cudaEventCreate(&e); events.push_back(e); }
+        cudaEvent_t e = events[used++];
+        cudaEventRecord(e, stream);
+        return e;
+    }
+    void DestroyEvents() { for (cudaEvent_t e : events) cudaEventDestroy(e); events.clear(); }
+
+    // One direction-optimising search; every rank calls it with the same arguments.  The direction
+    // rule is the one of BFSEnactor (Beamer's alpha / beta on global frontier figures).
+    cudaError_t RunPeer(Problem *problem, VertexId src, bool dopt, double alpha, double beta, bool record, SearchStats *out)
+    {
+        if (!p2p_ready) return util::GRError(cudaErrorNotReady, "peer mappings have not been imported", __FILE__, __LINE__);
+        typename Problem::Base::Graph &g = *problem->graph;
+        const int P = peers.parts;
+        const unsigned long long seg_words = SegWords(problem);
+        const unsigned long long n = (unsigned long long)g.nodes;
+        size_t used = 0;
+        trace.clear();
+        cudaEvent_t ev_start = Mark(used);
+
+        // ---- reset: no host round trip; the first counter exchange is the barrier behind it
+        GR_TRY(problem->Reset(-1, VERTEX_FRONTIERS, 1.0, true));
+        problem->src = src;
+        in_sel = 0;
+        GR_TRY(ResetBase());
+        if (g.local_nodes) GR_TRY(cudaMemsetAsync(problem->labels.ptr, 0xff, sizeof(VertexId) * (size_t)g.local_nodes, stream));
+        GR_TRY(problem->visited_mask.Zero(stream));
+        GR_TRY(problem->frontier_map[0].Zero(stream));
+        GR_TRY(problem->next_map.Zero(stream));
+        GR_TRY(problem->recv_map.Zero(stream));
+        GR_TRY(sent_words.Zero(stream));
+        unsigned long long sent_so_far = 0;
+        const bool valid = src >= 0 && (unsigned long long)src < n;
+        const bool mine = valid && g.part.Mine(src);
+        {
+            DataSlice ds = problem->MakeDataSlice(0);
+            SeedSourceKernel<VertexId, DataSlice><<<1, 32, 0, stream>>>(ds, src, problem->frontier_queues[0].ptr, problem->frontier_map[0].ptr);
+            SeedCountersKernel<SizeT><<<1, 1, 0, stream>>>(Counters(), g.row_offsets.ptr, mine ? (long long)g.part.Local(src) : -1ll);
+            GR_TRY(cudaGetLastError());
+            enactor_stats.launches += 2;
+        }
+        GR_TRY(ExchangeCounters());
+
+        unsigned long long frontier = 0, frontier_edges = 0;
+        for (int p = 0; p < P; ++p) { frontier += h_all.ptr[p].out_len; frontier_edges += h_all.ptr[p].out_degree; }
+        unsigned long long local_q = h_all.ptr[peers.rank].out_len, local_hint = h_all.ptr[peers.rank].out_degree;
+        unsigned long long unexplored = global_edges > frontier_edges ? global_edges - frontier_edges : 0;
+        unsigned long long edges_visited = frontier_edges, nodes_visited = frontier, inspected = 0, exch_bytes = 0, prev_len = 0;
+        bool pull = false, gathered = false, queue_valid = true;
+        int cur = 0;
+        long long level = 0, push_levels = 0, pull_levels = 0;
+
+        while (frontier > 0) {
+            if (dopt) {
+                if (!pull && (double)frontier_edges > (double)unexplored / alpha) pull = true;
+                else if (pull && frontier < prev_len && (double)frontier < (double)n / beta) pull = false;
+            }
+            cudaEvent_t m0 = 0, m1 = 0, m2 = 0, m3 = 0, m4 = 0;
+            unsigned long long lvl_bytes = 0;
+            if (record) m0 = Mark(used);
+            if (pull) {
+                if (record) m1 = Mark(used);
+                if (!gathered && P > 1) {       // first pull level after push levels: own segment -> every peer
+                    ScatterSegmentKernel<<<util::FillGrid(seg_words >> 2), 256, 0, stream>>>(peers, cur, seg_words);
+                    GR_TRY(cudaGetLastError());
+                    ++enactor_stats.launches;
+                    GR_TRY(PeerBarrier());
+                    lvl_bytes += 4ull * seg_words * (unsigned long long)(P - 1);
+                }
+                if (record) m2 = Mark(used);
+                GR_TRY(MergeVisited(problem, cur));
+                GR_TRY(Pull(problem, (VertexId)level, cur, &peers));      // publishes map cur^1 on every device
+                lvl_bytes += 4ull * seg_words * (unsigned long long)(P - 1);
+                cur ^= 1;
+                queue_valid = false;
+                gathered = true;
+                ++pull_levels;
+            } else {
+                if (!queue_valid) { GR_TRY(MapToQueue(problem, cur)); queue_valid = true; }
+                GR_TRY(Push(problem, (VertexId)level, local_q, local_hint, false));
+                if (record) m1 = Mark(used);
+                ScatterNextKernel<<<util::FillGrid(seg_words * (unsigned long long)P), 256, 0, stream>>>(
+                    peers, problem->next_map.ptr, seg_words, sent_words.ptr);
+                GR_TRY(cudaGetLastError());
+                ++enactor_stats.launches;
+                GR_TRY(PeerBarrier());
+                if (record) m2 = Mark(used);
+                GR_TRY(Absorb(problem, (VertexId)level, cur ^ 1, true));
+                cur ^= 1;
+                gathered = false;
+                ++push_levels;
+            }
+            if (record) m3 = Mark(used);
+            GR_TRY(ExchangeCounters());
+            if (record) m4 = Mark(used);
+            unsigned long long f = 0, fe = 0, ins = 0, max_ins = 0, ovf = 0;
+            for (int p = 0; p < P; ++p) {
+                const oprtr::LevelCounters &c = h_all.ptr[p];
+                f += c.out_len; fe += c.out_degree; ins += c.edges; ovf += c.overflow;
+                if (c.edges > max_ins) max_ins = c.edges;
+            }
+            if (ovf) return util::GRError(cudaErrorInvalidConfiguration, "frontier queue overflow on a partitioned level", __FILE__, __LINE__);
+            if (!pull && record) {  // bytes this device actually sent: the lines of the discovery map that held a bit
+                unsigned long long sw = 0;
+                GR_TRY(cudaMemcpyAsync(&sw, sent_words.ptr, sizeof(sw), cudaMemcpyDeviceToHost, stream));
+                GR_TRY(cudaStreamSynchronize(stream));
+                lvl_bytes += 4ull * (sw - sent_so_far);
+                sent_so_far = sw;
+            }
+            if (record) {
+                LevelTrace t;
+                t.level = (int)level; t.kind = pull ? 1 : 0;
+                t.frontier = frontier; t.discovered = f; t.edges = ins; t.max_edges = max_ins; t.exchange_bytes = lvl_bytes;
+                float a = 0, b = 0, c = 0, d = 0;
+                cudaEventSynchronize(m4);
+                cudaEventElapsedTime(&a, m0, m1); cudaEventElapsedTime(&b, m1, m2);
+                cudaEventElapsedTime(&c, m2, m3); cudaEventElapsedTime(&d, m3, m4);
+                t.compute_ms = a + c; t.exchange_ms = b + d;
+                trace.push_back(t);
+            }
+            prev_len = frontier;
+            frontier = f; frontier_edges = fe;
+            local_q = h_all.ptr[peers.rank].out_len; local_hint = h_all.ptr[peers.rank].out_degree;
+            inspected += ins;
+            unexplored = unexplored > frontier_edges ? unexplored - frontier_edges : 0;
+            edges_visited += frontier_edges;
+            nodes_visited += frontier;
+            exch_bytes += lvl_bytes;
+            ++level;
+        }
+        if (!record && push_levels) {   // push payload of the whole search (the traced path counted it per level)
+            unsigned long long sw = 0;
+            GR_TRY(cudaMemcpyAsync(&sw, sent_words.ptr, sizeof(sw), cudaMemcpyDeviceToHost, stream));
+            GR_TRY(cudaStreamSynchronize(stream));
+            exch_bytes += 4ull * sw;
+        }
+        cudaEvent_t ev_end = Mark(used);
+        GR_TRY(cudaEventSynchronize(ev_end));
+        float ms = 0;
+        cudaEventElapsedTime(&ms, ev_start, ev_end);
+        if (out) {
+            out->elapsed_ms = ms; out->iterations = level; out->push_levels = push_levels; out->pull_levels = pull_levels;
+            out->launches = enactor_stats.launches; out->edges_visited = edges_visited; out->edges_inspected = inspected;
+            out->exchange_bytes = exch_bytes; out->nodes_visited = nodes_visited;
+        }
+        return cudaSuccess;
     }
 };
 

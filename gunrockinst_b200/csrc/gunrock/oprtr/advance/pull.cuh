@@ -63,6 +63,11 @@ struct PullArgs {
     const SizeT    *fwd_row_offsets;        // forward (out-edge) offsets for the degree sum; NULL: use g
     VertexId       *out_queue;              // optional: also enqueue found vertices
     unsigned long long out_cap;
+    // partitioned runs with peer-memory exchange: the same frontier map on the other devices
+    // (NVLink mappings).  Every word this device publishes is also stored there, so the map is
+    // complete everywhere when the level ends and no all-gather pass follows the sweep.
+    unsigned       *peer_out[7] = {};
+    int             peers = 0;
     LevelCounters  *slots;
     long long       queue_index;
     long long       iteration;
@@ -161,7 +166,10 @@ __device__ __forceinline__ void Sweep(
         const unsigned incl = util::WarpInclusiveSum(cnt);
         const unsigned total = __shfl_sync(util::kFullMask, incl, 31);
         if (total == 0) {                                       // uniform across the warp
-            if ((lane & 3) == 0 && w < num_words) args.frontier_out[seg + w] = 0;
+            if ((lane & 3) == 0 && w < num_words) {
+                args.frontier_out[seg + w] = 0;
+                for (int p = 0; p < args.peers; ++p) args.peer_out[p][seg + w] = 0;
+            }
             c = counter ? chunk_stride + (long long)__shfl_sync(util::kFullMask, ticket, 0) * kTicketCounters + my_counter
                         : c + chunk_stride;
             continue;
@@ -279,6 +287,7 @@ __device__ __forceinline__ void Sweep(
         if (lane < kChunkWords && w0 + lane < num_words) {
             const unsigned fm = s_found[lane];
             args.frontier_out[seg + w0 + lane] = fm;
+            for (int p = 0; p < args.peers; ++p) args.peer_out[p][seg + w0 + lane] = fm;
             if (fm) args.visited[seg + w0 + lane] = vis_l | fm;
             my_found += (unsigned)__popc(fm);
         }

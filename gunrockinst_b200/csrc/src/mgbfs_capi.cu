@@ -4,6 +4,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <vector>
 #include "../../../include/gunrock_b200.h"
 #include "graph_handle.cuh"
 #include "../gunrock/app/bfs/mgbfs_enactor.cuh"
@@ -21,6 +22,10 @@ struct MgRunnerBase {
     virtual cudaError_t Labels(int *labels_host) = 0;
     virtual cudaError_t ReadCounters(grb_mg_level *out) = 0;
     virtual int Launches() = 0;
+    virtual cudaError_t PeerExport(unsigned char *handles) = 0;
+    virtual cudaError_t PeerImport(int world, const unsigned char *all, unsigned long long global_edges) = 0;
+    virtual cudaError_t RunPeer(int src, bool dopt, double alpha, double beta, bool record, grb_mg_stats *out) = 0;
+    virtual int PeerLevels(grb_mg_trace *out, int cap) = 0;
 };
 
 template <typename SizeT>
@@ -42,6 +47,8 @@ struct MgRunner : MgRunnerBase {
         GR_TRY(problem.Init(g, s));
         GR_TRY(problem.Reset(-1, gunrock::app::VERTEX_FRONTIERS, 1.0));    // sizes the queues
         GR_TRY(enactor.Setup(&problem, s));
+        GR_TRY(enactor.SetupPeers(&problem));
+        enactor.global_edges = (unsigned long long)g->edges;     // one device; peer import sets the global sum
         return h_counters.Allocate(1);
     }
     cudaError_t Reset(int src, unsigned long long *src_degree) override
@@ -87,6 +94,80 @@ struct MgRunner : MgRunnerBase {
         return cudaSuccess;
     }
     int Launches() override { return enactor.enactor_stats.launches; }
+
+    // ---- peer-memory exchange ----
+    std::vector<void *> opened;         // IPC mappings to close
+    void *PeerBuffer(int which)
+    {
+        switch (which) {
+            case 0: return problem.frontier_map[0].ptr;
+            case 1: return problem.frontier_map[1].ptr;
+            case 2: return problem.recv_map.ptr;
+            default: return enactor.mailbox.ptr;
+        }
+    }
+    cudaError_t PeerExport(unsigned char *handles) override
+    {
+        static_assert(sizeof(cudaIpcMemHandle_t) == GRB_IPC_HANDLE_BYTES, "IPC handle size");
+        for (int b = 0; b < GRB_MG_PEER_BUFFERS; ++b) {
+            cudaIpcMemHandle_t h;
+            GR_TRY(cudaIpcGetMemHandle(&h, PeerBuffer(b)));
+            memcpy(handles + b * GRB_IPC_HANDLE_BYTES, &h, sizeof(h));
+        }
+        return cudaSuccess;
+    }
+    cudaError_t PeerImport(int world, const unsigned char *all, unsigned long long global_edges) override
+    {
+        gunrock::app::bfs::PeerTable &pt = enactor.peers;
+        if (world != pt.parts)
+            return gunrock::util::GRError(cudaErrorInvalidValue, "peer import: world size differs from the partition", __FILE__, __LINE__);
+        enactor.global_edges = global_edges;
+        for (int r = 0; r < world; ++r) {
+            if (r == pt.rank) continue;
+            void *ptrs[GRB_MG_PEER_BUFFERS];
+            for (int b = 0; b < GRB_MG_PEER_BUFFERS; ++b) {
+                cudaIpcMemHandle_t h;
+                memcpy(&h, all + ((size_t)r * GRB_MG_PEER_BUFFERS + b) * GRB_IPC_HANDLE_BYTES, sizeof(h));
+                GR_TRY(cudaIpcOpenMemHandle(&ptrs[b], h, cudaIpcMemLazyEnablePeerAccess));
+                opened.push_back(ptrs[b]);
+            }
+            pt.map[0][r] = (unsigned *)ptrs[0];
+            pt.map[1][r] = (unsigned *)ptrs[1];
+            pt.recv[r]   = (unsigned *)ptrs[2];
+            pt.mailbox[r] = (gunrock::app::bfs::Mailbox *)ptrs[3];
+        }
+        enactor.p2p_ready = true;
+        return cudaSuccess;
+    }
+    cudaError_t RunPeer(int src, bool dopt, double alpha, double beta, bool record, grb_mg_stats *out) override
+    {
+        typename Enactor::SearchStats st;
+        GR_TRY(enactor.RunPeer(&problem, src, dopt, alpha, beta, record, &st));
+        if (out) {
+            out->elapsed_ms = st.elapsed_ms; out->iterations = st.iterations; out->push_levels = st.push_levels;
+            out->pull_levels = st.pull_levels; out->gpu_launches = st.launches; out->edges_visited = st.edges_visited;
+            out->edges_inspected = st.edges_inspected; out->exchange_bytes = st.exchange_bytes;
+            out->nodes_visited = st.nodes_visited;
+        }
+        return cudaSuccess;
+    }
+    int PeerLevels(grb_mg_trace *out, int cap) override
+    {
+        int k = 0;
+        for (const auto &t : enactor.trace) {
+            if (k >= cap) break;
+            out[k].level = t.level; out[k].kind = t.kind; out[k].frontier = t.frontier; out[k].discovered = t.discovered;
+            out[k].edges = t.edges; out[k].max_edges = t.max_edges; out[k].exchange_bytes = t.exchange_bytes;
+            out[k].compute_ms = t.compute_ms; out[k].exchange_ms = t.exchange_ms;
+            ++k;
+        }
+        return k;
+    }
+    ~MgRunner() override
+    {
+        for (void *p : opened) cudaIpcCloseMemHandle(p);
+        enactor.DestroyEvents();
+    }
 };
 
 struct grb_mgbfs_s {
@@ -160,6 +241,29 @@ extern "C" int grb_mgbfs_stream(grb_mgbfs_t ctx, void **cuda_stream)
 }
 extern "C" int grb_mgbfs_labels(grb_mgbfs_t ctx, int32_t *labels_host)
 { MG_ENTER(ctx); GRB_TRY(ctx->runner->Labels(labels_host)); return 0; }
+extern "C" int grb_mgbfs_peer_export(grb_mgbfs_t ctx, unsigned char *handles)
+{ MG_ENTER(ctx); if (!handles) return (int)cudaErrorInvalidValue; GRB_TRY(ctx->runner->PeerExport(handles)); return 0; }
+extern "C" int grb_mgbfs_peer_import(grb_mgbfs_t ctx, int world, const unsigned char *all_handles, uint64_t global_edges)
+{
+    MG_ENTER(ctx);
+    if (!all_handles || world < 1) return (int)cudaErrorInvalidValue;
+    GRB_TRY(ctx->runner->PeerImport(world, all_handles, global_edges));
+    return 0;
+}
+extern "C" int grb_mgbfs_run_peer(grb_mgbfs_t ctx, int32_t src, int direction_optimized, double alpha, double beta,
+                                  int record_levels, grb_mg_stats *out)
+{
+    MG_ENTER(ctx);
+    if (out) memset(out, 0, sizeof(*out));
+    GRB_TRY(ctx->runner->RunPeer(src, direction_optimized != 0, alpha, beta, record_levels != 0, out));
+    return 0;
+}
+extern "C" int grb_mgbfs_peer_levels(grb_mgbfs_t ctx, grb_mg_trace *out, int32_t cap, int32_t *count)
+{
+    if (!ctx || !out || !count) return (int)cudaErrorInvalidValue;
+    *count = ctx->runner->PeerLevels(out, cap);
+    return 0;
+}
 extern "C" void grb_mgbfs_destroy(grb_mgbfs_t ctx)
 {
     if (!ctx) return;

@@ -100,6 +100,44 @@ class DeviceEngine:
         _capi.check(_capi.lib().grb_mgbfs_counters(self._h, C.byref(lv)), "grb_mgbfs_counters")
         return int(lv.gpu_launches)
 
+    # ---- peer-memory exchange (include/gunrock_b200.h, grb_mgbfs_peer_*) -----------------------
+    def enable_peer_exchange(self, group=None):
+        """Exchange CUDA IPC handles of the buffers the peers write and map theirs; after this
+        `run_peer` runs whole searches natively with NVLink stores instead of collectives.
+        torch.distributed only ferries the handle bytes (and the global edge count) once."""
+        L = _capi.lib()
+        world = dist.get_world_size(group) if dist.is_initialized() else 1
+        if world == 1:
+            self.peer_ready = True
+            return
+        nbytes = _capi.IPC_HANDLE_BYTES * _capi.MG_PEER_BUFFERS
+        mine = (C.c_ubyte * nbytes)()
+        _capi.check(L.grb_mgbfs_peer_export(self._h, mine), "grb_mgbfs_peer_export")
+        every = [None] * world
+        dist.all_gather_object(every, (bytes(mine), self.local_edges), group=group)
+        blob = b"".join(h for h, _ in every)
+        buf = (C.c_ubyte * len(blob)).from_buffer_copy(blob)
+        _capi.check(L.grb_mgbfs_peer_import(self._h, world, buf, sum(m for _, m in every)), "grb_mgbfs_peer_import")
+        dist.barrier(group=group)           # nobody starts a search before every mapping exists
+        self.peer_ready = True
+
+    def run_peer(self, src, direction_optimized=True, alpha=14.0, beta=24.0, record_levels=False):
+        st = _capi.MgStats()
+        _capi.check(_capi.lib().grb_mgbfs_run_peer(self._h, int(src), int(direction_optimized), float(alpha),
+                                                   float(beta), int(record_levels), C.byref(st)), "grb_mgbfs_run_peer")
+        out = {k: getattr(st, k) for k, _ in st._fields_}
+        out["levels"] = []
+        if record_levels:
+            rec = (_capi.MgTrace * 128)()
+            cnt = C.c_int32()
+            _capi.check(_capi.lib().grb_mgbfs_peer_levels(self._h, rec, 128, C.byref(cnt)), "grb_mgbfs_peer_levels")
+            for r in rec[:cnt.value]:
+                out["levels"].append(dict(level=r.level, kind="pull" if r.kind else "push", frontier=r.frontier,
+                                          discovered=r.discovered, edges=r.edges, local_max_edges=r.max_edges,
+                                          exchange_bytes=r.exchange_bytes, compute_ms=r.compute_ms,
+                                          exchange_ms=r.exchange_ms))
+        return out
+
     def labels(self):
         out = np.empty(self.local_nodes, dtype=np.int32)
         _capi.check(_capi.lib().grb_mgbfs_labels(self._h, out.ctypes.data_as(C.c_void_p)), "grb_mgbfs_labels")
@@ -155,8 +193,14 @@ class PartitionedBfs:
     """Host loop of the partitioned DOBFS.  `engine` supplies the device steps and the tensors
     the collectives move; `group` is the torch.distributed process group (None = default)."""
 
-    def __init__(self, engine, group=None, direction_optimized=True, alpha=14.0, beta=24.0, record_levels=True):
+    def __init__(self, engine, group=None, direction_optimized=True, alpha=14.0, beta=24.0, record_levels=True,
+                 exchange="nccl"):
+        """exchange: "nccl" -- collectives of torch.distributed between the device steps (the host loop
+        below); "peer" -- the library's native loop with peer-memory stores (engine.run_peer)."""
         self.e = engine
+        self.exchange = exchange
+        if exchange == "peer" and not getattr(engine, "peer_ready", False):
+            engine.enable_peer_exchange(group)
         self.group = group
         self.dopt = direction_optimized
         self.alpha, self.beta = alpha, beta
@@ -196,6 +240,11 @@ class PartitionedBfs:
     def run(self, src):
         """-> stats dict; labels stay on the devices (engine.labels())."""
         e = self.e
+        if self.exchange == "peer":
+            t_wall = time.perf_counter()
+            st = e.run_peer(src, self.dopt, self.alpha, self.beta, self.record_levels)
+            st["wall_ms"] = (time.perf_counter() - t_wall) * 1e3
+            return st
         with e.stream_context():
             src_degree = e.reset(src)
             self.setup[0] = src_degree
@@ -275,6 +324,7 @@ class PartitionedBfs:
             rec["exchange_ms"] = e.elapsed_ms(m1, m2)
             rec["compute_ms"] = e.elapsed_ms(m0, m1) + e.elapsed_ms(m2, m3)
         return dict(elapsed_ms=e.elapsed_ms(ev_start, ev_end), wall_ms=wall_ms, iterations=level,
+                    gpu_launches=e.launches(),      # the context's counter restarts at every reset
                     edges_visited=edges_visited, edges_inspected=inspected, exchange_bytes=exch_bytes,
                     levels=levels, m_global=m_global)
 
@@ -327,9 +377,16 @@ def bench(args, rank, world, workload_config, ClockSampler, pick_sources, measur
     import json
     import os
     from . import Graph
+    import sys
     local = int(os.environ.get("LOCAL_RANK", rank))
+    # stdout carries exactly one JSON line: whatever libraries print meanwhile (NCCL announces its
+    # version on stdout) goes to stderr
+    sys.stdout.flush()
+    saved_stdout = os.dup(1)
+    os.dup2(2, 1)
     torch.cuda.set_device(local)
     os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+    os.environ.setdefault("MASTER_PORT", "29533")
     dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device("cuda", local))
     t_setup = time.time()
     try:
@@ -339,7 +396,8 @@ def bench(args, rank, world, workload_config, ClockSampler, pick_sources, measur
         scale = args.scale
         g = Graph.rmat(scale, 16, device=local, log_parts=lp, rank=rank)
         eng = DeviceEngine(g)
-        bfs = PartitionedBfs(eng, direction_optimized=True, record_levels=False)
+        exchange = getattr(args, "exchange", "peer")
+        bfs = PartitionedBfs(eng, direction_optimized=True, record_levels=False, exchange=exchange)
         sources = _pick_sources(g, eng, 64, 1234 + scale)
         clocks = ClockSampler(local)
         warm = max(args.warmup, 3)
@@ -352,18 +410,18 @@ def bench(args, rank, world, workload_config, ClockSampler, pick_sources, measur
         e0, e1 = eng.mark(), None
         edges = inspected = exch = 0
         levels = 0
-        launches0 = eng.launches()
+        launches = 0
         for i in range(args.steps):
             st = bfs.run(sources[i % len(sources)])
             edges += st["edges_visited"]
             inspected += st["edges_inspected"]
             exch += st["exchange_bytes"]
             levels += st["iterations"]
+            launches += st["gpu_launches"]
         e1 = eng.mark()
         dist.barrier()
         torch.cuda.synchronize()
         clocks.stop()
-        launches = eng.launches() - launches0
         t = torch.tensor([eng.elapsed_ms(e0, e1)], dtype=torch.float64, device=dev)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         ms = float(t.item())
@@ -372,7 +430,7 @@ def bench(args, rank, world, workload_config, ClockSampler, pick_sources, measur
         launches_all, m_global = int(cnt[0].item()), int(cnt[1].item())
 
         # traced pass: per-level compute / exchange split (events on the stream), max over ranks
-        tr = PartitionedBfs(eng, direction_optimized=True, record_levels=True)
+        tr = PartitionedBfs(eng, direction_optimized=True, record_levels=True, exchange=exchange)
         k = min(args.steps, 8)
         comp = torch.zeros(1, dtype=torch.float64, device=dev)
         exms = torch.zeros(1, dtype=torch.float64, device=dev)
@@ -408,7 +466,11 @@ def bench(args, rank, world, workload_config, ClockSampler, pick_sources, measur
             value = edges / (ms * 1e-3) / 1e9
             cfg = workload_config(args, scale, eng.nodes, m_global)
             cfg["partition"] = "1D, owner = low bits XOR hash(local row), %d devices" % world
-            cfg["exchange"] = "push: all_to_all of the discovery bitmap; pull: all_gather of the frontier bitmap (NCCL)"
+            cfg["exchange"] = ("push: all_to_all of the discovery bitmap; pull: all_gather of the frontier bitmap (NCCL)"
+                               if exchange == "nccl" else
+                               "peer memory over NVLink (CUDA IPC): pull sweeps store their frontier words on every device, "
+                               "push levels store the non-empty lines of the discovery map into the owner's receive buffer, "
+                               "counters and barriers are flag words in the peers' mailboxes; no collective call inside a search")
             comp_ms, ex_ms = float(comp.item()) / k, float(exms.item()) / k
             line = {
                 "metric": "bfs_gteps_rmat", "value": value, "unit": "GTEPS", "n_gpus": world, "steps": args.steps,
@@ -432,8 +494,14 @@ def bench(args, rank, world, workload_config, ClockSampler, pick_sources, measur
                 "graph500_gteps": value / 2.0, "edges_inspected_per_search": inspected / max(args.steps, 1),
                 "setup_s": round(time.time() - t_setup, 1),
             }
+            sys.stdout.flush()
+            os.dup2(saved_stdout, 1)
             print(json.dumps(line), flush=True)
+            os.dup2(2, 1)
         eng.close()
         g.close()
     finally:
         dist.destroy_process_group()
+        sys.stdout.flush()
+        os.dup2(saved_stdout, 1)
+        os.close(saved_stdout)

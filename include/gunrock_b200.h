@@ -225,6 +225,40 @@ int  grb_mgbfs_stream(grb_mgbfs_t ctx, void **cuda_stream);
 int  grb_mgbfs_labels(grb_mgbfs_t ctx, int32_t *labels_host);
 void grb_mgbfs_destroy(grb_mgbfs_t ctx);
 
+/* ---- peer-memory exchange: the same levels with NVLink stores instead of collectives ----
+ * Each process exports CUDA IPC handles of the buffers its peers write (frontier map 0,
+ * frontier map 1, receive map, mailbox), the harness moves the handle bytes between the
+ * processes (any transport; torch.distributed all_gather in gunrockinst_b200/partitioned.py),
+ * and every process imports all of them.  After that grb_mgbfs_run_peer runs a whole
+ * direction-optimising search natively: pull sweeps publish their frontier words on every
+ * device as they are produced, push levels store the lines of the discovery map that hold a
+ * bit straight into the owner's receive buffer, and level counters / barriers are flag words
+ * in the peers' mailboxes -- no collective library call inside a search.  All ranks must call
+ * it with the same arguments; a rank that waits more than 4 s for a peer gives up with
+ * cudaErrorLaunchTimeout.  With one device no import is needed. */
+#define GRB_IPC_HANDLE_BYTES 64
+#define GRB_MG_PEER_BUFFERS  4
+typedef struct {
+    double   elapsed_ms;         /* CUDA events on the context's stream, reset included */
+    int64_t  iterations, push_levels, pull_levels, gpu_launches;
+    uint64_t edges_visited;      /* sum of out-degrees of the visited vertices, all devices */
+    uint64_t edges_inspected;    /* neighbour entries inspected, all devices              */
+    uint64_t exchange_bytes;     /* bytes this device stored into peer memory             */
+    uint64_t nodes_visited;
+} grb_mg_stats;
+typedef struct {
+    int32_t  level, kind;        /* kind: 0 push, 1 pull */
+    uint64_t frontier, discovered, edges, max_edges, exchange_bytes;
+    float    compute_ms, exchange_ms;
+} grb_mg_trace;
+int  grb_mgbfs_peer_export(grb_mgbfs_t ctx, unsigned char *handles /* [GRB_MG_PEER_BUFFERS * 64] */);
+int  grb_mgbfs_peer_import(grb_mgbfs_t ctx, int world,
+                           const unsigned char *all_handles /* [world][GRB_MG_PEER_BUFFERS * 64] */,
+                           uint64_t global_edges);
+int  grb_mgbfs_run_peer(grb_mgbfs_t ctx, int32_t src, int direction_optimized, double alpha, double beta,
+                        int record_levels, grb_mg_stats *out);
+int  grb_mgbfs_peer_levels(grb_mgbfs_t ctx, grb_mg_trace *out, int32_t cap, int32_t *count);
+
 #ifdef __cplusplus
 }
 #endif

@@ -16,12 +16,13 @@ pytestmark = pytest.mark.gpu
 
 @pytest.mark.parametrize("scale", [10, 16])
 @pytest.mark.parametrize("dopt", [False, True])
-def test_world1_matches_oracle(gr, orc, scale, dopt):
+@pytest.mark.parametrize("exchange", ["nccl", "peer"])
+def test_world1_matches_oracle(gr, orc, scale, dopt, exchange):
     from gunrockinst_b200 import partitioned as pt
     ro, co = rmat_graph(orc, scale)
     g = gr.Graph.from_csr(ro, co, symmetric=True)
     eng = pt.DeviceEngine(g)
-    bfs = pt.PartitionedBfs(eng, direction_optimized=dopt)
+    bfs = pt.PartitionedBfs(eng, direction_optimized=dopt, exchange=exchange)
     for src in (0, 3, ro.size - 2):
         st = bfs.run(src)
         want = orc.bfs(ro, co, src)
@@ -57,14 +58,16 @@ def _worker(rank, world, port, scale, q):
         eng = pt.DeviceEngine(g)
         ro, co = oracle.rmat_csr(scale, 16)
         res = []
-        for dopt in (True, False):
-            bfs = pt.PartitionedBfs(eng, direction_optimized=dopt)
-            for src in (0, 1, 12345 % (1 << scale)):
-                st = bfs.run(src)
-                labels = pt.gather_labels(eng)
-                want = oracle.bfs(ro, co, src)
-                res.append((bool(np.array_equal(labels, want)), st["edges_visited"] == oracle.edges_visited(ro, want),
-                            st["exchange_bytes"] > 0))
+        for exchange in ("nccl", "peer", "nccl", "peer"):       # alternating: either path starts from the other's leftovers
+            for dopt in (True, False):
+                bfs = pt.PartitionedBfs(eng, direction_optimized=dopt, exchange=exchange)
+                for src in (0, 1, 12345 % (1 << scale)):
+                    st = bfs.run(src)
+                    labels = pt.gather_labels(eng)
+                    want = oracle.bfs(ro, co, src)
+                    res.append((bool(np.array_equal(labels, want)),
+                                st["edges_visited"] == oracle.edges_visited(ro, want),
+                                st["exchange_bytes"] > 0))
         if rank == 0:
             q.put(res)
     finally:

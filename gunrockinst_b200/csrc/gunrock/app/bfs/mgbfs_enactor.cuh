@@ -23,6 +23,8 @@
 // harness all-gathers, so one collective + one host read per level carries the frontier
 // length, its degree sum and the edges inspected of every device.
 #pragma once
+#include <atomic>
+#include <chrono>
 #include <vector>
 #include "bfs_enactor.cuh"
 #include "mgbfs_p2p.cuh"
@@ -296,7 +298,19 @@ class MGBFSEnactor : public EnactorBase {
         ExchangeCountersKernel<<<1, 32 * kMaxPeers, 0, stream>>>(peers, Counters(), epoch, h_all.ptr, h_status.ptr);
         GR_TRY(cudaGetLastError());
         ++enactor_stats.launches;
-        GR_TRY(cudaStreamSynchronize(stream));
+        // the kernel's last store is the status word in pinned host memory: polling it spares the
+        // wake-up latency of a stream synchronisation on every level
+        {
+            volatile unsigned long long *st = h_status.ptr;
+            const auto t0 = std::chrono::steady_clock::now();
+            unsigned spins = 0;
+            while (*st == 0) {
+                if ((++spins & 0xfffu) == 0 &&
+                    std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count() > 10.0) break;
+            }
+            if (*st == 0) GR_TRY(cudaStreamSynchronize(stream));
+            std::atomic_thread_fence(std::memory_order_acquire);
+        }
         if (*h_status.ptr != epoch)
             return util::GRError(cudaErrorLaunchTimeout, "peer exchange timed out (a peer stopped or the ranks diverged)", __FILE__, __LINE__);
         return cudaSuccess;

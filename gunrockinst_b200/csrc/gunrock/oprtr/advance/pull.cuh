@@ -185,27 +185,49 @@ __device__ __forceinline__ void Sweep(
 
         // ---- 2. probe, phase by phase over the whole list -------------------------------------------
         // (u * 32 < total is warp-uniform: unused phases of a short list are skipped)
-#pragma unroll
-        for (int u = 0; u < U; ++u) {
-            const unsigned idx = u * 32 + lane;
-            if (u * 32 < total && idx < total) {
-                const long long row = (w0 << 5) + s_cand[idx];
-                const SizeT b = args.g.row_offsets[row], e = args.g.row_offsets[row + 1];
-                s_begin[idx] = b;
-                const unsigned long long d = (unsigned long long)(e - b);
-                s_deg[idx] = d > 0x7fffffffull ? 0x7fffffffu : (unsigned)d;
-            }
-        }
+        // the dense head array (first entry of every row, -1: empty row) is indexed by the row like the
+        // offsets, so both gathers are issued together and the frontier probes below wait for the
+        // head only: the chain is head -> bit, with the offsets (needed for the degree sum and the
+        // retry walk) arriving in its shadow
         VertexId n0[U];
 #pragma unroll
         for (int u = 0; u < U; ++u) {
             const unsigned idx = u * 32 + lane;
             n0[u] = -1;
-            if (u * 32 < total && idx < total && s_deg[idx] != 0) {
-                // the dense head array turns this gather (one 128-byte line per vertex) into a
-                // coalesced read of consecutive rows
-                if (args.head) n0[u] = util::LoadStream(args.head + ((w0 << 5) + s_cand[idx]));
-                else           n0[u] = util::LoadStream(args.g.col_indices + s_begin[idx]);
+            if (args.head && u * 32 < total && idx < total)
+                n0[u] = util::LoadStream(args.head + ((w0 << 5) + s_cand[idx]));
+        }
+        SizeT rb[U], re[U];
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            const unsigned idx = u * 32 + lane;
+            rb[u] = 0; re[u] = 0;
+            if (u * 32 < total && idx < total) {
+                const long long row = (w0 << 5) + s_cand[idx];
+                rb[u] = args.g.row_offsets[row]; re[u] = args.g.row_offsets[row + 1];
+            }
+        }
+        if (!args.head) {
+#pragma unroll
+            for (int u = 0; u < U; ++u) {
+                const unsigned idx = u * 32 + lane;
+                if (u * 32 < total && idx < total && re[u] > rb[u])
+                    n0[u] = util::LoadStream(args.g.col_indices + rb[u]);
+            }
+        }
+        unsigned probe[U];
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            probe[u] = 0;
+            if (u * 32 < total && n0[u] >= 0) probe[u] = util::LoadCA(args.frontier_in + (ds.BitPos(n0[u]) >> 5));
+        }
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            const unsigned idx = u * 32 + lane;
+            if (u * 32 < total && idx < total) {
+                s_begin[idx] = rb[u];
+                const unsigned long long d = (unsigned long long)(re[u] - rb[u]);
+                s_deg[idx] = d > 0x7fffffffull ? 0x7fffffffu : (unsigned)d;
             }
         }
         unsigned hits = 0;
@@ -213,7 +235,7 @@ __device__ __forceinline__ void Sweep(
         for (int u = 0; u < U; ++u) {
             if (u * 32 < total && n0[u] >= 0) {
                 ++my_edges;
-                if (util::BitTest(args.frontier_in, ds.BitPos(n0[u]))) hits |= 1u << u;
+                if ((probe[u] >> (ds.BitPos(n0[u]) & 31)) & 1u) hits |= 1u << u;
             }
         }
         unsigned n_retry = 0;

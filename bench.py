@@ -142,9 +142,10 @@ def ncu_traffic(kernel_key):
     """per-launch DRAM bytes of the dominant kernel from the committed ncu capture, if any"""
     try:
         with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
-            return json.load(f).get(kernel_key)
+            rec = json.load(f).get(kernel_key)
+        return (float(rec["bytes_per_launch"]), rec.get("source")) if rec else (None, None)
     except Exception:
-        return None
+        return None, None
 
 
 def level_bytes(rec, offset_bytes, nodes):
@@ -283,7 +284,7 @@ def run_single(args):
     achieved = agg[dom]["bytes"] / (agg[dom]["ms"] * 1e-3) / 1e9 if agg[dom]["ms"] > 0 else 0.0
     roofline = {"bound": "hbm", "kernel": kernel_names.get(dom, dom), "achieved": achieved, "peak": peak,
                 "unit": "GB/s", "frac": achieved / peak, "peak_source": peak_src,
-                "traffic": ncu_traffic(dom),
+                "traffic": ncu_traffic(dom)[0], "traffic_source": ncu_traffic(dom)[1],
                 "launches_timed": agg[dom]["launches"],
                 "avg_launch_us": 1e3 * agg[dom]["ms"] / max(agg[dom]["launches"], 1),
                 "algo_bytes_per_launch": agg[dom]["bytes"] / max(agg[dom]["launches"], 1),

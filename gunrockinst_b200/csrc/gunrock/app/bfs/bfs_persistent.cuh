@@ -84,7 +84,13 @@ __device__ __forceinline__ unsigned long long GlobalTimerNs()
 
 template <typename PushPolicy, typename PullPolicy, bool NEED_SRC>
 union PersistentStorage {
-    oprtr::advance::lb::ExpandStorage<PushPolicy, NEED_SRC> expand;
+    // (the CTA-private scan of a short frontier is only alive together with the expansion: keeping it
+    //  inside the union keeps the kernel's shared-memory carve-out, and with it the L1 left for the
+    //  pull sweep's frontier-bit probes, close to the stand-alone kernels')
+    struct {
+        oprtr::advance::lb::ExpandStorage<PushPolicy, NEED_SRC> expand;
+        oprtr::advance::lb::SmallScanStorage<PushPolicy>        small;
+    } push;
     oprtr::advance::lb::ScanStorage<PushPolicy::THREADS>    scan;
     oprtr::advance::twc::Storage<PushPolicy, NEED_SRC>      twc;
     oprtr::advance::pull::SweepStorage<PullPolicy>          sweep;
@@ -141,6 +147,20 @@ __device__ __forceinline__ void BitmapToQueue(unsigned *bitmap, VertexId *queue,
 
 constexpr int kPersistentCtasPerSm = 4;
 
+// The pull sweep as a real call: inlined into the level loop it shares the 64-register budget with
+// every value the loop keeps alive and spills (~0.85 KB per thread; the sweep of a scale-25 level
+// ran 1.7x slower than the stand-alone pull::Kernel); as a callee it gets the whole budget and
+// only the loop state that is live across the call is saved.
+template <typename PullPolicy, typename Problem, typename PullFunctor>
+__device__ __noinline__ void SweepCall(
+    const typename Problem::DataSlice &ds,
+    const oprtr::advance::pull::PullArgs<typename Problem::VertexId, typename Problem::SizeT> &pa,
+    oprtr::advance::pull::SweepStorage<PullPolicy> &sm, oprtr::LevelCounters *slot_out,
+    long long first_chunk, long long chunk_stride)
+{
+    oprtr::advance::pull::Sweep<PullPolicy, Problem, PullFunctor>(ds, pa, sm, slot_out, first_chunk, chunk_stride);
+}
+
 template <typename PushPolicy, typename PullPolicy, typename Problem, typename PushFunctor, typename PullFunctor>
 __global__ void __launch_bounds__(PushPolicy::THREADS, kPersistentCtasPerSm)
 PersistentKernel(const __grid_constant__ typename Problem::DataSlice ds0,
@@ -157,7 +177,6 @@ PersistentKernel(const __grid_constant__ typename Problem::DataSlice ds0,
 
     __shared__ PersistentStorage<PushPolicy, PullPolicy, Problem::MARK_PREDECESSORS> sm;
     __shared__ unsigned long long s_level[5];           // the level's counters: one L2 read per CTA, not per warp
-    __shared__ oprtr::advance::lb::SmallScanStorage<PushPolicy> s_small;
     cg::grid_group grid = cg::this_grid();
     const unsigned cta = blockIdx.x, num_ctas = gridDim.x;
     const bool leader = cta == 0 && threadIdx.x == 0;
@@ -275,7 +294,7 @@ PersistentKernel(const __grid_constant__ typename Problem::DataSlice ds0,
                 // short frontier (first / last levels, a hub on its own): every CTA scans it privately
                 // and expands its share of the edge tiles -- one pass, all SMs, no extra barrier
                 kind = 3;
-                adv::lb::ExpandSmall<PushPolicy, Problem, PushFunctor>(ds, a, s_small, sm.expand, F, frontier_edges,
+                adv::lb::ExpandSmall<PushPolicy, Problem, PushFunctor>(ds, a, sm.push.small, sm.push.expand, F, frontier_edges,
                                                                        slot_out, cta, num_ctas);
             } else if (!lb) {
                 kind = 0;
@@ -293,7 +312,7 @@ PersistentKernel(const __grid_constant__ typename Problem::DataSlice ds0,
                 adv::lb::ScanTiles<PushPolicy, THREADS, 4>(a, sv, sm.scan, F, slot_out, true);
                 grid.sync(); ++sum.grid_syncs;
                 if (leader) *sv.ticket = 0;
-                adv::lb::ExpandTiles<PushPolicy, Problem, PushFunctor>(ds, a, sv, sm.expand, F, slot_out, cta, num_ctas);
+                adv::lb::ExpandTiles<PushPolicy, Problem, PushFunctor>(ds, a, sv, sm.push.expand, F, slot_out, cta, num_ctas);
             }
         } else {
             kind = 1;
@@ -308,7 +327,7 @@ PersistentKernel(const __grid_constant__ typename Problem::DataSlice ds0,
             pa.fwd_row_offsets = P.fwd_row_offsets;
             pa.out_queue = nullptr; pa.out_cap = 0;
             pa.slots = P.slots; pa.queue_index = qi; pa.iteration = level;
-            adv::pull::Sweep<PullPolicy, Problem, PullFunctor>(
+            SweepCall<PullPolicy, Problem, PullFunctor>(
                 ds, pa, sm.sweep, slot_out, (long long)cta * PullPolicy::WARPS + util::WarpId(),
                 (long long)num_ctas * PullPolicy::WARPS);
         }

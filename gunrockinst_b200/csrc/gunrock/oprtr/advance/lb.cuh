@@ -242,7 +242,7 @@ struct LocalScan {
 // Expands tiles cta, cta + num_ctas, ... of the scanned frontier.  Callable from any kernel whose
 // CTAs have Policy::THREADS threads (the stand-alone ExpandKernel below, the persistent BFS kernel).
 template <typename Policy, typename Problem, typename Functor, typename Scan>
-__device__ __forceinline__ void ExpandTilesFrom(
+__device__ __forceinline__ void ExpandTilesFromImpl(
     const typename Problem::DataSlice &ds,
     const Args<typename Policy::VertexId, typename Policy::SizeT> &args,
     const Scan &scan, const unsigned long long total,
@@ -389,6 +389,31 @@ __device__ __forceinline__ void ExpandTilesFrom(
     // per-CTA statistics: one atomic each
     BlockAccumulate<THREADS>(my_edges_total, sm.red, &slot_out->edges);
     if constexpr (Policy::TRACK_OUT_DEGREE) BlockAccumulate<THREADS>(stager.out_degree, sm.red, &slot_out->out_degree);
+}
+
+// does the functor block carry a partition (BC's does not: single device only)?
+template <typename T, typename = void> struct HasPartition { static const bool value = false; };
+template <typename T> struct HasPartition<T, decltype((void)(((T *)nullptr)->part), void())> { static const bool value = true; };
+
+// Entry: on a single device the functor block is handed over with a compile-time identity partition,
+// so the owner hash and the owner-major bit positions drop out of the per-edge code (see pull::Sweep).
+template <typename Policy, typename Problem, typename Functor, typename Scan>
+__device__ __forceinline__ void ExpandTilesFrom(
+    const typename Problem::DataSlice &ds,
+    const Args<typename Policy::VertexId, typename Policy::SizeT> &args,
+    const Scan &scan, const unsigned long long total,
+    ExpandStorage<Policy, Problem::MARK_PREDECESSORS> &sm,
+    unsigned long long in_len, LevelCounters *slot_out, unsigned cta, unsigned num_ctas)
+{
+    if constexpr (HasPartition<typename Problem::DataSlice>::value) {
+        if (ds.part.log_parts == 0) {
+            typename Problem::DataSlice d1 = ds;
+            d1.part = graph::Partition();
+            ExpandTilesFromImpl<Policy, Problem, Functor>(d1, args, scan, total, sm, in_len, slot_out, cta, num_ctas);
+            return;
+        }
+    }
+    ExpandTilesFromImpl<Policy, Problem, Functor>(ds, args, scan, total, sm, in_len, slot_out, cta, num_ctas);
 }
 
 // the scanned frontier lives in the global scratch (after ScanKernel / ScanTiles)

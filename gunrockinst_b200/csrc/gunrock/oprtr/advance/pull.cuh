@@ -94,8 +94,8 @@ struct SweepStorage {
 // The sweep itself, callable from any kernel whose CTAs have Policy::THREADS threads:
 // warp `first_chunk` of `chunk_stride` warps takes chunks first_chunk, first_chunk + chunk_stride, ...
 // Accumulates edges / out_degree / aux0 (= vertices examined) / out_len into `slot_out`.
-template <typename Policy, typename Problem, typename Functor>
-__device__ __forceinline__ void Sweep(
+template <typename Policy, typename Problem, typename Functor, bool SINGLE>
+__device__ __forceinline__ void SweepImpl(
     const typename Problem::DataSlice &ds,
     const PullArgs<typename Policy::VertexId, typename Policy::SizeT> &args,
     SweepStorage<Policy> &sm, LevelCounters *slot_out,
@@ -113,7 +113,7 @@ __device__ __forceinline__ void Sweep(
     const long long num_words  = (local_nodes + 31) >> 5;
     const long long num_chunks = (num_words + kChunkWords - 1) / kChunkWords;
     // first word of this device's segment inside the global bitmaps
-    const long long seg = ((long long)args.g.part.rank * local_nodes) >> 5;
+    const long long seg = SINGLE ? 0ll : ((long long)args.g.part.rank * local_nodes) >> 5;
     unsigned char *s_cand  = sm.cand[util::WarpId()];
     unsigned char *s_retry = sm.retry[util::WarpId()];
     SizeT         *s_begin = sm.begin[util::WarpId()];
@@ -127,7 +127,7 @@ __device__ __forceinline__ void Sweep(
     auto publish = [&](long long w0, unsigned idx, VertexId parent, long long epos) {
         const unsigned off = s_cand[idx];
         const long long row = (w0 << 5) + off;
-        const VertexId child = (VertexId)args.g.part.Global(row);
+        const VertexId child = SINGLE ? (VertexId)row : (VertexId)args.g.part.Global(row);
         const VertexId s_id = NEED_SRC ? parent : (VertexId)args.iteration;
         if (!VisitEdge<Policy, Problem, Functor>(&ds, s_id, child, (SizeT)epos, (SizeT)row)) return;
         atomicOr(s_found + (off >> 5), 1u << (off & 31));
@@ -322,6 +322,26 @@ __device__ __forceinline__ void Sweep(
     BlockAccumulate<THREADS>(my_cands,  sm.red, &slot_out->aux0);
     // found vertices are counted in out_len unless the queue path already did
     if (!args.out_queue) BlockAccumulate<THREADS>(my_found, sm.red, &slot_out->out_len);
+}
+
+// Entry: on a single device the partition arithmetic (owner hash, owner-major bit positions, global
+// <-> local ids) is the identity.  Handing the implementation copies whose partition is a
+// compile-time constant lets the compiler drop it from every per-vertex and per-edge path (it was
+// ~10 % of the sweep's instructions); the partitioned run takes the general instance.
+template <typename Policy, typename Problem, typename Functor>
+__device__ __forceinline__ void Sweep(
+    const typename Problem::DataSlice &ds,
+    const PullArgs<typename Policy::VertexId, typename Policy::SizeT> &args,
+    SweepStorage<Policy> &sm, LevelCounters *slot_out,
+    long long first_chunk, long long chunk_stride)
+{
+    if (args.g.part.log_parts == 0) {
+        typename Problem::DataSlice d1 = ds;       // (only the small functor block is copied: a copy
+        d1.part = graph::Partition();               //  of `args` ends up in local memory)
+        SweepImpl<Policy, Problem, Functor, true>(d1, args, sm, slot_out, first_chunk, chunk_stride);
+    } else {
+        SweepImpl<Policy, Problem, Functor, false>(ds, args, sm, slot_out, first_chunk, chunk_stride);
+    }
 }
 
 template <typename Policy, typename Problem, typename Functor>

@@ -78,7 +78,7 @@ class MgTrace(C.Structure):
                 ("compute_ms", C.c_float), ("exchange_ms", C.c_float)]
 
 
-IPC_HANDLE_BYTES, MG_PEER_BUFFERS = 64, 4
+IPC_HANDLE_BYTES, MG_PEER_BUFFERS, MGSSSP_PEER_BUFFERS = 64, 4, 3
 
 
 # gunrock.h (reference ABI, gunrock/gunrock.h:51-99)
@@ -171,6 +171,12 @@ def lib():
     sig("grb_mgbfs_peer_import", C.c_int, [p, C.c_int, p, u64])
     sig("grb_mgbfs_run_peer", C.c_int, [p, i32, C.c_int, dbl, dbl, C.c_int, C.POINTER(MgStats)])
     sig("grb_mgbfs_peer_levels", C.c_int, [p, C.POINTER(MgTrace), i32, C.POINTER(i32)])
+    sig("grb_mgsssp_create", C.c_int, [p, pp])
+    sig("grb_mgsssp_peer_export", C.c_int, [p, p])
+    sig("grb_mgsssp_peer_import", C.c_int, [p, C.c_int, p])
+    sig("grb_mgsssp_run", C.c_int, [p, i32, C.POINTER(MgStats)])
+    sig("grb_mgsssp_result", C.c_int, [p, p, p])
+    sig("grb_mgsssp_destroy", None, [p])
     for name in ("gunrock_bfs_func", "gunrock_cc_func", "gunrock_bc_func"):
         sig(name, None, [C.POINTER(GunrockGraph), C.POINTER(GunrockGraph), GunrockConfig, GunrockDataType])
     sig("gunrock_topk_func", None, [C.POINTER(GunrockGraph), p, p, p, C.POINTER(GunrockGraph),

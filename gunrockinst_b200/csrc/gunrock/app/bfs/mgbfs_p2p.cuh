@@ -42,9 +42,11 @@ struct Mailbox {
 
 // what a kernel needs to reach the peers (kernel parameter; pointers are IPC mappings, own
 // rank's entry is the local allocation)
-struct PeerTable {
+struct MailboxTable {
     int       parts = 1, rank = 0;
     Mailbox  *mailbox[kMaxPeers]  = {};
+};
+struct PeerTable : MailboxTable {
     unsigned *map[2][kMaxPeers]   = {};     // the two global frontier maps of every device
     unsigned *recv[kMaxPeers]     = {};     // received discovery segments of every device
 };
@@ -85,7 +87,7 @@ constexpr unsigned long long kWaitBudgetNs = 4000000000ull;      // 4 s
 // Posts `mine` (epoch `epoch`) everywhere, waits for everybody's post, copies the blocks to
 // `h_all` (pinned host) in rank order.
 static __global__ void __launch_bounds__(32 * kMaxPeers)
-ExchangeCountersKernel(PeerTable pt, const oprtr::LevelCounters *mine, unsigned long long epoch,
+ExchangeCountersKernel(MailboxTable pt, const oprtr::LevelCounters *mine, unsigned long long epoch,
                        oprtr::LevelCounters *h_all, unsigned long long *h_status)
 {
     const int p = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -119,7 +121,7 @@ ExchangeCountersKernel(PeerTable pt, const oprtr::LevelCounters *mine, unsigned 
 // barrier in the middle of a level (between "scatter my discoveries" and "absorb what I
 // received"): bump my count in every mailbox, wait until every sender's count reached `count`
 static __global__ void __launch_bounds__(32 * kMaxPeers)
-PeerBarrierKernel(PeerTable pt, unsigned long long count)
+PeerBarrierKernel(MailboxTable pt, unsigned long long count)
 {
     const int p = threadIdx.x >> 5, lane = threadIdx.x & 31;
     if (p < pt.parts && lane == 0) {
@@ -200,6 +202,56 @@ __global__ void SeedSourceKernel(DataSlice ds, VertexId src, VertexId *queue, un
         frontier_map0[pos >> 5] = 1u << (pos & 31);
     }
 }
+
+
+// Host side of the mailbox protocol for one device: owns the mailbox and the pinned landing
+// area, counts epochs.  (MGBFSEnactor carries the same state inline; new partitioned
+// primitives use this.)
+struct PeerComm {
+    MailboxTable table;
+    util::DeviceArray<Mailbox> mailbox;
+    util::PinnedArray<oprtr::LevelCounters> h_all;
+    util::PinnedArray<unsigned long long> h_status;
+    unsigned long long epoch = 0, bar_count = 0;
+    bool ready = false;
+
+    cudaError_t Setup(int parts, int rank, cudaStream_t s)
+    {
+        if (parts > kMaxPeers) return util::GRError(cudaErrorInvalidValue, "peer exchange supports up to 8 devices", __FILE__, __LINE__);
+        GR_TRY(mailbox.Allocate(1));
+        GR_TRY(mailbox.Zero(s));
+        GR_TRY(h_all.Allocate(kMaxPeers));
+        GR_TRY(h_status.Allocate(1));
+        table = MailboxTable();
+        table.parts = parts; table.rank = rank;
+        table.mailbox[rank] = mailbox.ptr;
+        epoch = bar_count = 0;
+        ready = (parts == 1);
+        return cudaStreamSynchronize(s);
+    }
+    // posts `mine`, waits for everybody's block of this epoch; h_all.ptr[0..parts) valid on return
+    cudaError_t Exchange(const oprtr::LevelCounters *mine, cudaStream_t s)
+    {
+        ++epoch;
+        *h_status.ptr = 0;
+        ExchangeCountersKernel<<<1, 32 * kMaxPeers, 0, s>>>(table, mine, epoch, h_all.ptr, h_status.ptr);
+        GR_TRY(cudaGetLastError());
+        volatile unsigned long long *st = h_status.ptr;
+        unsigned long long spins = 0;
+        while (*st == 0) { if (++spins > (1ull << 33)) break; }
+        if (*st == 0) GR_TRY(cudaStreamSynchronize(s));
+        if (*h_status.ptr != epoch)
+            return util::GRError(cudaErrorLaunchTimeout, "peer exchange timed out (a peer stopped or the ranks diverged)", __FILE__, __LINE__);
+        return cudaSuccess;
+    }
+    cudaError_t Barrier(cudaStream_t s)
+    {
+        if (table.parts == 1) return cudaSuccess;
+        ++bar_count;
+        PeerBarrierKernel<<<1, 32 * kMaxPeers, 0, s>>>(table, bar_count);
+        return cudaGetLastError();
+    }
+};
 
 }  // namespace bfs
 }  // namespace app

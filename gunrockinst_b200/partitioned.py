@@ -329,6 +329,75 @@ class PartitionedBfs:
                     levels=levels, m_global=m_global)
 
 
+class PartitionedSssp:
+    """1D-partitioned SSSP over peer memory (include/gunrock_b200.h, grb_mgsssp_*): one instance per
+    rank on that rank's slice of a weighted graph; every rank calls run() with the same source."""
+
+    def __init__(self, graph, group=None):
+        self.graph, self.group = graph, group
+        L = _capi.lib()
+        self._h = C.c_void_p()
+        _capi.check(L.grb_mgsssp_create(graph._h, C.byref(self._h)), "grb_mgsssp_create")
+        info = graph.info
+        self.parts, self.rank = 1 << info.log_parts, int(info.rank)
+        self.nodes, self.local_nodes = int(info.nodes), int(info.local_nodes)
+        world = dist.get_world_size(group) if dist.is_initialized() else 1
+        if world != self.parts:
+            raise ValueError("graph is partitioned %d ways but the group has %d ranks" % (self.parts, world))
+        if world > 1:
+            nbytes = _capi.IPC_HANDLE_BYTES * _capi.MGSSSP_PEER_BUFFERS
+            mine = (C.c_ubyte * nbytes)()
+            _capi.check(L.grb_mgsssp_peer_export(self._h, mine), "grb_mgsssp_peer_export")
+            every = [None] * world
+            dist.all_gather_object(every, bytes(mine), group=group)
+            blob = b"".join(every)
+            buf = (C.c_ubyte * len(blob)).from_buffer_copy(blob)
+            _capi.check(L.grb_mgsssp_peer_import(self._h, world, buf), "grb_mgsssp_peer_import")
+            dist.barrier(group=group)
+
+    def run(self, src):
+        st = _capi.MgStats()
+        _capi.check(_capi.lib().grb_mgsssp_run(self._h, int(src), C.byref(st)), "grb_mgsssp_run")
+        return dict(elapsed_ms=st.elapsed_ms, iterations=st.iterations, gpu_launches=st.gpu_launches,
+                    relaxations=st.edges_inspected, queued=st.nodes_visited)
+
+    def result(self):
+        """-> (dist uint32[local_nodes], preds int32[local_nodes]) of the owned rows"""
+        d = np.empty(self.local_nodes, dtype=np.uint32)
+        p = np.empty(self.local_nodes, dtype=np.int32)
+        _capi.check(_capi.lib().grb_mgsssp_result(self._h, d.ctypes.data_as(C.c_void_p), p.ctypes.data_as(C.c_void_p)),
+                    "grb_mgsssp_result")
+        return d, p
+
+    def gather(self):
+        """global (dist, preds) in vertex order on every rank; for tests"""
+        d, p = self.result()
+        lp = self.parts.bit_length() - 1
+        gd = np.empty(self.nodes, dtype=np.uint32)
+        gp = np.empty(self.nodes, dtype=np.int32)
+        if self.parts == 1:
+            ids = global_ids(self.local_nodes, lp, 0)
+            gd[ids], gp[ids] = d, p
+            return gd, gp
+        every = [None] * self.parts
+        dist.all_gather_object(every, (d, p), group=self.group)
+        for r, (dd, pp) in enumerate(every):
+            ids = global_ids(self.local_nodes, lp, r)
+            gd[ids], gp[ids] = dd, pp
+        return gd, gp
+
+    def close(self):
+        if self._h:
+            _capi.lib().grb_mgsssp_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
 def gather_labels(engine, group=None):
     """all ranks' labels -> one global int32[n] array in vertex order (on every rank); for tests"""
     world = dist.get_world_size(group) if dist.is_initialized() else 1

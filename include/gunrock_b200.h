@@ -116,8 +116,9 @@ typedef struct {
     double  alpha, beta;          /* <= 0: library defaults                           */
     double  queue_sizing;         /* <= 0: 1.0                                        */
     int32_t record_levels;
-    int32_t host_loop;            /* 0: whole level loop in one cooperative kernel; 1: one
-                                     launch set + counter fetch per level, driven by the host */
+    int32_t host_loop;            /* 0: by size (one cooperative kernel up to 2^24 vertices, host-driven
+                                     above); 1: one launch set + counter fetch per level, driven by
+                                     the host; 2: whole level loop in one cooperative kernel */
 } grb_bfs_config;
 
 typedef struct grb_bfs_s *grb_bfs_t;
@@ -258,6 +259,26 @@ int  grb_mgbfs_peer_import(grb_mgbfs_t ctx, int world,
 int  grb_mgbfs_run_peer(grb_mgbfs_t ctx, int32_t src, int direction_optimized, double alpha, double beta,
                         int record_levels, grb_mg_stats *out);
 int  grb_mgbfs_peer_levels(grb_mgbfs_t ctx, grb_mg_trace *out, int32_t cap, int32_t *count);
+
+/* ---- 1D-partitioned SSSP over peer memory -----------------------------------------------
+ * Same partition and handle hand-over as the BFS above (3 buffers per device: the 64-bit
+ * distance|predecessor words, the touched bitmap, the mailbox).  A remote relaxation is a 64-bit
+ * atomicMin issued over NVLink by the advance kernel that found the shorter path; the owner
+ * collects what was touched into its next frontier.  Relaxation arithmetic and outputs as the
+ * reference's SSSP (gunrock/app/sssp/sssp_functor.cuh:52-66, sssp_problem.cuh:325,372): uint32
+ * distances, UINT_MAX = unreachable, predecessor = own id for the source and unreached vertices.
+ * The graph needs edge weights.  grb_mg_stats: iterations, gpu_launches, edges_inspected =
+ * relaxations executed on all devices, nodes_visited = vertices queued over all iterations. */
+#define GRB_MGSSSP_PEER_BUFFERS 3
+typedef struct grb_mgsssp_s *grb_mgsssp_t;
+int  grb_mgsssp_create(grb_graph_t g, grb_mgsssp_t *out);
+int  grb_mgsssp_peer_export(grb_mgsssp_t ctx, unsigned char *handles /* [GRB_MGSSSP_PEER_BUFFERS * 64] */);
+int  grb_mgsssp_peer_import(grb_mgsssp_t ctx, int world,
+                            const unsigned char *all_handles /* [world][GRB_MGSSSP_PEER_BUFFERS * 64] */);
+int  grb_mgsssp_run(grb_mgsssp_t ctx, int32_t src, grb_mg_stats *out);     /* every rank, same src */
+/* distances / predecessors of the rows this device owns, local-row order (either may be NULL) */
+int  grb_mgsssp_result(grb_mgsssp_t ctx, uint32_t *dist_host, int32_t *preds_host);
+void grb_mgsssp_destroy(grb_mgsssp_t ctx);
 
 #ifdef __cplusplus
 }

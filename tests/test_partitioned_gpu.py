@@ -90,3 +90,83 @@ def test_multi_device_matches_oracle(gr, world):
         p.join(timeout=120)
         assert p.exitcode == 0
     assert all(all(r) for r in res), res
+
+
+# ---- partitioned SSSP over peer memory -------------------------------------------------------
+def _check_sssp(ro, co, w, src, dist, preds, want):
+    ok = bool(np.array_equal(dist, want))
+    # predecessors: any valid parent (the reference's benign race) -- the tree
+    # edge must exist and close the distance exactly; source and unreached vertices name themselves
+    n = ro.size - 1
+    v = np.arange(n)
+    reached = (dist != 0xFFFFFFFF) & (v != src)
+    ok &= bool(np.all(preds[~reached] == v[~reached]))
+    for x in np.nonzero(reached)[0][:20000]:
+        p = int(preds[x])
+        nb = co[ro[p]:ro[p + 1]]
+        hit = np.nonzero(nb == x)[0]
+        ok &= hit.size > 0 and int(dist[p]) + int(w[ro[p] + hit[0]]) == int(dist[x])
+    return ok
+
+
+@pytest.mark.parametrize("scale", [10, 15])
+def test_sssp_world1_matches_oracle(gr, orc, scale):
+    from gunrockinst_b200 import partitioned as pt
+    ro, co = rmat_graph(orc, scale)
+    w = orc.edge_weights(ro, co, 7)
+    g = gr.Graph.from_csr(ro, co, weights=w, symmetric=True)
+    sp = pt.PartitionedSssp(g)
+    for src in (0, 5, ro.size - 2):
+        st = sp.run(src)
+        want, _ = orc.sssp(ro, co, w, src)
+        dist_, preds = sp.gather()
+        assert _check_sssp(ro, co, w, src, dist_, preds, want)
+        assert st["iterations"] >= 1 or ro[src + 1] == ro[src]
+    sp.close()
+
+
+def _sssp_worker(rank, world, port, scale, q):
+    sys.path.insert(0, ROOT)
+    import torch
+    import torch.distributed as dist
+    import gunrockinst_b200 as gr
+    from gunrockinst_b200 import partitioned as pt
+    import oracle
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    torch.cuda.set_device(rank)
+    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device("cuda", rank))
+    try:
+        lp = world.bit_length() - 1
+        g = gr.Graph.rmat(scale, 16, device=rank, log_parts=lp, rank=rank, weight_seed=7)
+        sp = pt.PartitionedSssp(g)
+        ro, co = oracle.rmat_csr(scale, 16)
+        w = oracle.edge_weights(ro, co, 7)
+        res = []
+        for src in (0, 1, 12345 % (1 << scale)):
+            st = sp.run(src)
+            dist_, preds = sp.gather()
+            want, _ = oracle.sssp(ro, co, w, src)
+            res.append(_check_sssp(ro, co, w, src, dist_, preds, want))
+        if rank == 0:
+            q.put(res)
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("world", [2, 4, 8])
+def test_sssp_multi_device_matches_oracle(gr, world):
+    if gr.device_count() < world:
+        pytest.skip("needs %d devices" % world)
+    import torch.multiprocessing as mp
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_sssp_worker, args=(r, world, port, 15, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    res = q.get(timeout=600)
+    for p in procs:
+        p.join(timeout=120)
+        assert p.exitcode == 0
+    assert all(res), res

@@ -24,7 +24,8 @@ else:
 print("graph: n=%d m=%d built in %.1fs" % (g.nodes, g.edges, time.time() - t0), flush=True)
 PEAK = 6539.5
 for name, mode in [("warmup", dict(direction_optimized=True)),
-                   ("dobfs", dict(direction_optimized=True)), ("dobfs-host", dict(direction_optimized=True, host_loop=True)),
+                   ("dobfs", dict(direction_optimized=True)), ("dobfs-host", dict(direction_optimized=True, host_loop=1)),
+                   ("dobfs-pk", dict(direction_optimized=True, host_loop=2)),
                    ("push-auto", dict()), ("push-host", dict(host_loop=True)), ("push-lb", dict(traversal_mode=1)),
                    ("idempotent", dict(idempotence=True))]:
     bfs = gr.Bfs(g, record_levels=True, **mode)

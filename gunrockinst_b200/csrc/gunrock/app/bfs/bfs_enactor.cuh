@@ -21,6 +21,9 @@
 // compares vertex counts, dobfs_enactor.cuh:397,569, with alpha=12, beta=6 from
 // test_dobfs.cu:533-534; depths do not depend on the rule.)
 #pragma once
+#ifndef GRB_PULL_CTAS
+#define GRB_PULL_CTAS 6      // resident CTAs per SM the stand-alone pull sweep is bounded for
+#endif
 #include <vector>
 #include "bfs_functor.cuh"
 #include "../enactor_base.cuh"
@@ -120,7 +123,7 @@ class BFSEnactor : public EnactorBase {
     // degree tracking on for the fused (non-idempotent) mode
     typedef oprtr::advance::KernelPolicy<Problem, 256, 4, 5, true, true>   AdvancePolicy;
     typedef oprtr::advance::KernelPolicy<Problem, 256, 4, 5, true, false>  IdemAdvancePolicy;
-    typedef oprtr::advance::KernelPolicy<Problem, 256, 4, 4, false, false> PullPolicy;
+    typedef oprtr::advance::KernelPolicy<Problem, 256, 4, GRB_PULL_CTAS, false, false> PullPolicy;
     // reference: END_BITMASK_CULL = 5 (bfs_enactor.cuh:594); the word-atomic mask stays exact, so keep it on
     typedef oprtr::filter::KernelPolicy<Problem, 256, 4, 6, -1>            FilterPolicy;
 

@@ -145,7 +145,10 @@ __device__ __forceinline__ void BitmapToQueue(unsigned *bitmap, VertexId *queue,
     }
 }
 
-constexpr int kPersistentCtasPerSm = 4;
+#ifndef GRB_PERSISTENT_CTAS
+#define GRB_PERSISTENT_CTAS 4
+#endif
+constexpr int kPersistentCtasPerSm = GRB_PERSISTENT_CTAS;
 
 // The pull sweep as a real call: inlined into the level loop it shares the 64-register budget with
 // every value the loop keeps alive and spills (~0.85 KB per thread; the sweep of a scale-25 level

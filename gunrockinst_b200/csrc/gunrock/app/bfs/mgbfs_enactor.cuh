@@ -123,7 +123,7 @@ class MGBFSEnactor : public EnactorBase {
     typedef MgPushFunctor<VertexId, SizeT, Value, Problem>     PushFunctor;
     typedef ReverseBFSFunctor<VertexId, SizeT, Value, Problem> PullFunctor;
     typedef oprtr::advance::KernelPolicy<Problem, 256, 4, 5, true, false>  AdvancePolicy;
-    typedef oprtr::advance::KernelPolicy<Problem, 256, 4, 4, false, false> PullPolicy;
+    typedef oprtr::advance::KernelPolicy<Problem, 256, 4, GRB_PULL_CTAS, false, false> PullPolicy;
 
     oprtr::advance::LbScratch<SizeT> lb_scratch;
     int in_sel = 0;                      // frontier_queues[in_sel] is the local frontier

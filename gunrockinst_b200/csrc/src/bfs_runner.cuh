@@ -44,11 +44,11 @@ struct BfsRunner : BfsRunnerBase {
             if (cfg->beta > 0) opt.beta = cfg->beta;
             if (cfg->queue_sizing > 0) queue_sizing = cfg->queue_sizing;
             opt.record_levels = cfg->record_levels != 0;
-            // 0: choose by size -- one persistent kernel up to 2^24 vertices (a level costs less than a
+            // 0: choose by size -- one persistent kernel below 2^24 vertices (a level costs less than a
             // launch + counter fetch there), the host-driven loop of stand-alone kernels above (at scale
             // 25 they run the big levels 1.1-1.35x faster: 5 instead of 4 resident CTAs per SM, fewer
             // live registers around the operator bodies); 1: host loop; 2: persistent kernel
-            opt.host_loop = cfg->host_loop == 1 || (cfg->host_loop == 0 && g->nodes > (1ll << 24));
+            opt.host_loop = cfg->host_loop == 1 || (cfg->host_loop == 0 && g->nodes >= (1ll << 24));
         }
         GR_TRY(problem.Init(g, s));
         GR_TRY(cudaEventCreate(&e0)); GR_TRY(cudaEventCreate(&e1)); GR_TRY(cudaEventCreate(&e2));

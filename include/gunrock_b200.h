@@ -116,7 +116,7 @@ typedef struct {
     double  alpha, beta;          /* <= 0: library defaults                           */
     double  queue_sizing;         /* <= 0: 1.0                                        */
     int32_t record_levels;
-    int32_t host_loop;            /* 0: by size (one cooperative kernel up to 2^24 vertices, host-driven
+    int32_t host_loop;            /* 0: by size (one cooperative kernel below 2^24 vertices, host-driven
                                      above); 1: one launch set + counter fetch per level, driven by
                                      the host; 2: whole level loop in one cooperative kernel */
 } grb_bfs_config;

@@ -75,7 +75,7 @@ class MgStats(C.Structure):
 class MgTrace(C.Structure):
     _fields_ = [("level", C.c_int32), ("kind", C.c_int32), ("frontier", C.c_uint64), ("discovered", C.c_uint64),
                 ("edges", C.c_uint64), ("max_edges", C.c_uint64), ("exchange_bytes", C.c_uint64),
-                ("compute_ms", C.c_float), ("exchange_ms", C.c_float)]
+                ("candidates", C.c_uint64), ("compute_ms", C.c_float), ("exchange_ms", C.c_float)]
 
 
 IPC_HANDLE_BYTES, MG_PEER_BUFFERS, MGSSSP_PEER_BUFFERS = 64, 4, 3

@@ -21,6 +21,9 @@
 // compares vertex counts, dobfs_enactor.cuh:397,569, with alpha=12, beta=6 from
 // test_dobfs.cu:533-534; depths do not depend on the rule.)
 #pragma once
+#ifndef GRB_LB_CTAS
+#define GRB_LB_CTAS 8        // resident CTAs per SM of the push-direction advance kernels
+#endif
 #ifndef GRB_PULL_CTAS
 #define GRB_PULL_CTAS 6      // resident CTAs per SM the stand-alone pull sweep is bounded for
 #endif
@@ -121,7 +124,7 @@ class BFSEnactor : public EnactorBase {
     // sm_100a policies: 256-thread CTAs, 4 neighbour entries per thread per tile,
     // grids of 148 x MIN_CTAS persistent CTAs; operator-level bitmask pre-cull on,
     // degree tracking on for the fused (non-idempotent) mode
-    typedef oprtr::advance::KernelPolicy<Problem, 256, 4, 5, true, true>   AdvancePolicy;
+    typedef oprtr::advance::KernelPolicy<Problem, 256, 4, GRB_LB_CTAS, true, true>   AdvancePolicy;
     typedef oprtr::advance::KernelPolicy<Problem, 256, 4, 5, true, false>  IdemAdvancePolicy;
     typedef oprtr::advance::KernelPolicy<Problem, 256, 4, GRB_PULL_CTAS, false, false> PullPolicy;
     // reference: END_BITMASK_CULL = 5 (bfs_enactor.cuh:594); the word-atomic mask stays exact, so keep it on

@@ -145,6 +145,12 @@ __device__ __forceinline__ void BitmapToQueue(unsigned *bitmap, VertexId *queue,
     }
 }
 
+#ifndef GRB_PERSISTENT_SPECIALISE
+#define GRB_PERSISTENT_SPECIALISE true
+#endif
+#ifndef GRB_SWEEP_CALL
+#define GRB_SWEEP_CALL __forceinline__
+#endif
 #ifndef GRB_PERSISTENT_CTAS
 #define GRB_PERSISTENT_CTAS 4
 #endif
@@ -155,13 +161,13 @@ constexpr int kPersistentCtasPerSm = GRB_PERSISTENT_CTAS;
 // ran 1.7x slower than the stand-alone pull::Kernel); as a callee it gets the whole budget and
 // only the loop state that is live across the call is saved.
 template <typename PullPolicy, typename Problem, typename PullFunctor>
-__device__ __noinline__ void SweepCall(
+__device__ GRB_SWEEP_CALL void SweepCall(
     const typename Problem::DataSlice &ds,
     const oprtr::advance::pull::PullArgs<typename Problem::VertexId, typename Problem::SizeT> &pa,
     oprtr::advance::pull::SweepStorage<PullPolicy> &sm, oprtr::LevelCounters *slot_out,
     long long first_chunk, long long chunk_stride)
 {
-    oprtr::advance::pull::Sweep<PullPolicy, Problem, PullFunctor>(ds, pa, sm, slot_out, first_chunk, chunk_stride);
+    oprtr::advance::pull::Sweep<PullPolicy, Problem, PullFunctor, GRB_PERSISTENT_SPECIALISE>(ds, pa, sm, slot_out, first_chunk, chunk_stride);
 }
 
 template <typename PushPolicy, typename PullPolicy, typename Problem, typename PushFunctor, typename PullFunctor>
@@ -297,7 +303,7 @@ PersistentKernel(const __grid_constant__ typename Problem::DataSlice ds0,
                 // short frontier (first / last levels, a hub on its own): every CTA scans it privately
                 // and expands its share of the edge tiles -- one pass, all SMs, no extra barrier
                 kind = 3;
-                adv::lb::ExpandSmall<PushPolicy, Problem, PushFunctor>(ds, a, sm.push.small, sm.push.expand, F, frontier_edges,
+                adv::lb::ExpandSmall<PushPolicy, Problem, PushFunctor, GRB_PERSISTENT_SPECIALISE>(ds, a, sm.push.small, sm.push.expand, F, frontier_edges,
                                                                        slot_out, cta, num_ctas);
             } else if (!lb) {
                 kind = 0;
@@ -315,7 +321,7 @@ PersistentKernel(const __grid_constant__ typename Problem::DataSlice ds0,
                 adv::lb::ScanTiles<PushPolicy, THREADS, 4>(a, sv, sm.scan, F, slot_out, true);
                 grid.sync(); ++sum.grid_syncs;
                 if (leader) *sv.ticket = 0;
-                adv::lb::ExpandTiles<PushPolicy, Problem, PushFunctor>(ds, a, sv, sm.push.expand, F, slot_out, cta, num_ctas);
+                adv::lb::ExpandTiles<PushPolicy, Problem, PushFunctor, GRB_PERSISTENT_SPECIALISE>(ds, a, sv, sm.push.expand, F, slot_out, cta, num_ctas);
             }
         } else {
             kind = 1;

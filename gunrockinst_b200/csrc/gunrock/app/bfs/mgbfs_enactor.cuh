@@ -247,7 +247,7 @@ class MGBFSEnactor : public EnactorBase {
     // ------------------------------------------------------------------------------------------
     struct LevelTrace {
         int level, kind;                    // kind: 0 push, 1 pull
-        unsigned long long frontier, discovered, edges, max_edges, exchange_bytes;
+        unsigned long long frontier, discovered, edges, max_edges, exchange_bytes, candidates;
         float compute_ms, exchange_ms;
     };
     struct SearchStats {
@@ -420,10 +420,10 @@ class MGBFSEnactor : public EnactorBase {
             if (record) m3 = Mark(used);
             GR_TRY(ExchangeCounters());
             if (record) m4 = Mark(used);
-            unsigned long long f = 0, fe = 0, ins = 0, max_ins = 0, ovf = 0;
+            unsigned long long f = 0, fe = 0, ins = 0, max_ins = 0, ovf = 0, cands = 0;
             for (int p = 0; p < P; ++p) {
                 const oprtr::LevelCounters &c = h_all.ptr[p];
-                f += c.out_len; fe += c.out_degree; ins += c.edges; ovf += c.overflow;
+                f += c.out_len; fe += c.out_degree; ins += c.edges; ovf += c.overflow; cands += c.aux0;
                 if (c.edges > max_ins) max_ins = c.edges;
             }
             if (ovf) return util::GRError(cudaErrorInvalidConfiguration, "frontier queue overflow on a partitioned level", __FILE__, __LINE__);
@@ -437,7 +437,7 @@ class MGBFSEnactor : public EnactorBase {
             if (record) {
                 LevelTrace t;
                 t.level = (int)level; t.kind = pull ? 1 : 0;
-                t.frontier = frontier; t.discovered = f; t.edges = ins; t.max_edges = max_ins; t.exchange_bytes = lvl_bytes;
+                t.frontier = frontier; t.discovered = f; t.edges = ins; t.max_edges = max_ins; t.exchange_bytes = lvl_bytes; t.candidates = pull ? cands : 0;
                 float a = 0, b = 0, c = 0, d = 0;
                 cudaEventSynchronize(m4);
                 cudaEventElapsedTime(&a, m0, m1); cudaEventElapsedTime(&b, m1, m2);

@@ -397,7 +397,7 @@ template <typename T> struct HasPartition<T, decltype((void)(((T *)nullptr)->par
 
 // Entry: on a single device the functor block is handed over with a compile-time identity partition,
 // so the owner hash and the owner-major bit positions drop out of the per-edge code (see pull::Sweep).
-template <typename Policy, typename Problem, typename Functor, typename Scan>
+template <typename Policy, typename Problem, typename Functor, bool SPECIALISE = true, typename Scan>
 __device__ __forceinline__ void ExpandTilesFrom(
     const typename Problem::DataSlice &ds,
     const Args<typename Policy::VertexId, typename Policy::SizeT> &args,
@@ -405,7 +405,7 @@ __device__ __forceinline__ void ExpandTilesFrom(
     ExpandStorage<Policy, Problem::MARK_PREDECESSORS> &sm,
     unsigned long long in_len, LevelCounters *slot_out, unsigned cta, unsigned num_ctas)
 {
-    if constexpr (HasPartition<typename Problem::DataSlice>::value) {
+    if constexpr (SPECIALISE && HasPartition<typename Problem::DataSlice>::value) {
         if (ds.part.log_parts == 0) {
             typename Problem::DataSlice d1 = ds;
             d1.part = graph::Partition();
@@ -417,7 +417,7 @@ __device__ __forceinline__ void ExpandTilesFrom(
 }
 
 // the scanned frontier lives in the global scratch (after ScanKernel / ScanTiles)
-template <typename Policy, typename Problem, typename Functor>
+template <typename Policy, typename Problem, typename Functor, bool SPECIALISE = true>
 __device__ __forceinline__ void ExpandTiles(
     const typename Problem::DataSlice &ds,
     const Args<typename Policy::VertexId, typename Policy::SizeT> &args,
@@ -430,7 +430,7 @@ __device__ __forceinline__ void ExpandTiles(
     __syncthreads();
     const unsigned long long total = sm.red[0];
     GlobalScan<typename Policy::SizeT> scan = {scratch};
-    ExpandTilesFrom<Policy, Problem, Functor>(ds, args, scan, total, sm, in_len, slot_out, cta, num_ctas);
+    ExpandTilesFrom<Policy, Problem, Functor, SPECIALISE>(ds, args, scan, total, sm, in_len, slot_out, cta, num_ctas);
 }
 
 // Small frontiers (in_len <= SMALL_ITEMS): every CTA scans the frontier's degrees itself into shared
@@ -444,7 +444,7 @@ struct SmallScanStorage {
     unsigned long long     warp[Policy::THREADS / 32 + 1];
 };
 
-template <typename Policy, typename Problem, typename Functor>
+template <typename Policy, typename Problem, typename Functor, bool SPECIALISE = true>
 __device__ __forceinline__ void ExpandSmall(
     const typename Problem::DataSlice &ds,
     const Args<typename Policy::VertexId, typename Policy::SizeT> &args,
@@ -489,7 +489,7 @@ __device__ __forceinline__ void ExpandSmall(
     __syncthreads();
     if (cta == 0 && threadIdx.x == 0) slot_out->scan_total = running;
     LocalScan<SizeT> scan = {ss.scanned, ss.row_start, (long long)in_len};
-    ExpandTilesFrom<Policy, Problem, Functor>(ds, args, scan, running, sm, in_len, slot_out, cta, num_ctas);
+    ExpandTilesFrom<Policy, Problem, Functor, SPECIALISE>(ds, args, scan, running, sm, in_len, slot_out, cta, num_ctas);
 }
 
 template <typename Policy, typename Problem, typename Functor>

@@ -43,6 +43,9 @@
 // per inspected neighbour entry (column id + frontier bit probe), 4 per found
 // vertex (label).
 #pragma once
+#ifndef GRB_PULL_OVERLAP
+#define GRB_PULL_OVERLAP 0
+#endif
 #include "common.cuh"
 
 namespace gunrock {
@@ -185,6 +188,7 @@ __device__ __forceinline__ void SweepImpl(
 
         // ---- 2. probe, phase by phase over the whole list -------------------------------------------
         // (u * 32 < total is warp-uniform: unused phases of a short list are skipped)
+#if GRB_PULL_OVERLAP
         // the dense head array (first entry of every row, -1: empty row) is indexed by the row like the
         // offsets, so both gathers are issued together and the frontier probes below wait for the
         // head only: the chain is head -> bit, with the offsets (needed for the degree sum and the
@@ -238,6 +242,39 @@ __device__ __forceinline__ void SweepImpl(
                 if ((probe[u] >> (ds.BitPos(n0[u]) & 31)) & 1u) hits |= 1u << u;
             }
         }
+#else
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            const unsigned idx = u * 32 + lane;
+            if (u * 32 < total && idx < total) {
+                const long long row = (w0 << 5) + s_cand[idx];
+                const SizeT b = args.g.row_offsets[row], e = args.g.row_offsets[row + 1];
+                s_begin[idx] = b;
+                const unsigned long long d = (unsigned long long)(e - b);
+                s_deg[idx] = d > 0x7fffffffull ? 0x7fffffffu : (unsigned)d;
+            }
+        }
+        VertexId n0[U];
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            const unsigned idx = u * 32 + lane;
+            n0[u] = -1;
+            if (u * 32 < total && idx < total && s_deg[idx] != 0) {
+                // the dense head array turns this gather (one 128-byte line per vertex) into a
+                // coalesced read of consecutive rows
+                if (args.head) n0[u] = util::LoadStream(args.head + ((w0 << 5) + s_cand[idx]));
+                else           n0[u] = util::LoadStream(args.g.col_indices + s_begin[idx]);
+            }
+        }
+        unsigned hits = 0;
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            if (u * 32 < total && n0[u] >= 0) {
+                ++my_edges;
+                if (util::BitTest(args.frontier_in, ds.BitPos(n0[u]))) hits |= 1u << u;
+            }
+        }
+#endif
         unsigned n_retry = 0;
 #pragma unroll
         for (int u = 0; u < U; ++u) {
@@ -328,14 +365,14 @@ __device__ __forceinline__ void SweepImpl(
 // <-> local ids) is the identity.  Handing the implementation copies whose partition is a
 // compile-time constant lets the compiler drop it from every per-vertex and per-edge path (it was
 // ~10 % of the sweep's instructions); the partitioned run takes the general instance.
-template <typename Policy, typename Problem, typename Functor>
+template <typename Policy, typename Problem, typename Functor, bool SPECIALISE = true>
 __device__ __forceinline__ void Sweep(
     const typename Problem::DataSlice &ds,
     const PullArgs<typename Policy::VertexId, typename Policy::SizeT> &args,
     SweepStorage<Policy> &sm, LevelCounters *slot_out,
     long long first_chunk, long long chunk_stride)
 {
-    if (args.g.part.log_parts == 0) {
+    if (SPECIALISE && args.g.part.log_parts == 0) {
         typename Problem::DataSlice d1 = ds;       // (only the small functor block is copied: a copy
         d1.part = graph::Partition();               //  of `args` ends up in local memory)
         SweepImpl<Policy, Problem, Functor, true>(d1, args, sm, slot_out, first_chunk, chunk_stride);

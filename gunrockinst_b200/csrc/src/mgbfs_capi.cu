@@ -157,7 +157,7 @@ struct MgRunner : MgRunnerBase {
         for (const auto &t : enactor.trace) {
             if (k >= cap) break;
             out[k].level = t.level; out[k].kind = t.kind; out[k].frontier = t.frontier; out[k].discovered = t.discovered;
-            out[k].edges = t.edges; out[k].max_edges = t.max_edges; out[k].exchange_bytes = t.exchange_bytes;
+            out[k].edges = t.edges; out[k].max_edges = t.max_edges; out[k].exchange_bytes = t.exchange_bytes; out[k].candidates = t.candidates;
             out[k].compute_ms = t.compute_ms; out[k].exchange_ms = t.exchange_ms;
             ++k;
         }

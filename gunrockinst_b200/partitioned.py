@@ -134,7 +134,7 @@ class DeviceEngine:
             for r in rec[:cnt.value]:
                 out["levels"].append(dict(level=r.level, kind="pull" if r.kind else "push", frontier=r.frontier,
                                           discovered=r.discovered, edges=r.edges, local_max_edges=r.max_edges,
-                                          exchange_bytes=r.exchange_bytes, compute_ms=r.compute_ms,
+                                          exchange_bytes=r.exchange_bytes, candidates=r.candidates, compute_ms=r.compute_ms,
                                           exchange_ms=r.exchange_ms))
         return out
 
@@ -315,6 +315,7 @@ class PartitionedBfs:
                     marks.append((m0, m1, m2, m3))
                     levels.append(dict(level=level, kind="pull" if pull else "push", frontier=prev_len,
                                        discovered=frontier, edges=lvl_inspected, exchange_bytes=lvl_bytes,
+                                       candidates=int(c[:, CTR_CANDS].sum()) if pull else 0,
                                        local_max_edges=int(c[:, CTR_EDGES].max())))
                 level += 1
             ev_end = e.mark()
@@ -505,8 +506,15 @@ def bench(args, rank, world, workload_config, ClockSampler, pick_sources, measur
         exms = torch.zeros(1, dtype=torch.float64, device=dev)
         ex_bytes = 0
         lv_trace = None
+        osz = int(g.info.offset_bytes)
+        pull_bytes, pull_ms, pull_launches = 0, 0.0, 0
         for i in range(k):
             st = tr.run(sources[i % len(sources)])
+            for l in st["levels"]:
+                if l["kind"] == "pull":      # algorithmic bytes of the sweep on all devices
+                    pull_bytes += l.get("candidates", 0) * 2 * osz + 5 * l["edges"] + 4 * l["discovered"] + 3 * (eng.nodes // 8)
+                    pull_ms += l["compute_ms"]
+                    pull_launches += 1
             comp += sum(l["compute_ms"] for l in st["levels"])
             exms += sum(l["exchange_ms"] for l in st["levels"])
             ex_bytes += st["exchange_bytes"]
@@ -514,6 +522,9 @@ def bench(args, rank, world, workload_config, ClockSampler, pick_sources, measur
                 lv_trace = st["levels"]
         dist.all_reduce(comp, op=dist.ReduceOp.MAX)
         dist.all_reduce(exms, op=dist.ReduceOp.MAX)
+        pms = torch.tensor([pull_ms], dtype=torch.float64, device=dev)
+        dist.all_reduce(pms, op=dist.ReduceOp.MAX)
+        pull_ms = float(pms.item())
 
         # end to end for a resident partitioned graph: source in, this rank's labels out to the host
         torch.cuda.synchronize()
@@ -550,11 +561,15 @@ def bench(args, rank, world, workload_config, ClockSampler, pick_sources, measur
                              "achieved_gbs_per_gpu": (ex_bytes / k) / max(ex_ms * 1e-3, 1e-12) / 1e9,
                              "nvlink_peak_gbs_per_direction": 900.0,
                              "levels_per_search": levels / max(args.steps, 1), "first_search_levels": lv_trace},
-                "roofline": {"bound": "hbm", "kernel": "partitioned level kernels (advance push / pull sweep)",
-                             "achieved": None, "peak": peak, "unit": "GB/s", "frac": None, "peak_source": peak_src,
-                             "traffic": None,
-                             "note": "per-kernel roofline is reported by the single-device line; here compute and "
-                                     "exchange time per search are split above"},
+                "roofline": {"bound": "hbm", "kernel": "advance::pull::Kernel (+ visited merge), all devices",
+                             "achieved": (pull_bytes / (pull_ms * 1e-3) / 1e9) if pull_ms > 0 else None,
+                             "peak": peak * world, "unit": "GB/s",
+                             "frac": (pull_bytes / (pull_ms * 1e-3) / 1e9 / (peak * world)) if pull_ms > 0 else None,
+                             "peak_source": peak_src + " x %d devices" % world, "traffic": None,
+                             "launches_timed": pull_launches,
+                             "note": "algorithmic bytes of the pull levels on all devices over their compute time "
+                                     "(events on the stream, max over ranks); compute and exchange time per search "
+                                     "are split in `exchange`"},
                 "cpu_baseline": None,
                 "e2e": {"value": e2e_edges / max(e2e_s, 1e-9) / 1e9, "unit": "GTEPS", "h2d_bytes_per_step": 4,
                         "d2h_bytes_per_step": 4 * eng.local_nodes * world, "steps": e2e_steps,

@@ -250,6 +250,7 @@ typedef struct {
 typedef struct {
     int32_t  level, kind;        /* kind: 0 push, 1 pull */
     uint64_t frontier, discovered, edges, max_edges, exchange_bytes;
+    uint64_t candidates;         /* pull: unvisited vertices examined, all devices */
     float    compute_ms, exchange_ms;
 } grb_mg_trace;
 int  grb_mgbfs_peer_export(grb_mgbfs_t ctx, unsigned char *handles /* [GRB_MG_PEER_BUFFERS * 64] */);

@@ -21,6 +21,12 @@
 // compares vertex counts, dobfs_enactor.cuh:397,569, with alpha=12, beta=6 from
 // test_dobfs.cu:533-534; depths do not depend on the rule.)
 #pragma once
+#ifndef GRB_FILTER_IPT
+#define GRB_FILTER_IPT 4      // filter: items per thread per tile
+#endif
+#ifndef GRB_FILTER_CTAS
+#define GRB_FILTER_CTAS 6     // filter: resident CTAs per SM
+#endif
 #ifndef GRB_LB_CTAS
 #define GRB_LB_CTAS 8        // resident CTAs per SM of the push-direction advance kernels
 #endif
@@ -128,12 +134,12 @@ class BFSEnactor : public EnactorBase {
     typedef oprtr::advance::KernelPolicy<Problem, 256, 4, 5, true, false>  IdemAdvancePolicy;
     typedef oprtr::advance::KernelPolicy<Problem, 256, 4, GRB_PULL_CTAS, false, false> PullPolicy;
     // reference: END_BITMASK_CULL = 5 (bfs_enactor.cuh:594); the word-atomic mask stays exact, so keep it on
-    typedef oprtr::filter::KernelPolicy<Problem, 256, 4, 6, -1>            FilterPolicy;
+    typedef oprtr::filter::KernelPolicy<Problem, 256, GRB_FILTER_IPT, GRB_FILTER_CTAS, -1> FilterPolicy;
 
     oprtr::advance::LbScratch<SizeT> lb_scratch;
     std::vector<LevelRecord> levels;
     unsigned long long edges_visited = 0;       // sum of out-degrees of visited vertices (reference GTEPS numerator)
-    cudaEvent_t ev_a = nullptr, ev_b = nullptr;
+    cudaEvent_t ev_a = nullptr, ev_b = nullptr, ev_c = nullptr;
     bool set_up = false;
     // persistent (single cooperative kernel) loop
     static const int kMaxRecords = 1024;
@@ -152,6 +158,7 @@ class BFSEnactor : public EnactorBase {
     {
         if (ev_a) cudaEventDestroy(ev_a);
         if (ev_b) cudaEventDestroy(ev_b);
+        if (ev_c) cudaEventDestroy(ev_c);
     }
 
     // one-time allocations (outside any timed region; the reference cudaMallocs its
@@ -164,7 +171,7 @@ class BFSEnactor : public EnactorBase {
         if (max_items < items) max_items = items;
         GR_TRY(lb_scratch.Allocate(max_items, (size_t)problem->graph->edges + 1, AdvancePolicy::SCAN_TILE,
                                    AdvancePolicy::TILE_EDGES, s));
-        if (!ev_a) { GR_TRY(cudaEventCreate(&ev_a)); GR_TRY(cudaEventCreate(&ev_b)); }
+        if (!ev_a) { GR_TRY(cudaEventCreate(&ev_a)); GR_TRY(cudaEventCreate(&ev_b)); GR_TRY(cudaEventCreate(&ev_c)); }
         if constexpr (!Problem::ENABLE_IDEMPOTENCE) GR_TRY(SetupPersistent(problem));
         set_up = true;
         return cudaSuccess;
@@ -498,10 +505,13 @@ class BFSEnactor : public EnactorBase {
             DataSlice ds = problem->MakeDataSlice(level);
             AdvArgs a = PushArgs(problem, level);
             oprtr::advance::MODE mode = (opt.traversal_mode == 2) ? oprtr::advance::TWC_FORWARD
-                                      : (opt.traversal_mode == 1 || F > 4096) ? oprtr::advance::LB
+                                      : (opt.traversal_mode == 1 || F > 4096 ||
+                                         (level == 0 && problem->src_degree >= opt.lb_min_edges)) ? oprtr::advance::LB
                                       : oprtr::advance::TWC_FORWARD;
+            if (opt.record_levels) GR_TRY(cudaEventRecord(ev_a, stream));
             GR_TRY((oprtr::advance::LaunchKernel<IdemAdvancePolicy, Problem, BfsFunctor>(
                 mode, dev, ds, a, &lb_scratch, (unsigned long long)g.edges, stream)));
+            if (opt.record_levels) GR_TRY(cudaEventRecord(ev_b, stream));
             enactor_stats.launches += (mode == oprtr::advance::LB) ? 3 : 2;
             frontier_attribute.queue_index++;
             frontier_attribute.selector ^= 1;
@@ -518,6 +528,7 @@ class BFSEnactor : public EnactorBase {
             fa.iteration = level + 1;
             fa.compact = true;
             GR_TRY((oprtr::filter::LaunchKernel<FilterPolicy, Problem, BfsFunctor>(dev.sm_count, ds, fa, stream)));
+            if (opt.record_levels) GR_TRY(cudaEventRecord(ev_c, stream));
             // one fetch covers both slots (advance wrote queue_index, filter queue_index + 1)
             oprtr::LevelCounters ca, cf;
             GR_TRY(work_progress.Fetch(frontier_attribute.queue_index, ca, stream));
@@ -530,6 +541,18 @@ class BFSEnactor : public EnactorBase {
             enactor_stats.algo_bytes += F * (4 + 2 * osz) + 5 * ca.edges + 4 * ca.out_len     // advance
                                       + 5 * ca.out_len + 8 * cf.out_len;                          // filter
             ++enactor_stats.push_levels;
+            if (opt.record_levels) {
+                // two records per level: the advance (every neighbour emitted) and the filter that culls and
+                // compacts them (kind 4: frontier = items read, discovered = items kept)
+                LevelRecord ra, rf;
+                ra.level = level; ra.pull = (mode == oprtr::advance::LB) ? 2 : 0;
+                ra.frontier = F; ra.edges = ca.edges; ra.discovered = ca.out_len; ra.candidates = 0; ra.switch_ms = 0;
+                rf.level = level; rf.pull = 4;
+                rf.frontier = ca.out_len; rf.edges = 0; rf.discovered = cf.out_len; rf.candidates = 0; rf.switch_ms = 0;
+                GR_TRY(cudaEventElapsedTime(&ra.ms, ev_a, ev_b));
+                GR_TRY(cudaEventElapsedTime(&rf.ms, ev_b, ev_c));
+                levels.push_back(ra); levels.push_back(rf);
+            }
             frontier_attribute.queue_length = cf.out_len;
             frontier_attribute.queue_index++;
             frontier_attribute.selector ^= 1;

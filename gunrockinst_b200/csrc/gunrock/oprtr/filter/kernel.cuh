@@ -24,6 +24,9 @@
 // Algorithmic HBM bytes per call: 4 per input item (+1 mask probe when
 // culling by bitmask) + 4 per output item.
 #pragma once
+#ifndef GRB_FILTER_MASK_LOAD
+#define GRB_FILTER_MASK_LOAD util::LoadCA
+#endif
 #include "../work_progress.cuh"
 #include "../../util/device_intrinsics.cuh"
 
@@ -124,7 +127,7 @@ Kernel(const __grid_constant__ typename Problem::DataSlice ds,
                 unsigned word[IPT];
 #pragma unroll
                 for (int r = 0; r < IPT; ++r)
-                    word[r] = (id[r] >= 0) ? util::LoadCA(ds.d_visited_mask + (ds.BitPos(id[r]) >> 5)) : 0u;
+                    word[r] = (id[r] >= 0) ? GRB_FILTER_MASK_LOAD(ds.d_visited_mask + (ds.BitPos(id[r]) >> 5)) : 0u;
 #pragma unroll
                 for (int r = 0; r < IPT; ++r) {
                     if (id[r] < 0) continue;

@@ -1,0 +1,73 @@
+"""The command-line rig (tests/rigs/gunrock_rig.c), counterpart of the reference's
+tests/{bfs,dobfs,sssp,cc,pr}/test_*.cu programs: option parsing on the CPU, full runs with the
+built-in CPU validation on the GPU (market and rmat graph types, the reference's flags)."""
+import os
+import subprocess
+
+import numpy as np
+import pytest
+
+from conftest import ROOT
+
+RIG = os.path.join(ROOT, "tests", "_bin", "gunrock_rig")
+
+
+def _build():
+    subprocess.check_call(["make", "-s", "-C", os.path.join(ROOT, "tests", "rigs")])
+
+
+def test_rig_builds_and_prints_usage():
+    _build()
+    p = subprocess.run([RIG], capture_output=True, text=True)
+    assert p.returncode == 1 and "market <file>" in p.stdout and "--traversal-mode" in p.stdout
+    p = subprocess.run([RIG, "bfs", "nonsense"], capture_output=True, text=True)
+    assert p.returncode == 1
+
+
+def _write_mtx(path, n, edges, values=None):
+    with open(path, "w") as f:
+        f.write("%%MatrixMarket matrix coordinate %s general\n" % ("integer" if values is not None else "pattern"))
+        f.write("%d %d %d\n" % (n, n, len(edges)))
+        for k, (a, b) in enumerate(edges):
+            f.write("%d %d%s\n" % (a + 1, b + 1, "" if values is None else " %d" % values[k]))
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("args", [
+    ["bfs"], ["bfs", "--mark-pred"], ["bfs", "--idempotence=1"], ["bfs", "--traversal-mode=1", "--src=largestdegree"],
+    ["bfs", "--traversal-mode=2", "--src=3", "--iteration-num=3"], ["dobfs"], ["dobfs", "--src=largestdegree", "--v"],
+    ["sssp"], ["sssp", "--delta-factor=4", "--src=5"], ["cc"], ["pr"], ["pr", "--src=0", "--max-iter=50", "--error=1e-7"]])
+def test_rig_market(tmp_path, args):
+    _build()
+    rng = np.random.RandomState(7)
+    n = 600
+    edges = [(int(a), int(b)) for a, b in rng.randint(0, n - 40, size=(3000, 2))]      # last 40 vertices stay isolated
+    vals = [int(v) for v in rng.randint(1, 65, size=len(edges))]
+    path = str(tmp_path / "g.mtx")
+    _write_mtx(path, n, edges, vals if args[0] == "sssp" else None)
+    p = subprocess.run([RIG, args[0], "market", path, "--undirected"] + args[1:], capture_output=True, text=True, timeout=300)
+    assert p.returncode == 0, p.stdout[-2000:] + p.stderr[-2000:]
+    assert "TEST PASSED" in p.stdout and "INCORRECT" not in p.stdout
+    if args[0] in ("bfs", "dobfs", "sssp") and not ("--idempotence=1" in args and "--mark-pred" in args):
+        assert "Label Validity: CORRECT" in p.stdout
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("prim", ["bfs", "dobfs", "sssp", "cc", "pr"])
+def test_rig_rmat(prim):
+    _build()
+    p = subprocess.run([RIG, prim, "rmat", "--rmat_scale=14", "--rmat_edgefactor=8"], capture_output=True, text=True, timeout=600)
+    assert p.returncode == 0, p.stdout[-2000:] + p.stderr[-2000:]
+    assert "TEST PASSED" in p.stdout
+    edges = int(p.stdout.split(" nodes, ")[1].split(" directed edges")[0])
+    assert edges > (1 << 14) * 8        # a real graph was generated (duplicates and self loops removed)
+
+
+@pytest.mark.gpu
+def test_rig_directed_market_bfs(tmp_path):
+    # no --undirected: the reader's (col, row) convention decides the edge direction (graphio/market.cuh:139-141)
+    _build()
+    path = str(tmp_path / "d.mtx")
+    _write_mtx(path, 6, [(0, 1), (1, 2), (2, 3), (4, 5)])
+    p = subprocess.run([RIG, "bfs", "market", path, "--src=3"], capture_output=True, text=True, timeout=120)
+    assert p.returncode == 0 and "Label Validity: CORRECT" in p.stdout, p.stdout + p.stderr

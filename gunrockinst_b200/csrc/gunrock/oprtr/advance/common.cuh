@@ -75,6 +75,7 @@ struct Stager {
                 if (fb + k < args.out_cap) args.out_queue[fb + k] = v;
                 else slot_out->overflow = 1;
                 if constexpr (Policy::TRACK_OUT_DEGREE) {
+                    if (OutputIsEdges(args.type)) v = args.g.col_indices[v];       // degree of the vertex the edge points to
                     if (args.g.part.Mine(v)) {
                         long long row = args.g.part.Local(v);
                         out_degree += (unsigned long long)(args.g.row_offsets[row + 1] - args.g.row_offsets[row]);

@@ -22,8 +22,13 @@ enum MODE {
     LB_BACKWARD     // alias of the pull direction kept for source compatibility
 };
 
-// what a frontier holds (only vertex -> vertex is on the accelerated path)
+// what the input / output frontier holds (reference: advance::TYPE, oprtr/advance/kernel_policy.cuh:54-60):
+// an input EDGE id stands for the vertex that edge points to (edge_map_partitioned/kernel.cuh:356-359,
+// 385-388); an output edge frontier receives the CSR entry index of every successful edge instead of
+// its destination (:409-413).  Edge ids travel in VertexId queues, as in the reference (SizeT = int).
 enum TYPE { V2V, V2E, E2V, E2E };
+__host__ __device__ __forceinline__ bool InputIsEdges(TYPE t)  { return t == E2V || t == E2E; }
+__host__ __device__ __forceinline__ bool OutputIsEdges(TYPE t) { return t == V2E || t == E2E; }
 
 // how successful edges are written
 enum OUTPUT {
@@ -79,6 +84,7 @@ struct Args {
     long long           queue_index;            // accumulate into slot queue_index+1
     long long           iteration;              // passed as s_id when !MARK_PREDECESSORS
     OUTPUT              output;
+    TYPE                type = V2V;
 };
 
 // scratch the LB mode needs; sized once for the largest frontier (no per-call cudaMalloc,

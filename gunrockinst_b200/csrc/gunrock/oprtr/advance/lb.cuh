@@ -144,6 +144,11 @@ __device__ __forceinline__ void ScanTiles(
             item[r] = -1;
             if (i < in_len) item[r] = args.in_queue ? util::LoadCG(args.in_queue + i) : (VertexId)args.g.part.Global((long long)i);
         }
+        if (InputIsEdges(args.type) && args.in_queue) {         // an edge id stands for the vertex it points to
+#pragma unroll
+            for (int r = 0; r < R; ++r)
+                item[r] = (item[r] >= 0 && (long long)item[r] < args.g.edges) ? args.g.col_indices[item[r]] : (VertexId)-1;
+        }
 #pragma unroll
         for (int r = 0; r < R; ++r) {
             deg[r] = 0; first[r] = 0;
@@ -210,6 +215,16 @@ struct ExpandStorage {
     StagerStorage<Policy> stager;
     unsigned long long red[Policy::THREADS / 32 + 1];
 };
+
+// the vertex behind input item i (an edge id stands for the vertex it points to)
+template <typename VertexId, typename SizeT>
+__device__ __forceinline__ VertexId SourceOf(const Args<VertexId, SizeT> &args, long long i)
+{
+    if (!args.in_queue) return (VertexId)args.g.part.Global(i);
+    const VertexId x = args.in_queue[i];
+    if (InputIsEdges(args.type)) return (x >= 0 && (long long)x < args.g.edges) ? args.g.col_indices[x] : (VertexId)-1;
+    return x;
+}
 
 // where ExpandTiles finds the scanned frontier: the global scratch ScanKernel filled ...
 template <typename SizeT>
@@ -287,7 +302,7 @@ __device__ __forceinline__ void ExpandTilesFromImpl(
                 const ScanT s = scan.Scanned(i0 + j), e = scan.Scanned(i0 + j + 1);
                 const long long rel = (long long)s - (long long)tile_start;     // < 0 only for j == 0
                 sm.base[j] = (SizeT)((long long)scan.RowStart(i0 + j) - rel);
-                if constexpr (NEED_SRC) sm.src[j] = args.in_queue ? args.in_queue[i0 + j] : (VertexId)args.g.part.Global(i0 + j);
+                if constexpr (NEED_SRC) sm.src[j] = SourceOf(args, i0 + j);
                 const int slot = rel < 0 ? 0 : (int)rel;
                 if (e > s && slot < TILE_E) {       // unique: the lists that start inside a tile start at distinct slots
                     sm.own[slot] = j;
@@ -365,18 +380,17 @@ __device__ __forceinline__ void ExpandTilesFromImpl(
             bool ok = false;
             if (live[r]) {
                 VertexId s_id;
-                if constexpr (NEED_SRC) s_id = windowed ? sm.src[item[r]]
-                                      : (args.in_queue ? args.in_queue[i0 + item[r]] : (VertexId)args.g.part.Global(i0 + item[r]));
+                if constexpr (NEED_SRC) s_id = windowed ? sm.src[item[r]] : SourceOf(args, i0 + item[r]);
                 else                    s_id = (VertexId)args.iteration;
                 ok = VisitEdge<Policy, Problem, Functor>(&ds, s_id, nbr[r], pos[r], (SizeT)(i0 + item[r]));
             }
             if (args.output == OUT_COMPACT) {
-                stager.Push(ok, nbr[r]);
+                stager.Push(ok, OutputIsEdges(args.type) ? (VertexId)pos[r] : nbr[r]);
             } else if (args.output == OUT_TOMBSTONE) {
                 const int ly = r * THREADS + threadIdx.x;
                 if (ly < tile_edges) {
                     const unsigned long long y = tile_start + ly;
-                    if (y < args.out_cap) args.out_queue[y] = ok ? nbr[r] : (VertexId)-1;
+                    if (y < args.out_cap) args.out_queue[y] = ok ? (OutputIsEdges(args.type) ? (VertexId)pos[r] : nbr[r]) : (VertexId)-1;
                     else slot_out->overflow = 1;
                 }
             }
@@ -466,6 +480,11 @@ __device__ __forceinline__ void ExpandSmall(
         const unsigned long long i = (unsigned long long)r * T + threadIdx.x;
         item[r] = -1;
         if (i < in_len) item[r] = args.in_queue ? util::LoadCG(args.in_queue + i) : (VertexId)args.g.part.Global((long long)i);
+    }
+    if (InputIsEdges(args.type) && args.in_queue) {
+#pragma unroll
+        for (int r = 0; r < R; ++r)
+            item[r] = (item[r] >= 0 && (long long)item[r] < args.g.edges) ? args.g.col_indices[item[r]] : (VertexId)-1;
     }
 #pragma unroll
     for (int r = 0; r < R; ++r) {

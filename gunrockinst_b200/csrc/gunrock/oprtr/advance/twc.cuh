@@ -87,7 +87,7 @@ __device__ __forceinline__ void ExpandItems(
                 b = __shfl_sync(util::kFullMask, b, leader);
                 if (ok) {
                     const unsigned long long at = b + __popc(m & ((1u << lane) - 1));
-                    if (at < args.out_cap) args.out_queue[at] = nbr;
+                    if (at < args.out_cap) args.out_queue[at] = OutputIsEdges(args.type) ? (VertexId)pos : nbr;
                     else slot_out->overflow = 1;
                     if constexpr (Policy::TRACK_OUT_DEGREE) {
                         if (args.g.part.Mine(nbr)) {
@@ -107,6 +107,8 @@ __device__ __forceinline__ void ExpandItems(
         long long begin = 0, end = 0;
         if (i < in_len) {
             v = args.in_queue ? util::LoadCG(args.in_queue + i) : (VertexId)args.g.part.Global((long long)i);
+            if (InputIsEdges(args.type) && args.in_queue)       // an edge id stands for the vertex it points to
+                v = (v >= 0 && (long long)v < args.g.edges) ? args.g.col_indices[v] : (VertexId)-1;
             if (v >= 0 && (long long)v < args.g.nodes) {
                 long long row = args.g.part.Local(v);
                 begin = (long long)args.g.row_offsets[row];

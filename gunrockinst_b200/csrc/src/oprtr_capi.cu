@@ -95,6 +95,9 @@ cudaError_t RunAdvance(gunrock::graph::DeviceCsr<int, SizeT> *g, cudaStream_t s,
     a.in_len = (unsigned long long)in_len; a.d_in_len = nullptr;
     a.out_cap = (unsigned long long)out_cap;
     a.slots = wp.d_slots.ptr; a.queue_index = 0; a.iteration = 7;
+    // bits 4-5 of `mode`: what the frontiers hold (0 V2V, 1 V2E, 2 E2V, 3 E2E)
+    a.type = (oprtr::advance::TYPE)((mode >> 4) & 3);
+    mode &= 15;
     a.output = output == 0 ? oprtr::advance::OUT_NONE : (output == 1 ? oprtr::advance::OUT_COMPACT : oprtr::advance::OUT_TOMBSTONE);
     if (mode == 0 && a.output == oprtr::advance::OUT_TOMBSTONE)
         return util::GRError(cudaErrorInvalidValue, "tombstone output exists in LB mode only", __FILE__, __LINE__);

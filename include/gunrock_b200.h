@@ -160,7 +160,10 @@ int grb_topk(int device, int64_t nodes, const int32_t *row_offsets_host, const i
  *   CondEdge(s,d,e)  : edge_hits[e] += 1; src_sum[d] += s; return ((s + d) % 3) != 0
  *   ApplyEdge(s,d,e) : dst_hits[d] += 1
  *   CondFilter(v)    : return v % 2 == 0        ApplyFilter(v): dst_hits[v] += 1
- * mode: 0 TWC, 1 LB.  output: 0 none, 1 compact, 2 tombstone (LB only).
+ * mode: 0 TWC, 1 LB, plus 16 * frontier type (0 V2V, 1 V2E, 2 E2V, 3 E2E: an input edge id stands
+ * for the vertex that edge points to, an output edge frontier receives CSR entry indices --
+ * reference advance::TYPE, oprtr/advance/kernel_policy.cuh:54-60).
+ * output: 0 none, 1 compact, 2 tombstone (LB only).
  * All array arguments are host pointers; out_queue must hold out_cap ids. */
 int grb_test_advance(grb_graph_t g, int mode, int output,
                      const int32_t *in_queue, int64_t in_len,

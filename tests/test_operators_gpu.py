@@ -69,6 +69,43 @@ def test_advance_contract(gr, orc, mode, scale):
     g.close()
 
 
+@pytest.mark.parametrize("mode", [0, 1], ids=["twc", "lb"])
+@pytest.mark.parametrize("atype", [1, 2, 3], ids=["V2E", "E2V", "E2E"])
+def test_advance_frontier_types(gr, orc, mode, atype):
+    """reference advance::TYPE (oprtr/advance/kernel_policy.cuh:54-60): an input EDGE id stands for the vertex
+    the edge points to (edge_map_partitioned/kernel.cuh:356-359); an output edge frontier receives the CSR
+    entry index of each successful edge (:409-413)"""
+    ro, co = rmat_graph(orc, 10, 8)
+    n, m = ro.size - 1, co.size
+    g = gr.Graph.from_csr(ro, co)
+    rng = np.random.RandomState(atype)
+    in_edges, out_edges = atype in (2, 3), atype in (1, 3)
+    queues = [rng.randint(0, m if in_edges else n, 500), np.array([3, -1, 3, (m if in_edges else n) + 5, 0]),
+              np.arange(m if in_edges else n)[::7]]
+    for q in queues:
+        while True:     # the harness sizes the LB scratch for m expanded entries (a frontier without duplicates)
+            verts = [(int(co[x]) if 0 <= x < m else -1) for x in q] if in_edges else list(q)
+            if sum(int(ro[v + 1] - ro[v]) for v in verts if 0 <= v < n) <= m:
+                break
+            q = q[:len(q) // 2]
+        eh, ss, dh, slots = expect_advance(ro, co, verts, n)
+        eids = []                                                    # CSR entry behind every slot, frontier order
+        for s in verts:
+            if 0 <= s < n:
+                eids.extend(range(ro[s], ro[s + 1]))
+        eids = np.array(eids, dtype=np.int64)
+        want = np.where(slots >= 0, eids, -1) if out_edges else slots
+        for output in [0, 1] + ([2] if mode == 1 else []):
+            out, out_len, geh, gss, gdh, insp = run_advance(gr, g, mode + 16 * atype, output, q, slots.size + 8, n, m)
+            assert np.array_equal(geh, eh) and np.array_equal(gss, ss) and np.array_equal(gdh, dh)
+            assert insp == slots.size
+            if output == 1:
+                assert np.array_equal(np.sort(out), np.sort(want[want >= 0]))
+            elif output == 2:
+                assert np.array_equal(out, want)
+    g.close()
+
+
 def test_advance_reports_overflow(gr, orc):
     ro, co = rmat_graph(orc, 10, 8)
     n, m = ro.size - 1, co.size

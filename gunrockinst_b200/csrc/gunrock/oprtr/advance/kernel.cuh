@@ -10,6 +10,7 @@
 #include "lb.cuh"
 #include "twc.cuh"
 #include "pull.cuh"
+#include "reduce.cuh"
 
 namespace gunrock {
 namespace oprtr {

@@ -131,6 +131,67 @@ extern "C" int grb_test_advance(grb_graph_t g, int mode, int output, const int32
                                                 out_len, edge_hits, src_sum, dst_hits, edges_inspected));
 }
 
+template <typename SizeT>
+cudaError_t RunNeighborReduce(gunrock::graph::DeviceCsr<int, SizeT> *g, cudaStream_t s, int op, int rtype, int atype,
+                              const int32_t *in_queue, int64_t in_len, const int32_t *values, int32_t *reduced,
+                              int32_t *out_queue, int64_t out_cap, int64_t *out_len)
+{
+    using namespace gunrock;
+    typedef ProbeProblem<SizeT> Problem;
+    typedef ProbeFunctor<Problem> Functor;
+    typedef oprtr::advance::KernelPolicy<Problem, 256, 4, 5, false, false> Policy;
+    const size_t n = (size_t)g->nodes, m = (size_t)g->edges;
+    util::DeviceArray<int> d_in, d_out, d_eh, d_dh, d_val, d_red;
+    util::DeviceArray<long long> d_ss;
+    oprtr::WorkProgress wp;
+    oprtr::advance::DeviceInfo dev;
+    GR_TRY(dev.Query(g->device));
+    GR_TRY(wp.Setup(s));
+    if (in_queue) GR_TRY(d_in.FromHost(in_queue, (size_t)in_len, s));
+    GR_TRY(d_val.FromHost(values, rtype == 2 ? m : n, s));
+    GR_TRY(d_red.Allocate((size_t)in_len + 1));
+    GR_TRY(d_out.Allocate((size_t)out_cap + 1));
+    GR_TRY(d_eh.Allocate(m + 1)); GR_TRY(d_eh.Zero(s));
+    GR_TRY(d_dh.Allocate(n + 1)); GR_TRY(d_dh.Zero(s));
+    GR_TRY(d_ss.Allocate(n + 1)); GR_TRY(d_ss.Zero(s));
+    typename Problem::DataSlice ds;
+    ds.edge_hits = d_eh.ptr; ds.src_sum = d_ss.ptr; ds.dst_hits = d_dh.ptr;
+    ds.nodes = g->nodes; ds.local_nodes = g->local_nodes; ds.part = g->part;
+    oprtr::advance::Args<int, SizeT> a;
+    a.g = g->View();
+    a.in_queue = in_queue ? d_in.ptr : nullptr;
+    a.out_queue = out_queue ? d_out.ptr : nullptr;
+    a.in_len = (unsigned long long)in_len; a.d_in_len = nullptr; a.out_cap = (unsigned long long)out_cap;
+    a.slots = wp.d_slots.ptr; a.queue_index = 0; a.iteration = 7;
+    a.output = out_queue ? oprtr::advance::OUT_COMPACT : oprtr::advance::OUT_NONE;
+    a.type = (oprtr::advance::TYPE)(atype & 3);
+    oprtr::advance::ReduceArgs<int> r;
+    r.values = d_val.ptr; r.reduced = d_red.ptr;
+    r.op = (oprtr::advance::REDUCE_OP)op; r.rtype = (oprtr::advance::REDUCE_TYPE)rtype;
+    GR_TRY((oprtr::advance::LaunchNeighborReduce<Policy, Problem, Functor, int>(dev.sm_count, ds, a, r, s)));
+    oprtr::LevelCounters c;
+    GR_TRY(wp.Fetch(1, c, s));
+    if (out_len) *out_len = c.overflow ? -1 : (int64_t)c.out_len;
+    if (out_queue) {
+        size_t k = (size_t)(c.out_len < (unsigned long long)out_cap ? c.out_len : (unsigned long long)out_cap);
+        GR_TRY(d_out.ToHost(out_queue, k, s));
+    }
+    if (reduced) GR_TRY(d_red.ToHost(reduced, (size_t)in_len, s));
+    return cudaStreamSynchronize(s);
+}
+
+extern "C" int grb_test_neighbor_reduce(grb_graph_t g, int op, int rtype, int atype, const int32_t *in_queue, int64_t in_len,
+                                        const int32_t *values, int32_t *reduced, int32_t *out_queue, int64_t out_cap,
+                                        int64_t *out_len)
+{
+    if (!g || in_len < 0 || out_cap < 0 || !values || rtype < 1 || rtype > 2) return (int)cudaErrorInvalidValue;
+    GRB_TRY(cudaSetDevice(g->device()));
+    return (int)(g->g32 ? RunNeighborReduce<int>(g->g32, g->stream, op, rtype, atype, in_queue, in_len, values, reduced,
+                                                 out_queue, out_cap, out_len)
+                        : RunNeighborReduce<long long>(g->g64, g->stream, op, rtype, atype, in_queue, in_len, values,
+                                                       reduced, out_queue, out_cap, out_len));
+}
+
 extern "C" int grb_test_filter(int device, int64_t nodes, int compact, const int32_t *in_queue, int64_t in_len,
                                int32_t *out_queue, int64_t out_cap, int64_t *out_len, int32_t *dst_hits)
 {

@@ -170,6 +170,15 @@ int grb_test_advance(grb_graph_t g, int mode, int output,
                      int32_t *out_queue, int64_t out_cap, int64_t *out_len,
                      int32_t *edge_hits, int64_t *src_sum, int32_t *dst_hits,
                      uint64_t *edges_inspected);
+/* neighbour-reduce advance (reference: advance::LaunchKernel with R_OP / R_TYPE,
+ * oprtr/advance/kernel.cuh:731-761): reduced[i] = op over the edges (s, d, e) of input item i that
+ * pass the probe functor's CondEdge of values[d] (rtype 1, VERTEX: n values) or values[e] (rtype 2,
+ * EDGE: m values); identity when none passes.  op: the reference's REDUCE_OP numbering
+ * (1 PLUS, 3 MULTIPLIES, 5 BIT_OR, 6 BIT_AND, 7 BIT_XOR, 8 MAXIMUM, 9 MINIMUM).  atype: frontier
+ * type as above.  out_queue (optional) receives the compacted output frontier. */
+int grb_test_neighbor_reduce(grb_graph_t g, int op, int rtype, int atype,
+                             const int32_t *in_queue, int64_t in_len, const int32_t *values,
+                             int32_t *reduced, int32_t *out_queue, int64_t out_cap, int64_t *out_len);
 int grb_test_filter(int device, int64_t nodes, int compact,
                     const int32_t *in_queue, int64_t in_len,
                     int32_t *out_queue, int64_t out_cap, int64_t *out_len,

@@ -106,6 +106,50 @@ def test_advance_frontier_types(gr, orc, mode, atype):
     g.close()
 
 
+@pytest.mark.parametrize("op", [1, 3, 5, 6, 7, 8, 9], ids=["plus", "mul", "or", "and", "xor", "max", "min"])
+@pytest.mark.parametrize("rtype", [1, 2], ids=["vertex", "edge"])
+def test_neighbor_reduce(gr, orc, op, rtype):
+    """reference: advance with R_OP / R_TYPE + SegReduceCsr (oprtr/advance/kernel.cuh:731-761,
+    edge_map_partitioned/kernel.cuh:417-470): accepted edges contribute values[d] / values[e], rejected ones
+    and empty lists the operator's identity"""
+    ro, co = rmat_graph(orc, 10, 8)
+    n, m = ro.size - 1, co.size
+    g = gr.Graph.from_csr(ro, co)
+    rng = np.random.RandomState(10 * op + rtype)
+    values = (rng.randint(1, 3, m if rtype == 2 else n) if op == 3 else rng.randint(-1000, 1000, m if rtype == 2 else n)).astype(np.int32)
+    ident = {1: 0, 3: 1, 5: 0, 6: -1, 7: 0, 8: -2**31, 9: 2**31 - 1}[op]
+    fold = {1: lambda a, b: a + b, 3: lambda a, b: a * b, 5: lambda a, b: a | b, 6: lambda a, b: a & b,
+            7: lambda a, b: a ^ b, 8: max, 9: min}[op]
+    L = gr._capi.lib()
+    p = lambda a: a.ctypes.data_as(C.c_void_p) if a is not None else None
+    for atype, q in ((0, np.concatenate([rng.randint(0, n, 400), [-1, n + 2, 0]])), (0, None), (2, rng.randint(0, m, 300))):
+        items = np.arange(n) if q is None else q
+        verts = [(int(co[x]) if 0 <= x < m else -1) for x in items] if atype == 2 else list(items)
+        want, emitted = [], []
+        for s in verts:
+            acc = ident
+            if 0 <= s < n:
+                for e in range(ro[s], ro[s + 1]):
+                    d = int(co[e])
+                    if (s + d) % 3 != 0:
+                        acc = fold(acc, int(values[e if rtype == 2 else d]))
+                        if op == 3:
+                            acc = ((acc + 2**31) % 2**32) - 2**31        # int32 wrap-around of the product
+                        emitted.append(d)
+            want.append(acc)
+        qq = np.ascontiguousarray(q, dtype=np.int32) if q is not None else None
+        got = np.zeros(len(items), np.int32)
+        out = np.zeros(len(emitted) + 8, np.int32)
+        out_len = C.c_int64()
+        rc = L.grb_test_neighbor_reduce(g._h, op, rtype, atype, p(qq), len(items), p(values), p(got), p(out), out.size,
+                                        C.byref(out_len))
+        assert rc == 0
+        assert np.array_equal(got.astype(np.int64), np.array(want, dtype=np.int64))
+        assert out_len.value == len(emitted)
+        assert np.array_equal(np.sort(out[:out_len.value]), np.sort(np.array(emitted, dtype=np.int32)))
+    g.close()
+
+
 def test_advance_reports_overflow(gr, orc):
     ro, co = rmat_graph(orc, 10, 8)
     n, m = ro.size - 1, co.size

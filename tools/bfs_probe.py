@@ -28,6 +28,8 @@ for name, mode in [("warmup", dict(direction_optimized=True)),
                    ("dobfs-pk", dict(direction_optimized=True, host_loop=2)),
                    ("push-auto", dict()), ("push-host", dict(host_loop=True)), ("push-lb", dict(traversal_mode=1)),
                    ("idempotent", dict(idempotence=True))]:
+    if os.environ.get("PROBE_ONLY") and name not in os.environ["PROBE_ONLY"].split(","):
+        continue
     bfs = gr.Bfs(g, record_levels=True, **mode)
     best = None
     for r in range(runs):

@@ -266,13 +266,27 @@ def _config(**kw):
     return c
 
 
+class _MallocBlock:
+    """Owner of a buffer the library malloc()ed for the caller: free()s it when the last view goes."""
+
+    def __init__(self, ptr):
+        self.ptr = ptr
+
+    def __del__(self):
+        ptr, self.ptr = self.ptr, None
+        if ptr and _capi is not None and getattr(_capi, "free_host", None) is not None:   # (module teardown)
+            _capi.free_host(ptr)          # caller frees (shared_lib_tests/test_bfs.c:58,66)
+
+
 def _take_node_values(out, n, dtype):
+    """The library's result buffer as a numpy array, without a second host copy: the array keeps the
+    malloc()ed block alive and releases it with free() when it is collected."""
     if not out.node_values:
         raise GunrockError("library returned no node_values (see stderr)")
-    arr = np.ctypeslib.as_array(C.cast(out.node_values, C.POINTER(C.c_int32)), shape=(max(n, 1),))[:n]
-    res = arr.view(dtype).copy()
-    _capi.free_host(out.node_values)      # caller frees (shared_lib_tests/test_bfs.c:58,66)
-    return res
+    block = _MallocBlock(out.node_values)
+    buf = (C.c_int32 * max(n, 1)).from_address(out.node_values)
+    buf._block = block                      # numpy holds `buf` as the array's base, `buf` holds the block
+    return np.frombuffer(buf, dtype=np.int32)[:n].view(dtype)
 
 
 def gunrock_bfs_func(row_offsets, col_indices, **cfg):

@@ -399,6 +399,72 @@ class PartitionedSssp:
             pass
 
 
+class PartitionedPagerank:
+    """1D-partitioned PageRank over peer memory (include/gunrock_b200.h, grb_mgpr_*): one instance per
+    rank on that rank's slice of a symmetric graph; every rank calls run() with the same arguments."""
+
+    def __init__(self, graph, group=None):
+        self.graph, self.group = graph, group
+        L = _capi.lib()
+        self._h = C.c_void_p()
+        _capi.check(L.grb_mgpr_create(graph._h, C.byref(self._h)), "grb_mgpr_create")
+        info = graph.info
+        self.parts, self.rank = 1 << info.log_parts, int(info.rank)
+        self.nodes, self.local_nodes = int(info.nodes), int(info.local_nodes)
+        world = dist.get_world_size(group) if dist.is_initialized() else 1
+        if world != self.parts:
+            raise ValueError("graph is partitioned %d ways but the group has %d ranks" % (self.parts, world))
+        if world > 1:
+            nbytes = _capi.IPC_HANDLE_BYTES * _capi.MGPR_PEER_BUFFERS
+            mine = (C.c_ubyte * nbytes)()
+            _capi.check(L.grb_mgpr_peer_export(self._h, mine), "grb_mgpr_peer_export")
+            every = [None] * world
+            dist.all_gather_object(every, bytes(mine), group=group)
+            blob = b"".join(every)
+            buf = (C.c_ubyte * len(blob)).from_buffer_copy(blob)
+            _capi.check(L.grb_mgpr_peer_import(self._h, world, buf), "grb_mgpr_peer_import")
+            dist.barrier(group=group)
+
+    def run(self, src=-1, delta=0.85, threshold=1e-6, max_iter=1000):
+        st = _capi.MgStats()
+        _capi.check(_capi.lib().grb_mgpr_run(self._h, int(src), float(delta), float(threshold), int(max_iter),
+                                             C.byref(st)), "grb_mgpr_run")
+        return dict(elapsed_ms=st.elapsed_ms, sweep_ms=st.edges_visited / 1e3, iterations=st.iterations,
+                    prune_sweeps=st.push_levels, gpu_launches=st.gpu_launches, edges_inspected=st.edges_inspected,
+                    valid_nodes=st.nodes_visited, exchange_bytes=st.exchange_bytes)
+
+    def result(self):
+        """-> fp64 ranks of the owned rows, local-row order"""
+        r = np.empty(max(self.local_nodes, 1), dtype=np.float64)
+        _capi.check(_capi.lib().grb_mgpr_result(self._h, r.ctypes.data_as(C.c_void_p)), "grb_mgpr_result")
+        return r[:self.local_nodes]
+
+    def gather(self):
+        """global fp64 ranks in vertex order on every rank; for tests"""
+        r = self.result()
+        lp = self.parts.bit_length() - 1
+        out = np.empty(self.nodes, dtype=np.float64)
+        if self.parts == 1:
+            out[global_ids(self.local_nodes, lp, 0)] = r
+            return out
+        every = [None] * self.parts
+        dist.all_gather_object(every, r, group=self.group)
+        for k, rr in enumerate(every):
+            out[global_ids(self.local_nodes, lp, k)] = rr
+        return out
+
+    def close(self):
+        if self._h:
+            _capi.lib().grb_mgpr_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
 def gather_labels(engine, group=None):
     """all ranks' labels -> one global int32[n] array in vertex order (on every rank); for tests"""
     world = dist.get_world_size(group) if dist.is_initialized() else 1

@@ -293,6 +293,30 @@ int  grb_mgsssp_run(grb_mgsssp_t ctx, int32_t src, grb_mg_stats *out);     /* ev
 int  grb_mgsssp_result(grb_mgsssp_t ctx, uint32_t *dist_host, int32_t *preds_host);
 void grb_mgsssp_destroy(grb_mgsssp_t ctx);
 
+/* ---- 1D-partitioned PageRank over peer memory -------------------------------------------
+ * Same partition and handle hand-over (3 buffers per device: the two generations of the
+ * replicated contributions rank / degree, the two generations of the replicated "degree
+ * reached zero" map of the pruning phase, the mailbox).  A sweep gathers along the in-edges
+ * of the owned rows from the local replica (no remote atomics); the kernel that finishes the
+ * sweep stores every owned vertex's new contribution into all replicas over NVLink.  Pruning,
+ * damping, base term and the moving test are the reference's (gunrock/app/pr/
+ * pr_functor.cuh:32-175, pr_enactor.cuh:247-329,346-487), in fp64 like grb_pagerank.  The
+ * graph must be symmetric.  grb_mg_stats: iterations = sweeps, push_levels = pruning sweeps,
+ * nodes_visited = vertices that survived the pruning (all devices), edges_inspected = entries
+ * walked on all devices, exchange_bytes = bytes this device stored into peer memory,
+ * edges_visited = microseconds of the power iteration alone. */
+#define GRB_MGPR_PEER_BUFFERS 3
+typedef struct grb_mgpr_s *grb_mgpr_t;
+int  grb_mgpr_create(grb_graph_t g, grb_mgpr_t *out);
+int  grb_mgpr_peer_export(grb_mgpr_t ctx, unsigned char *handles /* [GRB_MGPR_PEER_BUFFERS * 64] */);
+int  grb_mgpr_peer_import(grb_mgpr_t ctx, int world,
+                          const unsigned char *all_handles /* [world][GRB_MGPR_PEER_BUFFERS * 64] */);
+/* every rank, same arguments (src < 0: global PageRank, else personalised) */
+int  grb_mgpr_run(grb_mgpr_t ctx, int32_t src, double delta, double threshold, int32_t max_iter, grb_mg_stats *out);
+/* fp64 ranks of the rows this device owns, local-row order */
+int  grb_mgpr_result(grb_mgpr_t ctx, double *ranks_host);
+void grb_mgpr_destroy(grb_mgpr_t ctx);
+
 #ifdef __cplusplus
 }
 #endif

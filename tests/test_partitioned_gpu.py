@@ -170,3 +170,101 @@ def test_sssp_multi_device_matches_oracle(gr, world):
         p.join(timeout=120)
         assert p.exitcode == 0
     assert all(res), res
+
+
+# ---- partitioned PageRank (grb_mgpr_*): same tolerance and iteration count as tests/test_pr_gpu.py ----
+PR_TOL = 1e-6
+
+
+def _check_pr(ranks, st, want, it):
+    scale = max(1.0, float(np.abs(want).max()))
+    err = float(np.max(np.abs(ranks - want))) if want.size else 0.0
+    return st["iterations"] == it and err <= PR_TOL * scale, (st["iterations"], it, err)
+
+
+@pytest.mark.parametrize("name", ["bips98_606", "chesapeake", "test_cc", "test_pr"])
+def test_pagerank_world1_fixtures(gr, orc, name):
+    from conftest import load_golden
+    from gunrockinst_b200 import partitioned as pt
+    n, ro, co, _ = load_golden(name)
+    g = gr.Graph.from_csr(ro, co, symmetric=True)
+    pr = pt.PartitionedPagerank(g)
+    for kw in (dict(), dict(src=0, threshold=0.01, max_iter=20), dict(max_iter=3), dict(max_iter=0)):
+        want, it = orc.pagerank(ro, co, kw.get("delta", 0.85), kw.get("threshold", 1e-6), kw.get("max_iter", 1000),
+                                kw.get("src", -1))
+        st = pr.run(**kw)
+        ok, why = _check_pr(pr.gather(), st, want, it)
+        assert ok, (kw, why)
+    pr.close()
+
+
+@pytest.mark.parametrize("scale", [10, 16])
+def test_pagerank_world1_rmat(gr, orc, scale):
+    from gunrockinst_b200 import partitioned as pt
+    ro, co = rmat_graph(orc, scale)
+    g = gr.Graph.from_csr(ro, co, symmetric=True)
+    pr = pt.PartitionedPagerank(g)
+    want, it = orc.pagerank(ro, co, 0.85, 1e-6, 1000, -1)
+    for _ in range(2):                                  # a second run on the same context starts clean
+        st = pr.run()
+        ok, why = _check_pr(pr.gather(), st, want, it)
+        assert ok, why
+    assert st["iterations"] > 3 and st["valid_nodes"] == int(np.count_nonzero(np.diff(ro)))
+    single, _, st1 = gr.pagerank(g)                     # the single-device push formulation, same graph
+    assert st1["iterations"] == st["iterations"]
+    assert np.max(np.abs(single - pr.gather())) <= PR_TOL * max(1.0, float(want.max()))
+    pr.close()
+
+
+def test_pagerank_needs_symmetric_graph(gr, orc):
+    from gunrockinst_b200 import partitioned as pt
+    ro, co = rmat_graph(orc, 10, 4, False)
+    g = gr.Graph.from_csr(ro, co, symmetric=False)
+    with pytest.raises(gr.GunrockError):
+        pt.PartitionedPagerank(g)
+
+
+def _pr_worker(rank, world, port, scale, q):
+    sys.path.insert(0, ROOT)
+    import torch
+    import torch.distributed as dist
+    import gunrockinst_b200 as gr
+    from gunrockinst_b200 import partitioned as pt
+    import oracle
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    torch.cuda.set_device(rank)
+    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device("cuda", rank))
+    try:
+        lp = world.bit_length() - 1
+        g = gr.Graph.rmat(scale, 16, device=rank, log_parts=lp, rank=rank)
+        pr = pt.PartitionedPagerank(g)
+        ro, co = oracle.rmat_csr(scale, 16)
+        res = []
+        for kw in (dict(), dict(src=0, threshold=0.01, max_iter=20), dict(max_iter=3), dict()):
+            want, it = oracle.pagerank(ro, co, kw.get("delta", 0.85), kw.get("threshold", 1e-6),
+                                       kw.get("max_iter", 1000), kw.get("src", -1))
+            st = pr.run(**kw)
+            res.append(_check_pr(pr.gather(), st, want, it))
+        if rank == 0:
+            q.put(res)
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("world", [2, 4, 8])
+def test_pagerank_multi_device_matches_oracle(gr, world):
+    if gr.device_count() < world:
+        pytest.skip("needs %d devices" % world)
+    import torch.multiprocessing as mp
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_pr_worker, args=(r, world, port, 15, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    res = q.get(timeout=600)
+    for p in procs:
+        p.join(timeout=120)
+        assert p.exitcode == 0
+    assert all(ok for ok, _ in res), res

@@ -158,3 +158,75 @@ class NumpyEngine:
 
     def synchronize(self):
         pass
+
+
+def partitioned_pagerank(row_offsets, col, log_parts, rank, group=None, src=-1, delta=0.85, threshold=1e-6, max_iter=1000):
+    """numpy restatement of the steps of csrc/gunrock/app/pr/mgpr_enactor.cuh for one rank (the
+    replicas are filled by all_gather where the kernels store into peer memory, the counter blocks by
+    all_reduce): pruning with the replicated "degree just reached zero" map, then gather sweeps over
+    the in-edges of the owned rows from the replicated contributions.  Works on the in- and out-edge
+    lists separately, so it also covers directed graphs (the device code requires a symmetric one).
+    -> (fp64 ranks of the owned rows in local-row order, sweeps, pruning sweeps)"""
+    import torch.distributed as dist
+    import scipy.sparse as sp
+    parts = 1 << log_parts
+    n = row_offsets.size - 1
+    ln = n >> log_parts
+    gids = [global_ids(ln, log_parts, r) for r in range(parts)]
+    pos = np.empty(n, dtype=np.int64)                         # vertex -> owner-major replica position
+    for r in range(parts):
+        pos[gids[r]] = r * ln + np.arange(ln)
+    mine = gids[rank]
+    a = sp.csr_matrix((np.ones(col.size, dtype=np.int8), col, row_offsets), shape=(n, n))
+    at = a.T.tocsr()
+    out_rows = [col[row_offsets[v]:row_offsets[v + 1]] for v in mine]
+    in_rows = [at.indices[at.indptr[v]:at.indptr[v + 1]] for v in mine]
+
+    def publish(segment):                                     # every device's segment -> the whole replica
+        if parts == 1:
+            return segment.copy()
+        t = [torch.empty(ln, dtype=torch.from_numpy(segment).dtype) for _ in range(parts)]
+        dist.all_gather(t, torch.from_numpy(np.ascontiguousarray(segment)), group=group)
+        return np.concatenate([x.numpy() for x in t])
+
+    def total(*vals):
+        t = torch.tensor(vals, dtype=torch.int64)
+        if parts > 1:
+            dist.all_reduce(t, group=group)
+        return [int(x) for x in t]
+
+    deg = np.array([r.size for r in out_rows], dtype=np.int64)
+    rank_v = np.full(ln, 1.0 - delta)
+    zero = publish((deg == 0).astype(np.uint8))
+    qlen, zeros = total(ln, int((deg == 0).sum()))
+    prev, prune_sweeps = 0, 0
+    while prev != qlen:
+        prev = qlen
+        prune_sweeps += 1
+        if zeros == 0:
+            break
+        my_zero = zero[rank * ln:(rank + 1) * ln].astype(bool)
+        for i, row in enumerate(out_rows):                    # advance: one off per out-neighbour that just hit zero
+            deg[i] -= int(zero[pos[row]].sum())
+        deg[my_zero] = -1                                     # rows that were at zero when the sweep began leave
+        alive = deg >= 0
+        new_zero = alive & (deg == 0)
+        zero = publish(new_zero.astype(np.uint8))
+        qlen, zeros = total(int(alive.sum()), int(new_zero.sum()))
+    sweeps = 0
+    if qlen > 0 and max_iter > 0:
+        alive = deg > 0
+        rank_v[~alive] = 0.0
+        contrib = publish(np.where(alive, rank_v / np.maximum(deg, 1), 0.0))
+        base = np.array([1.0 if (src == -1 or src == v) else 0.0 for v in mine])
+        while True:
+            acc = np.array([contrib[pos[row]].sum() if alive[i] else 0.0 for i, row in enumerate(in_rows)])
+            nxt = delta * acc + (1.0 - delta) * base
+            moving = int((np.abs(nxt - rank_v)[alive] > threshold).sum())
+            rank_v[alive] = nxt[alive]
+            contrib = publish(np.where(alive, rank_v / np.maximum(deg, 1), 0.0))
+            sweeps += 1
+            (moving,) = total(moving)
+            if moving == 0 or sweeps >= max_iter:
+                break
+    return rank_v, sweeps, prune_sweeps

@@ -82,3 +82,54 @@ def test_partition_rule_is_a_bijection():
             seen[g] += 1
             assert all(owner_of(int(v), lp) == r for v in g[:64])
         assert np.all(seen == 1)
+
+
+def _pr_worker(rank, world, port, scale, undirected, q):
+    sys.path.insert(0, ROOT)
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import oracle
+    from gunrockinst_b200.partitioned import global_ids
+    from mg_sim import partitioned_pagerank
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        ro, co = oracle.rmat_csr(scale, 4, undirected=undirected)
+        lp = world.bit_length() - 1
+        out = []
+        for kw in (dict(), dict(src=0, threshold=0.01, max_iter=20), dict(max_iter=3)):
+            mine, sweeps, prunes = partitioned_pagerank(ro, co, lp, rank, **kw)
+            every = [None] * world
+            dist.all_gather_object(every, mine)
+            got = np.empty(ro.size - 1)
+            for r, seg in enumerate(every):
+                got[global_ids(seg.size, lp, r)] = seg
+            want, it = oracle.pagerank(ro, co, kw.get("delta", 0.85), kw.get("threshold", 1e-6),
+                                       kw.get("max_iter", 1000), kw.get("src", -1))
+            out.append((sweeps, it, float(np.max(np.abs(got - want))), max(1.0, float(want.max())), prunes))
+        if rank == 0:
+            q.put(out)
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("world", [1, 2, 4])
+@pytest.mark.parametrize("undirected", [True, False])
+def test_partitioned_pagerank_restatement_matches_oracle(world, undirected):
+    """the algorithm of grb_mgpr_* (replicated zero-degree map for the pruning, gather from replicated
+    contributions) against the oracle's restatement of the reference's push formulation"""
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_pr_worker, args=(r, world, port, 9, undirected, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    res = q.get(timeout=240)
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    for sweeps, it, err, scale, prunes in res:
+        assert sweeps == it
+        assert err <= 1e-6 * scale
+    if not undirected:
+        assert res[0][4] > 2                                   # the pruning cascaded over several sweeps

@@ -2,7 +2,7 @@
 # partitioned PageRank on one box: bash tools/gpu_mgpr.sh <tag> <scale> <n...>   (parity tests first)
 tag=${1:-p}; scale=${2:-24}; shift; shift
 out=gpurun_out; mkdir -p $out
-timeout 900 python -m pytest tests/test_partitioned_gpu.py -m gpu -x -q -k pagerank > $out/mgpr_${tag}_pytest.log 2>&1
+timeout 900 python -m pytest tests/test_partitioned_gpu.py -m gpu -x -q -k "${MGPR_TESTS:-pagerank}" > $out/mgpr_${tag}_pytest.log 2>&1
 echo "pytest rc=$?"; tail -3 $out/mgpr_${tag}_pytest.log
 for n in "$@"; do
   f=$out/mgpr_${tag}_n${n}_s$scale

@@ -150,7 +150,7 @@ MgPrInitKernel(const SizeT *row_offsets, long long local_nodes, graph::Partition
 // end of a pruning sweep: rows whose degree was zero when the sweep began leave (degree -1), the
 // others stay with what the advance left them; the next generation of the map marks the rows
 // that have just reached zero.  out_len = rows that stay, aux1 = bits set in the new map.
-__global__ void __launch_bounds__(256)
+static __global__ void __launch_bounds__(256)
 MgPrPruneFinishKernel(long long local_nodes, graph::Partition part, PrPeerTable peers, int gen_in, int *deg,
                       oprtr::LevelCounters *c)
 {
@@ -211,7 +211,7 @@ MgPrStartKernel(long long local_nodes, graph::Partition part, PrPeerTable peers,
 // end of a sweep, per owned alive row: damping and base term, moving test, the new contribution
 // into generation gen_out of every replica, accumulator back to zero
 // (gunrock/app/pr/pr_functor.cuh:73-100)
-__global__ void __launch_bounds__(256)
+static __global__ void __launch_bounds__(256)
 MgPrFinishKernel(long long local_nodes, graph::Partition part, PrPeerTable peers, int gen_out, const int *deg,
                  double *rank, double *acc, double delta, double threshold, int src, oprtr::LevelCounters *c)
 {

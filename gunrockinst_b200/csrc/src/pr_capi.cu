@@ -9,6 +9,7 @@
 #include "graph_handle.cuh"
 #include "source_select.h"
 #include "../gunrock/app/pr/pr_enactor.cuh"
+#include "../gunrock/app/pr/mgpr_enactor.cuh"
 
 // counterpart of run_page_rank<VertexId, Value, SizeT> (pr_app.cu:120-195)
 template <typename SizeT>
@@ -56,16 +57,81 @@ static cudaError_t RunPr(gunrock::graph::DeviceCsr<int, SizeT> *g, cudaStream_t 
     return err;
 }
 
+// Symmetric graphs: the gather formulation of mgpr_enactor.cuh on one device (in-edges == the rows
+// already held, so a sweep sums contributions from a dense vector instead of issuing one fp64 atomic
+// per edge to a random line: 11.4 instead of 16.8 ms per sweep at scale 25).  Same pruning, damping,
+// moving test and sweep count; outputs as RunPr.
+template <typename SizeT>
+static cudaError_t RunPrGather(gunrock::graph::DeviceCsr<int, SizeT> *g, cudaStream_t stream, int src, double delta,
+                               double threshold, int max_iter, double *ranks64_host, int *sorted_ids_host,
+                               float *sorted_ranks_host, size_t top, grb_stats *stats)
+{
+    typedef gunrock::app::pr::MGPREnactor<SizeT> Enactor;
+    Enactor enactor;
+    typename Enactor::RunStats st;
+    GR_TRY(enactor.Setup(g, stream));
+    GR_TRY(enactor.Run(src, delta, threshold, max_iter, &st));
+    const size_t n = (size_t)g->local_nodes;
+    if (ranks64_host) GR_TRY(enactor.Extract(ranks64_host));
+    if (sorted_ids_host || sorted_ranks_host) {
+        // all (id, fp32 rank) pairs in descending rank, ties by ascending id (pr_enactor.cuh:497-500)
+        gunrock::util::DeviceArray<unsigned long long> keys_a, keys_b;
+        gunrock::util::DeviceArray<int> d_ids;
+        gunrock::util::DeviceArray<float> d_ranks;
+        gunrock::util::RadixSortScratch scratch;
+        GR_TRY(keys_a.Allocate(n)); GR_TRY(keys_b.Allocate(n)); GR_TRY(d_ids.Allocate(n)); GR_TRY(d_ranks.Allocate(n));
+        gunrock::app::pr::MakeSortKeysKernel<<<gunrock::util::FillGrid(n), 256, 0, stream>>>(enactor.rank.ptr, n, keys_a.ptr);
+        GR_TRY(cudaGetLastError());
+        unsigned long long *sorted = nullptr;
+        GR_TRY(gunrock::util::RadixSort64(keys_a.ptr, keys_b.ptr, n, 64, scratch, &sorted, stream));
+        gunrock::app::pr::UnpackSortedKernel<<<gunrock::util::FillGrid(n), 256, 0, stream>>>(sorted, n, d_ids.ptr, d_ranks.ptr);
+        GR_TRY(cudaGetLastError());
+        const size_t k = (top && top < n) ? top : n;
+        if (sorted_ids_host)   GR_TRY(cudaMemcpyAsync(sorted_ids_host, d_ids.ptr, sizeof(int) * k, cudaMemcpyDeviceToHost, stream));
+        if (sorted_ranks_host) GR_TRY(cudaMemcpyAsync(sorted_ranks_host, d_ranks.ptr, sizeof(float) * k, cudaMemcpyDeviceToHost, stream));
+        GR_TRY(cudaStreamSynchronize(stream));
+    }
+    if (stats) {
+        memset(stats, 0, sizeof(*stats));
+        stats->elapsed_ms = (float)st.elapsed_ms;
+        stats->iterations = st.iterations;
+        stats->edges_inspected = st.edges;
+        stats->edges_visited = (int64_t)st.edges;
+        stats->total_queued = st.valid_nodes * (unsigned long long)st.iterations;
+        stats->nodes_visited = (int64_t)st.valid_nodes;
+        // per walked entry 4 (column) + 8 (contribution); per alive vertex and sweep: queue 4, offsets,
+        // accumulator 8 + 8, rank 8 + 8, degree 4, contribution 8
+        stats->algo_bytes = 12ull * st.edges + (unsigned long long)st.iterations * st.valid_nodes * (48ull + 2ull * sizeof(SizeT));
+        stats->push_levels = (int32_t)st.iterations;
+        stats->pull_levels = (int32_t)st.prune_sweeps;
+        stats->gpu_launches = st.launches;
+        stats->reserved = (int32_t)(st.sweep_ms * 1000.0);         // microseconds of the power iteration alone
+    }
+    return cudaSuccess;
+}
+
+template <typename SizeT>
+static cudaError_t RunPrAny(gunrock::graph::DeviceCsr<int, SizeT> *g, cudaStream_t stream, int src, double delta,
+                            double threshold, int max_iter, double *ranks64_host, int *sorted_ids_host,
+                            float *sorted_ranks_host, size_t top, grb_stats *stats)
+{
+    if (g->symmetric && g->part.log_parts == 0 && g->local_nodes > 0 && g->edges > 0)
+        return RunPrGather<SizeT>(g, stream, src, delta, threshold, max_iter, ranks64_host, sorted_ids_host,
+                                  sorted_ranks_host, top, stats);
+    return RunPr<SizeT>(g, stream, src, delta, threshold, max_iter, ranks64_host, sorted_ids_host,
+                        sorted_ranks_host, top, stats);
+}
+
 static int PrDispatch(grb_graph_t g, int32_t src, double delta, double threshold, int32_t max_iter,
                       double *ranks64_host, int32_t *sorted_ids_host, float *sorted_ranks_host, size_t top,
                       grb_stats *stats)
 {
     if (!g) return (int)cudaErrorInvalidValue;
     GRB_TRY(cudaSetDevice(g->device()));
-    return (int)(g->g32 ? RunPr<int>(g->g32, g->stream, src, delta, threshold, max_iter, ranks64_host,
-                                     sorted_ids_host, sorted_ranks_host, top, stats)
-                        : RunPr<long long>(g->g64, g->stream, src, delta, threshold, max_iter, ranks64_host,
-                                           sorted_ids_host, sorted_ranks_host, top, stats));
+    return (int)(g->g32 ? RunPrAny<int>(g->g32, g->stream, src, delta, threshold, max_iter, ranks64_host,
+                                        sorted_ids_host, sorted_ranks_host, top, stats)
+                        : RunPrAny<long long>(g->g64, g->stream, src, delta, threshold, max_iter, ranks64_host,
+                                              sorted_ids_host, sorted_ranks_host, top, stats));
 }
 
 extern "C" int grb_pagerank(grb_graph_t g, int32_t src, double delta, double threshold, int32_t max_iter,

@@ -44,17 +44,24 @@ class Graph:
     # -- constructors ----------------------------------------------------------------
     @classmethod
     def from_csr(cls, row_offsets, col_indices, weights=None, symmetric=False, device=0,
-                 force_offset_bytes=0):
+                 force_offset_bytes=0, stream_from_host=False):
+        """stream_from_host: upload the offsets only; column ids and weights stay in (page-locked,
+        mapped) host memory and are read over PCIe by the kernels (problem_base.cuh:252-276).  The
+        graph object keeps the host arrays alive."""
         ro = np.ascontiguousarray(row_offsets)
         if ro.dtype not in (np.int32, np.int64):
             ro = ro.astype(np.int64)
         co = np.ascontiguousarray(col_indices, dtype=np.int32)
         w = np.ascontiguousarray(weights, dtype=np.uint32) if weights is not None else None
         h = C.c_void_p()
-        _capi.check(_capi.lib().grb_graph_from_host(
+        fn = "grb_graph_from_host_mapped" if stream_from_host else "grb_graph_from_host"
+        _capi.check(getattr(_capi.lib(), fn)(
             device, ro.size - 1, co.size, _ptr(ro), ro.dtype.itemsize, _ptr(co), _ptr(w),
-            int(bool(symmetric)), force_offset_bytes, C.byref(h)), "grb_graph_from_host")
-        return cls(h)
+            int(bool(symmetric)), force_offset_bytes, C.byref(h)), fn)
+        g = cls(h)
+        if stream_from_host:
+            g._host_arrays = (co, w)
+        return g
 
     @classmethod
     def rmat(cls, scale, edgefactor=16, seed=None, undirected=True, abcd=RMAT_ABCD, device=0,

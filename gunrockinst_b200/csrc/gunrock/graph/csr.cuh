@@ -103,17 +103,41 @@ struct DeviceCsr {
     }
     bool HasInverse() const { return symmetric || csc_offsets.size != 0; }
 
-    // upload a whole (unpartitioned) host CSR
+    // upload a whole (unpartitioned) host CSR.  stream_from_host: only the offsets are uploaded, the
+    // column ids (and weights) stay in the caller's memory, page-locked and mapped, and the kernels
+    // read them over PCIe as they go -- the reference's stream_from_host (gunrock/app/
+    // problem_base.cuh:252-276: cudaHostAlloc mapped + cudaHostGetDevicePointer) for graphs that do
+    // not fit the device or are searched once.  The caller keeps the arrays alive and unchanged.
     template <typename HostSizeT>
     cudaError_t FromHost(long long n, long long m, const HostSizeT *h_offsets,
-                         const VertexId *h_cols, const unsigned *h_weights, cudaStream_t s);
+                         const VertexId *h_cols, const unsigned *h_weights, cudaStream_t s,
+                         bool stream_from_host = false);
+    bool  streams_from_host = false;
+    void *registered_[2] = {nullptr, nullptr};      // host ranges this object page-locked
+    DeviceCsr() = default;
+    DeviceCsr(const DeviceCsr &) = delete;
+    DeviceCsr &operator=(const DeviceCsr &) = delete;
+    ~DeviceCsr()
+    {
+        col_indices.Release(); edge_values.Release();
+        for (void *r : registered_) if (r) cudaHostUnregister(r);
+    }
+    // device-visible alias of a host buffer; page-locks it when the caller has not
+    cudaError_t MapHost(const void *h, size_t bytes, void **dev, int slot)
+    {
+        if (cudaHostGetDevicePointer(dev, const_cast<void *>(h), 0) == cudaSuccess) return cudaSuccess;
+        (void)cudaGetLastError();                   // not page-locked yet
+        GR_TRY(cudaHostRegister(const_cast<void *>(h), bytes, cudaHostRegisterMapped));
+        registered_[slot] = const_cast<void *>(h);
+        return cudaHostGetDevicePointer(dev, const_cast<void *>(h), 0);
+    }
 };
 
 template <typename VertexId, typename SizeT>
 template <typename HostSizeT>
 cudaError_t DeviceCsr<VertexId, SizeT>::FromHost(long long n, long long m, const HostSizeT *h_offsets,
                                                  const VertexId *h_cols, const unsigned *h_weights,
-                                                 cudaStream_t s)
+                                                 cudaStream_t s, bool stream_from_host)
 {
     nodes = local_nodes = n; edges = m; part = Partition();
     if (sizeof(HostSizeT) == sizeof(SizeT)) {
@@ -126,6 +150,17 @@ cudaError_t DeviceCsr<VertexId, SizeT>::FromHost(long long n, long long m, const
         if (e == cudaSuccess) e = cudaStreamSynchronize(s);
         free(tmp);
         GR_TRY(e);
+    }
+    streams_from_host = stream_from_host && m > 0;
+    if (streams_from_host) {
+        void *d = nullptr;
+        GR_TRY(MapHost(h_cols, sizeof(VertexId) * (size_t)m, &d, 0));
+        col_indices.Borrow((VertexId *)d, (size_t)m);
+        if (h_weights) {
+            GR_TRY(MapHost(h_weights, sizeof(unsigned) * (size_t)m, &d, 1));
+            edge_values.Borrow((unsigned *)d, (size_t)m);
+        } else edge_values.size = 0;
+        return cudaSuccess;
     }
     GR_TRY(col_indices.FromHost(h_cols, (size_t)m, s));
     if (h_weights) GR_TRY(edge_values.FromHost(h_weights, (size_t)m, s));

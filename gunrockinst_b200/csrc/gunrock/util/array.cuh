@@ -143,6 +143,7 @@ struct DeviceArray {
     cudaError_t Allocate(size_t n)
     {
         if (n > cap) {
+            if (borrowed_) return cudaErrorInvalidValue;
             Release();
             // kPad bytes beyond the last element stay readable: kernels fetch aligned 16-byte groups
             size_t bytes = (n ? n : 1) * sizeof(T) + kPad, got = 0;
@@ -156,9 +157,16 @@ struct DeviceArray {
     }
     void Release()
     {
-        if (ptr) BlockCache::Device().Give(ptr, block_, device_);
-        ptr = nullptr; size = cap = 0; block_ = 0;
+        if (ptr && !borrowed_) BlockCache::Device().Give(ptr, block_, device_);
+        ptr = nullptr; size = cap = 0; block_ = 0; borrowed_ = false;
     }
+    // point at n elements somebody else owns (a mapped host buffer): never freed, never grown
+    void Borrow(T *device_visible, size_t n)
+    {
+        Release();
+        ptr = device_visible; size = cap = n; borrowed_ = true;
+    }
+    bool borrowed_ = false;
     cudaError_t Zero(cudaStream_t s) { return size ? cudaMemsetAsync(ptr, 0, size * sizeof(T), s) : cudaSuccess; }
     cudaError_t FromHost(const T *h, size_t n, cudaStream_t s)
     {
@@ -168,7 +176,8 @@ struct DeviceArray {
     }
     cudaError_t ToHost(T *h, size_t n, cudaStream_t s) const
     {
-        if (n) GR_TRY(cudaMemcpyAsync(h, ptr, n * sizeof(T), cudaMemcpyDeviceToHost, s));
+        // (cudaMemcpyDefault: a borrowed array may alias mapped host memory)
+        if (n) GR_TRY(cudaMemcpyAsync(h, ptr, n * sizeof(T), borrowed_ ? cudaMemcpyDefault : cudaMemcpyDeviceToHost, s));
         return cudaSuccess;
     }
 };

@@ -20,10 +20,10 @@ extern "C" int grb_device_count(void)
     return count;
 }
 
-extern "C" int grb_graph_from_host(int device, int64_t nodes, int64_t edges,
-                                   const void *row_offsets, int offset_bytes_in,
-                                   const int32_t *col_indices, const uint32_t *weights,
-                                   int symmetric, int force_offset_bytes, grb_graph_t *out)
+static int GraphFromHost(int device, int64_t nodes, int64_t edges,
+                         const void *row_offsets, int offset_bytes_in,
+                         const int32_t *col_indices, const uint32_t *weights,
+                         int symmetric, int force_offset_bytes, bool mapped, grb_graph_t *out)
 {
     if (!out || !row_offsets || (edges > 0 && !col_indices) || (offset_bytes_in != 4 && offset_bytes_in != 8))
         return (int)cudaErrorInvalidValue;
@@ -40,19 +40,38 @@ extern "C" int grb_graph_from_host(int device, int64_t nodes, int64_t edges,
         if (ob == 4) {
             h->g32 = new Csr32(); h->g32->device = device; h->g32->symmetric = symmetric != 0;
             e = (offset_bytes_in == 4)
-                ? h->g32->FromHost(nodes, edges, (const int *)row_offsets, col_indices, weights, h->stream)
-                : h->g32->FromHost(nodes, edges, (const long long *)row_offsets, col_indices, weights, h->stream);
+                ? h->g32->FromHost(nodes, edges, (const int *)row_offsets, col_indices, weights, h->stream, mapped)
+                : h->g32->FromHost(nodes, edges, (const long long *)row_offsets, col_indices, weights, h->stream, mapped);
         } else {
             h->g64 = new Csr64(); h->g64->device = device; h->g64->symmetric = symmetric != 0;
             e = (offset_bytes_in == 4)
-                ? h->g64->FromHost(nodes, edges, (const int *)row_offsets, col_indices, weights, h->stream)
-                : h->g64->FromHost(nodes, edges, (const long long *)row_offsets, col_indices, weights, h->stream);
+                ? h->g64->FromHost(nodes, edges, (const int *)row_offsets, col_indices, weights, h->stream, mapped)
+                : h->g64->FromHost(nodes, edges, (const long long *)row_offsets, col_indices, weights, h->stream, mapped);
         }
     }
     if (e == cudaSuccess) e = cudaStreamSynchronize(h->stream);
     if (e != cudaSuccess) { gunrock::util::GRError(e, "grb_graph_from_host", __FILE__, __LINE__); delete h; return (int)e; }
     *out = h;
     return 0;
+}
+
+extern "C" int grb_graph_from_host(int device, int64_t nodes, int64_t edges,
+                                   const void *row_offsets, int offset_bytes_in,
+                                   const int32_t *col_indices, const uint32_t *weights,
+                                   int symmetric, int force_offset_bytes, grb_graph_t *out)
+{
+    return GraphFromHost(device, nodes, edges, row_offsets, offset_bytes_in, col_indices, weights, symmetric,
+                         force_offset_bytes, false, out);
+}
+
+// the reference's stream_from_host (gunrock/app/problem_base.cuh:252-276)
+extern "C" int grb_graph_from_host_mapped(int device, int64_t nodes, int64_t edges,
+                                          const void *row_offsets, int offset_bytes_in,
+                                          const int32_t *col_indices, const uint32_t *weights,
+                                          int symmetric, int force_offset_bytes, grb_graph_t *out)
+{
+    return GraphFromHost(device, nodes, edges, row_offsets, offset_bytes_in, col_indices, weights, symmetric,
+                         force_offset_bytes, true, out);
 }
 
 extern "C" int grb_graph_get_info(grb_graph_t g, grb_graph_info *info)

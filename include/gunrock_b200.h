@@ -59,6 +59,16 @@ int grb_graph_from_host(int device, int64_t nodes, int64_t edges,
                         const int32_t *col_indices, const uint32_t *weights,
                         int symmetric, int force_offset_bytes, grb_graph_t *out);
 
+/* same, but only the offsets are uploaded: col_indices (and weights) stay in the caller's memory,
+ * page-locked and mapped into the device's address space, and the kernels read them over PCIe as
+ * they go -- the reference's stream_from_host (gunrock/app/problem_base.cuh:252-276) for graphs
+ * larger than device memory or searched once.  The arrays must stay alive and unchanged until
+ * grb_graph_destroy; memory the caller has already page-locked is used as it is. */
+int grb_graph_from_host_mapped(int device, int64_t nodes, int64_t edges,
+                               const void *row_offsets, int offset_bytes_in,
+                               const int32_t *col_indices, const uint32_t *weights,
+                               int symmetric, int force_offset_bytes, grb_graph_t *out);
+
 /* seeded R-MAT (a,b,c,d + per-level 5% noise exactly as graphio/utils.cuh:84-130),
  * nodes = 2^scale, `edges` generated tuples, undirected => reverse tuples added,
  * then the reference canonicalisation (sort by (row,col), drop duplicates and

@@ -82,3 +82,37 @@ def test_device_rmat_scale20_statistics(gr):
     assert np.array_equal(rkey, key)
     assert 0.9 * 32 * n < g.edges < 32 * n
     g.close()
+
+
+@pytest.mark.parametrize("pinned", [False, True])
+def test_stream_from_host_matches_resident_graph(gr, orc, pinned):
+    """grb_graph_from_host_mapped (the reference's stream_from_host, problem_base.cuh:252-276): column ids
+    and weights stay in host memory; every primitive must return what it returns on the uploaded copy."""
+    ro, co = rmat_graph(orc, 14)
+    w = orc.edge_weights(ro, co, 5)
+    if pinned:                                          # memory the caller page-locked itself
+        import torch
+        co = torch.from_numpy(co).pin_memory().numpy()
+        w = torch.from_numpy(w).pin_memory().numpy()
+    g = gr.Graph.from_csr(ro, co, weights=w, symmetric=True, stream_from_host=True)
+    assert (g.nodes, g.edges, g.info.has_weights) == (ro.size - 1, co.size, 1)
+    ro2, co2, w2 = g.download(want_weights=True)
+    assert np.array_equal(ro2, ro) and np.array_equal(co2, co) and np.array_equal(w2, w)
+    for mode in (dict(), dict(direction_optimized=True), dict(idempotence=True), dict(mark_pred=True)):
+        b = gr.Bfs(g, **mode)
+        for src in (0, 77):
+            labels, _, st = b.run(src)
+            want = orc.bfs(ro, co, src)
+            assert np.array_equal(labels, want), mode
+            assert st["edges_visited"] == orc.edges_visited(ro, want)
+        b.close()
+    dist, _, _ = gr.sssp(g, 0)
+    want, _ = orc.sssp(ro, co, w, 0)
+    assert np.array_equal(dist, want)
+    labels, ncomp, _ = gr.cc(g)
+    want_l, want_n = orc.cc(ro, co)
+    assert np.array_equal(labels, want_l) and ncomp == want_n
+    ranks, _, st = gr.pagerank(g)
+    want_r, it = orc.pagerank(ro, co, 0.85, 1e-6, 1000, -1)
+    assert st["iterations"] == it and np.max(np.abs(ranks - want_r)) <= 1e-6 * max(1.0, float(want_r.max()))
+    g.close()

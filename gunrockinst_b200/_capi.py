@@ -78,7 +78,7 @@ class MgTrace(C.Structure):
                 ("candidates", C.c_uint64), ("compute_ms", C.c_float), ("exchange_ms", C.c_float)]
 
 
-IPC_HANDLE_BYTES, MG_PEER_BUFFERS, MGSSSP_PEER_BUFFERS, MGPR_PEER_BUFFERS = 64, 4, 3, 3
+IPC_HANDLE_BYTES, MG_PEER_BUFFERS, MGSSSP_PEER_BUFFERS, MGPR_PEER_BUFFERS, MGCC_PEER_BUFFERS = 64, 4, 3, 3, 3
 
 
 # gunrock.h (reference ABI, gunrock/gunrock.h:51-99)
@@ -185,6 +185,12 @@ def lib():
     sig("grb_mgpr_run", C.c_int, [p, i32, dbl, dbl, i32, C.POINTER(MgStats)])
     sig("grb_mgpr_result", C.c_int, [p, p])
     sig("grb_mgpr_destroy", None, [p])
+    sig("grb_mgcc_create", C.c_int, [p, pp])
+    sig("grb_mgcc_peer_export", C.c_int, [p, p])
+    sig("grb_mgcc_peer_import", C.c_int, [p, C.c_int, p])
+    sig("grb_mgcc_run", C.c_int, [p, C.POINTER(MgStats)])
+    sig("grb_mgcc_result", C.c_int, [p, p, C.POINTER(i64)])
+    sig("grb_mgcc_destroy", None, [p])
     for name in ("gunrock_bfs_func", "gunrock_cc_func", "gunrock_bc_func"):
         sig(name, None, [C.POINTER(GunrockGraph), C.POINTER(GunrockGraph), GunrockConfig, GunrockDataType])
     sig("gunrock_topk_func", None, [C.POINTER(GunrockGraph), p, p, p, C.POINTER(GunrockGraph),

@@ -465,6 +465,74 @@ class PartitionedPagerank:
             pass
 
 
+class PartitionedCc:
+    """1D-partitioned connected components over peer memory (include/gunrock_b200.h, grb_mgcc_*): one
+    instance per rank on that rank's slice of a symmetric graph; every rank calls run()."""
+
+    def __init__(self, graph, group=None):
+        self.graph, self.group = graph, group
+        L = _capi.lib()
+        self._h = C.c_void_p()
+        _capi.check(L.grb_mgcc_create(graph._h, C.byref(self._h)), "grb_mgcc_create")
+        info = graph.info
+        self.parts, self.rank = 1 << info.log_parts, int(info.rank)
+        self.nodes, self.local_nodes = int(info.nodes), int(info.local_nodes)
+        world = dist.get_world_size(group) if dist.is_initialized() else 1
+        if world != self.parts:
+            raise ValueError("graph is partitioned %d ways but the group has %d ranks" % (self.parts, world))
+        if world > 1:
+            nbytes = _capi.IPC_HANDLE_BYTES * _capi.MGCC_PEER_BUFFERS
+            mine = (C.c_ubyte * nbytes)()
+            _capi.check(L.grb_mgcc_peer_export(self._h, mine), "grb_mgcc_peer_export")
+            every = [None] * world
+            dist.all_gather_object(every, bytes(mine), group=group)
+            blob = b"".join(every)
+            buf = (C.c_ubyte * len(blob)).from_buffer_copy(blob)
+            _capi.check(L.grb_mgcc_peer_import(self._h, world, buf), "grb_mgcc_peer_import")
+            dist.barrier(group=group)
+
+    def run(self):
+        st = _capi.MgStats()
+        _capi.check(_capi.lib().grb_mgcc_run(self._h, C.byref(st)), "grb_mgcc_run")
+        return dict(elapsed_ms=st.elapsed_ms, iterations=st.iterations, gpu_launches=st.gpu_launches,
+                    offers=st.edges_inspected, queued=st.nodes_visited)
+
+    def result(self):
+        """-> (labels int32[local_nodes] of the owned rows, number of owned component roots)"""
+        lab = np.empty(max(self.local_nodes, 1), dtype=np.int32)
+        roots = C.c_int64()
+        _capi.check(_capi.lib().grb_mgcc_result(self._h, lab.ctypes.data_as(C.c_void_p), C.byref(roots)),
+                    "grb_mgcc_result")
+        return lab[:self.local_nodes], int(roots.value)
+
+    def gather(self):
+        """-> (global labels in vertex order, component count) on every rank; for tests"""
+        lab, roots = self.result()
+        lp = self.parts.bit_length() - 1
+        out = np.empty(self.nodes, dtype=np.int32)
+        if self.parts == 1:
+            out[global_ids(self.local_nodes, lp, 0)] = lab
+            return out, roots
+        every = [None] * self.parts
+        dist.all_gather_object(every, (lab, roots), group=self.group)
+        total = 0
+        for r, (ll, rr) in enumerate(every):
+            out[global_ids(self.local_nodes, lp, r)] = ll
+            total += rr
+        return out, total
+
+    def close(self):
+        if self._h:
+            _capi.lib().grb_mgcc_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
 def gather_labels(engine, group=None):
     """all ranks' labels -> one global int32[n] array in vertex order (on every rank); for tests"""
     world = dist.get_world_size(group) if dist.is_initialized() else 1

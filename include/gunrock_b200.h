@@ -327,6 +327,27 @@ int  grb_mgpr_run(grb_mgpr_t ctx, int32_t src, double delta, double threshold, i
 int  grb_mgpr_result(grb_mgpr_t ctx, double *ranks_host);
 void grb_mgpr_destroy(grb_mgpr_t ctx);
 
+/* ---- 1D-partitioned connected components over peer memory ------------------------------
+ * Same partition, handle hand-over and buffers as the partitioned SSSP.  Minimum-label
+ * propagation: every vertex starts with its own id in the frontier, a smaller label travels along
+ * an edge as a 64-bit atomicMin into the owner's memory (over NVLink when remote), the owner
+ * re-queues rows whose label dropped; ends when no device holds an unsent improvement.  Labels as
+ * grb_cc / gunrock_cc_func: the smallest vertex id of the component (gunrock/app/cc/
+ * cc_problem.cuh:164-170 after canonicalisation).  The graph must be symmetric.  grb_mg_stats:
+ * iterations, gpu_launches, edges_inspected = label offers examined on all devices,
+ * nodes_visited = vertices queued over all iterations. */
+#define GRB_MGCC_PEER_BUFFERS 3
+typedef struct grb_mgcc_s *grb_mgcc_t;
+int  grb_mgcc_create(grb_graph_t g, grb_mgcc_t *out);
+int  grb_mgcc_peer_export(grb_mgcc_t ctx, unsigned char *handles /* [GRB_MGCC_PEER_BUFFERS * 64] */);
+int  grb_mgcc_peer_import(grb_mgcc_t ctx, int world,
+                          const unsigned char *all_handles /* [world][GRB_MGCC_PEER_BUFFERS * 64] */);
+int  grb_mgcc_run(grb_mgcc_t ctx, grb_mg_stats *out);                      /* every rank */
+/* labels of the rows this device owns, local-row order (may be NULL); *local_roots = owned vertices
+ * that are the label of their component (their sum over the devices is the component count) */
+int  grb_mgcc_result(grb_mgcc_t ctx, int32_t *labels_host, int64_t *local_roots);
+void grb_mgcc_destroy(grb_mgcc_t ctx);
+
 #ifdef __cplusplus
 }
 #endif

@@ -230,3 +230,54 @@ def partitioned_pagerank(row_offsets, col, log_parts, rank, group=None, src=-1, 
             if moving == 0 or sweeps >= max_iter:
                 break
     return rank_v, sweeps, prune_sweeps
+
+
+def partitioned_cc(row_offsets, col, log_parts, rank, group=None):
+    """numpy restatement of csrc/gunrock/app/cc/mgcc_enactor.cuh for one rank: minimum-label
+    propagation along the out-edges of the owned rows, offers to remote owners delivered by an
+    all_gather of (vertex, label) pairs where the kernels issue atomicMin into peer memory.
+    -> (labels of the owned rows in local-row order, iterations)"""
+    import torch.distributed as dist
+    parts = 1 << log_parts
+    n = row_offsets.size - 1
+    ln = n >> log_parts
+    mine = global_ids(ln, log_parts, rank)
+    local_of = {int(v): i for i, v in enumerate(mine)}
+    label = mine.copy()
+    queued = label.copy()
+    best = np.arange(n, dtype=np.int64)                 # best label sent per global vertex
+    frontier = list(range(ln))
+    iterations = 0
+    while True:
+        offers = {}
+        for i in frontier:
+            v = int(mine[i])
+            lab = int(label[i])
+            for d in col[row_offsets[v]:row_offsets[v + 1]]:
+                d = int(d)
+                if lab < best[d]:
+                    best[d] = lab
+                    offers[d] = min(lab, offers.get(d, lab))
+        if parts > 1:
+            every = [None] * parts
+            dist.all_gather_object(every, offers, group=group)
+        else:
+            every = [offers]
+        touched = set()
+        for off in every:
+            for d, lab in off.items():
+                if d in local_of and lab < label[local_of[d]]:
+                    label[local_of[d]] = lab
+                    touched.add(local_of[d])
+        frontier = []
+        for i in sorted(touched):
+            if label[i] < queued[i]:
+                queued[i] = label[i]
+                frontier.append(i)
+        total = torch.tensor([len(frontier)], dtype=torch.int64)
+        if parts > 1:
+            dist.all_reduce(total, group=group)
+        iterations += 1
+        if int(total) == 0:
+            break
+    return label.astype(np.int32), iterations

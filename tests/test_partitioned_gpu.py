@@ -268,3 +268,84 @@ def test_pagerank_multi_device_matches_oracle(gr, world):
         p.join(timeout=120)
         assert p.exitcode == 0
     assert all(ok for ok, _ in res), res
+
+
+# ---- partitioned connected components (grb_mgcc_*): labels must be the oracle's min-vertex labels ----
+@pytest.mark.parametrize("name", ["bips98_606", "chesapeake", "test_cc", "test_pr"])
+def test_cc_world1_fixtures(gr, orc, name):
+    from conftest import load_golden
+    from gunrockinst_b200 import partitioned as pt
+    n, ro, co, _ = load_golden(name)
+    g = gr.Graph.from_csr(ro, co, symmetric=True)
+    cc = pt.PartitionedCc(g)
+    want, count = orc.cc(ro, co)
+    for _ in range(2):                                  # a second run on the same context starts clean
+        st = cc.run()
+        labels, roots = cc.gather()
+        assert np.array_equal(labels, want) and roots == count
+        assert st["iterations"] >= 1
+    cc.close()
+
+
+@pytest.mark.parametrize("scale", [10, 16])
+def test_cc_world1_rmat(gr, orc, scale):
+    from gunrockinst_b200 import partitioned as pt
+    ro, co = rmat_graph(orc, scale)
+    g = gr.Graph.from_csr(ro, co, symmetric=True)
+    cc = pt.PartitionedCc(g)
+    cc.run()
+    labels, roots = cc.gather()
+    want, count = orc.cc(ro, co)
+    assert np.array_equal(labels, want) and roots == count
+    single, ncomp, _ = gr.cc(g)                         # the single-device hook / pointer-jump enactor
+    assert np.array_equal(single, labels) and ncomp == roots
+    cc.close()
+
+
+def _cc_worker(rank, world, port, scale, q):
+    sys.path.insert(0, ROOT)
+    import torch
+    import torch.distributed as dist
+    import gunrockinst_b200 as gr
+    from gunrockinst_b200 import partitioned as pt
+    import oracle
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    torch.cuda.set_device(rank)
+    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device("cuda", rank))
+    try:
+        lp = world.bit_length() - 1
+        res = []
+        for ef in (16, 2):                              # one giant component + dust; many small components
+            g = gr.Graph.rmat(scale, ef, device=rank, log_parts=lp, rank=rank)
+            cc = pt.PartitionedCc(g)
+            ro, co = oracle.rmat_csr(scale, ef)
+            want, count = oracle.cc(ro, co)
+            for _ in range(2):
+                st = cc.run()
+                labels, roots = cc.gather()
+                res.append((bool(np.array_equal(labels, want)), roots == count, st["iterations"], st["elapsed_ms"]))
+            cc.close()
+            g.close()
+        if rank == 0:
+            q.put(res)
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("world", [2, 4, 8])
+def test_cc_multi_device_matches_oracle(gr, world):
+    if gr.device_count() < world:
+        pytest.skip("needs %d devices" % world)
+    import torch.multiprocessing as mp
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_cc_worker, args=(r, world, port, 15, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    res = q.get(timeout=600)
+    for p in procs:
+        p.join(timeout=120)
+        assert p.exitcode == 0
+    assert all(a and b for a, b, _, _ in res), res

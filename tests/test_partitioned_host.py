@@ -133,3 +133,46 @@ def test_partitioned_pagerank_restatement_matches_oracle(world, undirected):
         assert err <= 1e-6 * scale
     if not undirected:
         assert res[0][4] > 2                                   # the pruning cascaded over several sweeps
+
+
+def _cc_worker(rank, world, port, scale, ef, q):
+    sys.path.insert(0, ROOT)
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import oracle
+    from gunrockinst_b200.partitioned import global_ids
+    from mg_sim import partitioned_cc
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        ro, co = oracle.rmat_csr(scale, ef)
+        lp = world.bit_length() - 1
+        mine, iterations = partitioned_cc(ro, co, lp, rank)
+        every = [None] * world
+        dist.all_gather_object(every, mine)
+        got = np.empty(ro.size - 1, dtype=np.int32)
+        for r, seg in enumerate(every):
+            got[global_ids(seg.size, lp, r)] = seg
+        want, count = oracle.cc(ro, co)
+        if rank == 0:
+            q.put((bool(np.array_equal(got, want)), int((got == np.arange(got.size)).sum()) == count, iterations))
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("world", [1, 2, 4])
+@pytest.mark.parametrize("ef", [8, 1])
+def test_partitioned_cc_restatement_matches_oracle(world, ef):
+    """the algorithm of grb_mgcc_* (minimum-label propagation with a best-sent replica and owner-side
+    re-queueing) against the oracle's union-find labels"""
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_cc_worker, args=(r, world, port, 9, ef, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    same, count_ok, iterations = q.get(timeout=240)
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    assert same and count_ok and iterations >= 2

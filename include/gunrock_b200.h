@@ -63,7 +63,10 @@ int grb_graph_from_host(int device, int64_t nodes, int64_t edges,
  * page-locked and mapped into the device's address space, and the kernels read them over PCIe as
  * they go -- the reference's stream_from_host (gunrock/app/problem_base.cuh:252-276) for graphs
  * larger than device memory or searched once.  The arrays must stay alive and unchanged until
- * grb_graph_destroy; memory the caller has already page-locked is used as it is. */
+ * grb_graph_destroy.  Memory the caller has already page-locked (cudaHostAlloc / cudaHostRegister)
+ * is used as it is; pageable memory is page-locked by this call (for a large array that costs as
+ * much as an upload) and released again by grb_graph_destroy of THIS handle -- do not share such
+ * arrays between two mapped handles with different lifetimes. */
 int grb_graph_from_host_mapped(int device, int64_t nodes, int64_t edges,
                                const void *row_offsets, int offset_bytes_in,
                                const int32_t *col_indices, const uint32_t *weights,

@@ -69,3 +69,37 @@ def test_product_package_does_not_import_the_oracle():
             if f.endswith((".py", ".cu", ".cuh", ".h")):
                 text = open(os.path.join(dirpath, f)).read()
                 assert "import oracle" not in text and "from oracle" not in text and "liboracle" not in text, f
+
+
+def test_malloced_result_is_handed_over_without_a_copy():
+    """gunrock.h ownership rule (shared_lib_tests/test_bfs.c:58,66): node_values is malloc()ed by the
+    library and freed by the caller.  The Python mirror wraps the block instead of copying it and must
+    free() it exactly once, when the last view of the array is gone."""
+    import gc
+    import numpy as np
+    import gunrockinst_b200 as g
+    libc = C.CDLL(None)
+    libc.malloc.restype = C.c_void_p
+    libc.malloc.argtypes = [C.c_size_t]
+    freed = []
+    real_free = g._capi.free_host
+    g._capi.free_host = lambda p: (freed.append(p), real_free(p))
+    try:
+        class Out:
+            node_values = libc.malloc(4 * 10)
+        C.memmove(Out.node_values, (C.c_int32 * 10)(*range(10)), 40)
+        arr = g._take_node_values(Out, 10, np.uint32)
+        assert arr.dtype == np.uint32 and arr.tolist() == list(range(10)) and arr.flags.writeable
+        assert arr.ctypes.data == Out.node_values               # the library's block itself
+        view = arr[2:5]
+        del arr
+        gc.collect()
+        assert freed == [] and view.tolist() == [2, 3, 4]        # a view keeps the block alive
+        del view
+        gc.collect()
+        assert freed == [Out.node_values]
+        Out.node_values = None
+        with pytest.raises(g.GunrockError):
+            g._take_node_values(Out, 10, np.int32)
+    finally:
+        g._capi.free_host = real_free

@@ -100,6 +100,16 @@ class Graph:
             return ro, co[:self.edges], (w[:self.edges] if w is not None else None)
         return ro, co[:self.edges]
 
+    def build_transpose(self):
+        """attach the transpose (CSC) of a directed graph: the inverse graph of a direction-optimising BFS"""
+        _capi.check(_capi.lib().grb_graph_build_transpose(self._h), "grb_graph_build_transpose")
+
+    def check_symmetric(self):
+        """True iff the resident CSR equals its transpose (what `symmetric=True` promises)"""
+        out = C.c_int(0)
+        _capi.check(_capi.lib().grb_graph_check_symmetric(self._h, C.byref(out)), "grb_graph_check_symmetric")
+        return bool(out.value)
+
     def device_ptrs(self):
         a, b, c = C.c_void_p(), C.c_void_p(), C.c_void_p()
         _capi.check(_capi.lib().grb_graph_device_ptrs(self._h, C.byref(a), C.byref(b), C.byref(c)),
@@ -133,10 +143,11 @@ class Bfs:
 
     def __init__(self, graph, mark_pred=False, idempotence=False, traversal_mode=0,
                  direction_optimized=False, alpha=0.0, beta=0.0, queue_sizing=0.0, record_levels=False,
-                 host_loop=False):
+                 host_loop=False, degree_order=False, stream_min_edges=0):
         self.graph = graph
         cfg = BfsConfig(int(mark_pred), int(idempotence), int(traversal_mode), int(direction_optimized),
-                        float(alpha), float(beta), float(queue_sizing), int(record_levels), int(host_loop))
+                        float(alpha), float(beta), float(queue_sizing), int(record_levels), int(host_loop),
+                        int(degree_order), int(stream_min_edges))
         self.mark_pred = bool(mark_pred)
         self._h = C.c_void_p()
         _capi.check(_capi.lib().grb_bfs_create(graph._h, C.byref(cfg), C.byref(self._h)), "grb_bfs_create")
@@ -172,7 +183,7 @@ class Bfs:
         _capi.check(L.grb_bfs_levels(self._h, None, 0, C.byref(cnt)), "grb_bfs_levels")
         arr = (LevelRecord * max(cnt.value, 1))()
         _capi.check(L.grb_bfs_levels(self._h, arr, cnt.value, C.byref(cnt)), "grb_bfs_levels")
-        kinds = {0: "push-twc", 1: "pull", 2: "push-lb", 3: "push-small", 4: "filter"}
+        kinds = {0: "push-twc", 1: "pull", 2: "push-lb", 3: "push-small", 4: "filter", 5: "push-stream"}
         return [dict(level=r.level, kind=kinds.get(r.kind, str(r.kind)), frontier=r.frontier, edges=r.edges,
                      discovered=r.discovered, candidates=r.candidates, ms=r.ms, switch_ms=r.switch_ms) for r in arr[:cnt.value]]
 

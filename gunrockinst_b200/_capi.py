@@ -57,7 +57,8 @@ class LevelRecord(C.Structure):
 class BfsConfig(C.Structure):
     _fields_ = [("mark_pred", C.c_int32), ("idempotence", C.c_int32), ("traversal_mode", C.c_int32),
                 ("direction_optimized", C.c_int32), ("alpha", C.c_double), ("beta", C.c_double),
-                ("queue_sizing", C.c_double), ("record_levels", C.c_int32), ("host_loop", C.c_int32)]
+                ("queue_sizing", C.c_double), ("record_levels", C.c_int32), ("host_loop", C.c_int32),
+                ("degree_order", C.c_int32), ("stream_min_edges", C.c_int32)]
 
 
 class MgLevel(C.Structure):
@@ -135,6 +136,8 @@ def lib():
     sig("grb_graph_from_host_mapped", C.c_int, [C.c_int, i64, i64, p, C.c_int, p, p, C.c_int, C.c_int, pp])
     sig("grb_graph_rmat", C.c_int, [C.c_int, C.c_int, i64, u64, C.c_int, dbl, dbl, dbl, dbl,
                                     C.c_int, C.c_int, u64, C.c_int, pp])
+    sig("grb_graph_build_transpose", C.c_int, [p])
+    sig("grb_graph_check_symmetric", C.c_int, [p, C.POINTER(C.c_int)])
     sig("grb_graph_get_info", C.c_int, [p, C.POINTER(GraphInfo)])
     sig("grb_graph_download", C.c_int, [p, p, p, p])
     sig("grb_graph_device_ptrs", C.c_int, [p, pp, pp, pp])

@@ -34,6 +34,8 @@
 #define GRB_PULL_CTAS 6      // resident CTAs per SM the stand-alone pull sweep is bounded for
 #endif
 #include <vector>
+#include <cstdlib>
+#include <cstdio>
 #include "bfs_functor.cuh"
 #include "../enactor_base.cuh"
 #include "bfs_persistent.cuh"
@@ -108,10 +110,13 @@ struct BFSOptions {
     bool   record_levels       = false;  // keep a per-level trace (adds two events per level)
     bool   host_loop           = false;  // drive every level from the host (the reference's structure) instead
                                          // of the single cooperative kernel of bfs_persistent.cuh
+    // host loop: push levels with at least this many frontier edges (idempotent mode: frontier items) take the
+    // streaming advance (oprtr/advance/lb_stream.cuh); 0 = never
+    unsigned long long stream_min_edges = 1ull << 20;
 };
 
 struct LevelRecord {
-    int level; int pull;                 // pull: 0 push-TWC, 1 pull, 2 push-LB
+    int level; int pull;                 // pull: 0 push-TWC, 1 pull, 2 push-LB, 5 push-LB streaming (lb_stream.cuh)
     unsigned long long frontier, edges, discovered, candidates;
     float ms;
     float switch_ms;                     // part of ms spent converting queue <-> bitmap (persistent loop)
@@ -133,6 +138,9 @@ class BFSEnactor : public EnactorBase {
     typedef oprtr::advance::KernelPolicy<Problem, 256, 4, GRB_LB_CTAS, true, true>   AdvancePolicy;
     typedef oprtr::advance::KernelPolicy<Problem, 256, 4, 5, true, false>  IdemAdvancePolicy;
     typedef oprtr::advance::KernelPolicy<Problem, 256, 4, GRB_PULL_CTAS, false, false> PullPolicy;
+    // streaming advance: one 1024-thread CTA per SM, tiles of 4096 entries staged in shared memory
+    typedef oprtr::advance::KernelPolicy<Problem, 1024, 4, 1, true, true>   StreamPolicy;
+    typedef oprtr::advance::KernelPolicy<Problem, 1024, 4, 1, true, false>  IdemStreamPolicy;
     // reference: END_BITMASK_CULL = 5 (bfs_enactor.cuh:594); the word-atomic mask stays exact, so keep it on
     typedef oprtr::filter::KernelPolicy<Problem, 256, GRB_FILTER_IPT, GRB_FILTER_CTAS, -1> FilterPolicy;
 
@@ -246,6 +254,15 @@ class BFSEnactor : public EnactorBase {
         return a;
     }
 
+    // words of the visited map the streaming advance mirrors in shared memory
+    template <typename P>
+    static unsigned HotWords(const Problem *problem)
+    {
+        const unsigned long long words = (unsigned long long)((problem->graph->nodes + 31) / 32);
+        const unsigned cap = oprtr::advance::lb::StreamMaxHotWords<P>();
+        return (unsigned)(words < cap ? words : cap);
+    }
+
     oprtr::advance::MODE PickMode(const BFSOptions &opt, unsigned long long frontier_edges)
     {
         if (opt.traversal_mode == 1) return oprtr::advance::LB;
@@ -268,7 +285,7 @@ class BFSEnactor : public EnactorBase {
         int per_sm = 0;
         GR_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, PersistentEntry(), AdvancePolicy::THREADS, 0));
         if (per_sm > kPersistentCtasPerSm) per_sm = kPersistentCtasPerSm;
-        persistent_ok = coop != 0 && per_sm > 0;
+        persistent_ok = coop != 0 && per_sm > 0 && !getenv("GRB_NO_PERSISTENT");
         persistent_grid = per_sm * dev.sm_count;
         GR_TRY(d_records.Allocate(kMaxRecords));
         GR_TRY(d_summary.Allocate(2));
@@ -332,6 +349,7 @@ class BFSEnactor : public EnactorBase {
         P.src = problem->src;
         P.sources = many_count ? d_sources.ptr : nullptr;
         P.num_sources = many_count;
+        P.src_map = many_count ? problem->src_map : nullptr;
         P.do_reset = reset_on_device ? 1 : 0;
         P.mask_words = (unsigned long long)problem->visited_mask.size;
         P.can_pull = can_pull ? 1 : 0;
@@ -345,8 +363,21 @@ class BFSEnactor : public EnactorBase {
         unsigned long long *cursor = reinterpret_cast<unsigned long long *>(d_summary.ptr + searches);
         unsigned long long desc_words = (unsigned long long)lb_scratch.tile_desc.size;
         void *kargs[] = {(void *)&ds, (void *)&P, (void *)&cursor, (void *)&desc_words};
-        GR_TRY(cudaLaunchCooperativeKernel((const void *)PersistentEntry(), dim3((unsigned)persistent_grid),
-                                           dim3(AdvancePolicy::THREADS), kargs, 0, stream));
+        cudaError_t le = getenv("GRB_FAIL_COOP_LAUNCH") ? cudaErrorCooperativeLaunchTooLarge
+                         : cudaLaunchCooperativeKernel((const void *)PersistentEntry(), dim3((unsigned)persistent_grid),
+                                                       dim3(AdvancePolicy::THREADS), kargs, 0, stream);
+        if (le != cudaSuccess) {
+            // co-residency is not available after all (MPS / SM partitioning, another context, a changed
+            // shared-memory carve-out): fall back to the host-driven loop for the rest of this context
+            (void)cudaGetLastError();
+            persistent_ok = false;
+            fprintf(stderr, "libgunrock (B200 build): cooperative launch of the persistent BFS kernel failed (%s); "
+                            "using the host-driven level loop\n", cudaGetErrorString(le));
+            if (many_count) return cudaErrorCooperativeLaunchTooLarge;      // the caller re-runs the batch search by search
+            if (reset_on_device) GR_TRY(problem->FillState(problem->src));
+            GR_TRY(ResetBase());
+            return EnactFused(problem, opt);
+        }
         enactor_stats.launches = 1;
         GR_TRY(cudaMemcpyAsync(h_summary.ptr, d_summary.ptr, sizeof(PersistentSummary) * (size_t)searches,
                                cudaMemcpyDeviceToHost, stream));
@@ -354,8 +385,21 @@ class BFSEnactor : public EnactorBase {
             GR_TRY(cudaMemcpyAsync(h_records.ptr, d_records.ptr, sizeof(DeviceLevelRecord) * kMaxRecords,
                                    cudaMemcpyDeviceToHost, stream));
         GR_TRY(cudaStreamSynchronize(stream));
-        const PersistentSummary &sum = h_summary.ptr[searches - 1];      // stats of the (last) search
-        lb_scratch.epoch = (unsigned)sum.epoch_end;        // the kernel wraps (and re-zeroes) on its own
+        // a search that overflowed its queues ends the batch: the later summaries stay zero.  Report the
+        // overflow whichever search raised it, and take the look-back epoch from the last search that ran
+        // (stale descriptor tags of a higher epoch must never look valid to a later scan).
+        int last_ran = 0;
+        bool overflowed = false;
+        for (int i = 0; i < searches; ++i) {
+            if (h_summary.ptr[i].ns_kernel != 0 || h_summary.ptr[i].levels != 0) last_ran = i;
+            if (h_summary.ptr[i].overflow) overflowed = true;
+        }
+        const PersistentSummary &sum = h_summary.ptr[overflowed ? last_ran : searches - 1];   // stats of the (last) search
+        lb_scratch.epoch = (unsigned)h_summary.ptr[last_ran].epoch_end;   // the kernel wraps (and re-zeroes) on its own
+        if (overflowed) {
+            GR_TRY(lb_scratch.tile_desc.Zero(stream));
+            lb_scratch.epoch = 0;
+        }
         enactor_stats.iteration = (long long)sum.levels;
         enactor_stats.total_queued = sum.total_queued;
         enactor_stats.edges_inspected = sum.edges_inspected;
@@ -375,7 +419,7 @@ class BFSEnactor : public EnactorBase {
                 levels.push_back(r);
             }
         }
-        if (sum.overflow)
+        if (overflowed)
             return util::GRError(cudaErrorInvalidConfiguration,
                                  "frontier queue overflow: increase queue_size", __FILE__, __LINE__);
         return cudaSuccess;
@@ -433,8 +477,20 @@ class BFSEnactor : public EnactorBase {
                 oprtr::advance::MODE mode = PickMode(opt, frontier_edges);
                 kind = (mode == oprtr::advance::LB) ? 2 : 0;
                 enactor_stats.launches += (mode == oprtr::advance::LB) ? 2 : 1;
-                GR_TRY((oprtr::advance::LaunchKernel<AdvancePolicy, Problem, BfsFunctor>(
-                    mode, dev, ds, PushArgs(problem, level), &lb_scratch, frontier_edges, stream)));
+                bool streamed = false;
+                if constexpr (!Problem::MARK_PREDECESSORS) {
+                    AdvArgs a = PushArgs(problem, level);
+                    if (mode == oprtr::advance::LB && opt.stream_min_edges && frontier_edges >= opt.stream_min_edges &&
+                        oprtr::advance::StreamEligible<StreamPolicy, Problem>(a)) {
+                        kind = 5;
+                        streamed = true;
+                        GR_TRY((oprtr::advance::LaunchStreamKernel<StreamPolicy, Problem, BfsFunctor>(
+                            dev, ds, a, &lb_scratch, frontier_edges, HotWords<StreamPolicy>(problem), stream)));
+                    }
+                }
+                if (!streamed)
+                    GR_TRY((oprtr::advance::LaunchKernel<AdvancePolicy, Problem, BfsFunctor>(
+                        mode, dev, ds, PushArgs(problem, level), &lb_scratch, frontier_edges, stream)));
             } else {
                 kind = 1;
                 ++enactor_stats.launches;
@@ -509,8 +565,18 @@ class BFSEnactor : public EnactorBase {
                                          (level == 0 && problem->src_degree >= opt.lb_min_edges)) ? oprtr::advance::LB
                                       : oprtr::advance::TWC_FORWARD;
             if (opt.record_levels) GR_TRY(cudaEventRecord(ev_a, stream));
-            GR_TRY((oprtr::advance::LaunchKernel<IdemAdvancePolicy, Problem, BfsFunctor>(
-                mode, dev, ds, a, &lb_scratch, (unsigned long long)g.edges, stream)));
+            bool streamed = false;
+            if constexpr (!Problem::MARK_PREDECESSORS) {
+                if (mode == oprtr::advance::LB && opt.stream_min_edges && F >= (opt.stream_min_edges >> 4) &&
+                    oprtr::advance::StreamEligible<IdemStreamPolicy, Problem>(a)) {
+                    streamed = true;
+                    GR_TRY((oprtr::advance::LaunchStreamKernel<IdemStreamPolicy, Problem, BfsFunctor>(
+                        dev, ds, a, &lb_scratch, (unsigned long long)g.edges, HotWords<IdemStreamPolicy>(problem), stream)));
+                }
+            }
+            if (!streamed)
+                GR_TRY((oprtr::advance::LaunchKernel<IdemAdvancePolicy, Problem, BfsFunctor>(
+                    mode, dev, ds, a, &lb_scratch, (unsigned long long)g.edges, stream)));
             if (opt.record_levels) GR_TRY(cudaEventRecord(ev_b, stream));
             enactor_stats.launches += (mode == oprtr::advance::LB) ? 3 : 2;
             frontier_attribute.queue_index++;
@@ -545,7 +611,7 @@ class BFSEnactor : public EnactorBase {
                 // two records per level: the advance (every neighbour emitted) and the filter that culls and
                 // compacts them (kind 4: frontier = items read, discovered = items kept)
                 LevelRecord ra, rf;
-                ra.level = level; ra.pull = (mode == oprtr::advance::LB) ? 2 : 0;
+                ra.level = level; ra.pull = streamed ? 5 : (mode == oprtr::advance::LB) ? 2 : 0;
                 ra.frontier = F; ra.edges = ca.edges; ra.discovered = ca.out_len; ra.candidates = 0; ra.switch_ms = 0;
                 rf.level = level; rf.pull = 4;
                 rf.frontier = ca.out_len; rf.edges = 0; rf.discovered = cf.out_len; rf.candidates = 0; rf.switch_ms = 0;

@@ -67,6 +67,8 @@ struct PersistentParams {
     VertexId src;                                   // the source, or ...
     const VertexId *sources;                        // ... num_sources of them, searched one after the other by ONE
     int      num_sources;                           //     launch (needs do_reset); summary[i] describes search i
+    const VertexId *src_map;                        // optional: sources[] are ids of the caller's graph, the graph
+                                                    //     here is its degree-ordered twin (src_map[v] = id here)
     int      do_reset;                              // 1: the kernel also does Problem::Reset's device work
     unsigned long long mask_words;                  // words of the visited bitmap (do_reset)
     int      can_pull;
@@ -201,7 +203,7 @@ PersistentKernel(const __grid_constant__ typename Problem::DataSlice ds0,
   for (int si = 0; si < num_searches; ++si) {
     const unsigned long long t_start = leader ? GlobalTimerNs() : 0ull;
     // ---- loop state: identical in every thread of the grid ------------------------------------
-    const VertexId src = P.sources ? P.sources[si] : P.src;
+    const VertexId src = P.sources ? (P.src_map ? P.src_map[P.sources[si]] : P.sources[si]) : P.src;
     const bool src_is_mine = P.g.part.Mine(src);
     unsigned long long F = src_is_mine ? 1ull : 0ull;
     unsigned long long frontier_edges = 0;

@@ -84,6 +84,9 @@ struct BFSProblem : ProblemBase<_VertexId, _SizeT> {
     util::DeviceArray<VertexId> head;                   // pull direction: first in-neighbour of every row
     util::DeviceArray<unsigned> next_map, recv_map;     // partitioned runs only (PrepareExchange)
     bool candidates_valid = false;
+    // the graph is the degree-ordered twin of the caller's graph: caller's id -> id here (device);
+    // applied by the persistent kernel to the sources of a batch (single runs translate on the host)
+    const VertexId *src_map = nullptr;
     unsigned long long src_degree = 0;
     VertexId src = 0;
 
@@ -154,10 +157,16 @@ struct BFSProblem : ProblemBase<_VertexId, _SizeT> {
     // fills below itself (bfs_persistent.cuh), which spares ~8 API calls and a host sync per search
     cudaError_t Reset(VertexId source, FrontierType ftype, double queue_sizing, bool on_device = false)
     {
-        cudaStream_t s = this->stream;
         GR_TRY(Base::ResetBase(ftype, queue_sizing));
         src = source;
         if (on_device) { src_degree = 0; return cudaSuccess; }
+        return FillState(source);
+    }
+
+    // the device work of Reset (what the persistent kernel otherwise does itself)
+    cudaError_t FillState(VertexId source)
+    {
+        cudaStream_t s = this->stream;
         const long long ln = this->graph->local_nodes;
         if (ln) GR_TRY(cudaMemsetAsync(labels.ptr, 0xff, sizeof(VertexId) * (size_t)ln, s));
         if (MARK_PREDECESSORS) GR_TRY(util::Fill(preds.ptr, (VertexId)-2, (unsigned long long)ln, s));

@@ -16,9 +16,7 @@
 // stored by LOCAL index, so each device builds its own slice without ever
 // holding the whole graph.
 #pragma once
-#include "../graph/csr.cuh"
-#include "../util/radix_sort.cuh"
-#include "../util/memset_kernel.cuh"
+#include "../graph/build.cuh"
 
 namespace gunrock {
 namespace graphio {
@@ -115,73 +113,6 @@ RmatGenerateKernel(RmatParams p, unsigned long long *keys, unsigned long long ca
     }
 }
 
-// ---- sorted tuples -> canonical CSR -----------------------------------------------------
-constexpr int kKeepThreads = 256, kKeepItems = 8, kKeepTile = kKeepThreads * kKeepItems;
-
-__device__ __forceinline__ bool KeepTuple(const unsigned long long *keys, unsigned long long i, int scale,
-                                          const graph::Partition &part)
-{
-    const unsigned long long k = keys[i];
-    if (i > 0 && keys[i - 1] == k) return false;                               // duplicate (csr.cuh:282-288)
-    const long long row = part.Global((long long)(k >> scale));
-    const long long col = (long long)(k & ((1ull << scale) - 1));
-    return row != col;                                                         // self loop
-}
-
-static __global__ void __launch_bounds__(kKeepThreads)
-CountKeptKernel(const unsigned long long *keys, unsigned long long n, int scale, graph::Partition part,
-                unsigned long long *tile_counts)
-{
-    __shared__ unsigned long long s_warp[kKeepThreads / 32 + 1];
-    const unsigned long long base = (unsigned long long)blockIdx.x * kKeepTile + (unsigned long long)threadIdx.x * kKeepItems;
-    unsigned long long mine = 0;
-#pragma unroll
-    for (int r = 0; r < kKeepItems; ++r)
-        if (base + r < n && KeepTuple(keys, base + r, scale, part)) ++mine;
-    unsigned long long total;
-    (void)util::BlockExclusiveSum<kKeepThreads>(mine, s_warp, total);
-    if (threadIdx.x == 0) tile_counts[blockIdx.x] = total;
-}
-
-// writes col[j] and krow[j] (local row) for every kept tuple j
-static __global__ void __launch_bounds__(kKeepThreads)
-CompactKeptKernel(const unsigned long long *keys, unsigned long long n, int scale, graph::Partition part,
-                  const unsigned long long *tile_offsets, int *col, int *krow)
-{
-    __shared__ unsigned long long s_warp[kKeepThreads / 32 + 1];
-    const unsigned long long base = (unsigned long long)blockIdx.x * kKeepTile + (unsigned long long)threadIdx.x * kKeepItems;
-    bool keep[kKeepItems];
-    unsigned long long mine = 0;
-#pragma unroll
-    for (int r = 0; r < kKeepItems; ++r) {
-        keep[r] = base + r < n && KeepTuple(keys, base + r, scale, part);
-        if (keep[r]) ++mine;
-    }
-    unsigned long long total;
-    unsigned long long at = tile_offsets[blockIdx.x] + util::BlockExclusiveSum<kKeepThreads>(mine, s_warp, total);
-#pragma unroll
-    for (int r = 0; r < kKeepItems; ++r) {
-        if (keep[r]) {
-            const unsigned long long k = keys[base + r];
-            col[at]  = (int)(k & ((1ull << scale) - 1));
-            krow[at] = (int)(k >> scale);
-            ++at;
-        }
-    }
-}
-
-// row_offsets[x] = first kept tuple whose local row is >= x
-template <typename SizeT>
-__global__ void RowOffsetsKernel(const int *krow, unsigned long long m, long long local_nodes, SizeT *row_offsets)
-{
-    const unsigned long long stride = (unsigned long long)gridDim.x * blockDim.x;
-    for (unsigned long long j = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x; j <= m; j += stride) {
-        const long long lo = (j == 0) ? 0 : (long long)krow[j - 1] + 1;
-        const long long hi = (j == m) ? local_nodes : (long long)krow[j];
-        for (long long x = lo; x <= hi; ++x) row_offsets[x] = (SizeT)j;
-    }
-}
-
 // symmetric weights in [1, 64] (both directions of an edge hash the same pair;
 // the reference's loader gives both directions the file's value, market.cuh:173-181)
 static __global__ void EdgeWeightsKernel(const int *krow, const int *col, unsigned long long m, graph::Partition part,
@@ -236,33 +167,14 @@ cudaError_t BuildRmatCsr(int scale, unsigned long long edges, unsigned long long
     GR_TRY(util::RadixSort64(keys_a.ptr, keys_b.ptr, tuples, key_bits, sort_scratch, &sorted, s));
     unsigned long long *spare = (sorted == keys_a.ptr) ? keys_b.ptr : keys_a.ptr;
 
-    // duplicates / self loops out, columns + rows compacted
-    const unsigned long long tiles = (tuples + kKeepTile - 1) / kKeepTile;
-    util::DeviceArray<unsigned long long> tile_counts, block_sums;
-    GR_TRY(tile_counts.Allocate((size_t)tiles + 2));
-    GR_TRY(block_sums.Allocate((size_t)util::ScanBlocks(tiles + 1) + 2));
+    // duplicates / self loops out, columns + rows compacted (graph/build.cuh)
     unsigned long long m = 0;
-    if (tiles) {
-        CountKeptKernel<<<(unsigned)tiles, kKeepThreads, 0, s>>>(sorted, tuples, scale, part, tile_counts.ptr);
-        GR_TRY(cudaGetLastError());
-        GR_TRY(util::ExclusiveScan<unsigned long long>(tile_counts.ptr, tile_counts.ptr, tiles, block_sums.ptr, s));
-        GR_TRY(cudaMemcpyAsync(&m, block_sums.ptr + util::ScanBlocks(tiles), sizeof(m), cudaMemcpyDeviceToHost, s));
-        GR_TRY(cudaStreamSynchronize(s));
-    }
-    if (sizeof(SizeT) == 4 && m >= 0x7fffffffull)
-        return util::GRError(cudaErrorInvalidValue, "R-MAT slice needs 64-bit edge offsets", __FILE__, __LINE__);
-    out.nodes = nodes; out.local_nodes = local_nodes; out.edges = (long long)m; out.part = part;
+    int *krow = nullptr;                                    // the idle sort buffer holds the kept rows
+    out.nodes = nodes; out.local_nodes = local_nodes; out.part = part;
     out.symmetric = undirected;
-    GR_TRY(out.col_indices.Allocate((size_t)m));
-    GR_TRY(out.row_offsets.Allocate((size_t)local_nodes + 1));
-    int *krow = reinterpret_cast<int *>(spare);             // the idle sort buffer holds the kept rows
-    if (tiles) {
-        CompactKeptKernel<<<(unsigned)tiles, kKeepThreads, 0, s>>>(sorted, tuples, scale, part, tile_counts.ptr,
-                                                                  out.col_indices.ptr, krow);
-        GR_TRY(cudaGetLastError());
-    }
-    RowOffsetsKernel<SizeT><<<util::FillGrid(m + 1), 256, 0, s>>>(krow, m, local_nodes, out.row_offsets.ptr);
-    GR_TRY(cudaGetLastError());
+    GR_TRY(graph::SortedKeysToCsr<SizeT>(sorted, spare, tuples, scale, part, true, local_nodes, out.row_offsets,
+                                         out.col_indices, &m, &krow, s));
+    out.edges = (long long)m;
     if (weight_seed) {
         GR_TRY(out.edge_values.Allocate((size_t)m));
         if (m) {

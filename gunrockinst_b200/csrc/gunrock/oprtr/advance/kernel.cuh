@@ -8,6 +8,7 @@
 // a relaunch loop of an instrumented kernel (:552-726); neither exists here.
 #pragma once
 #include "lb.cuh"
+#include "lb_stream.cuh"
 #include "twc.cuh"
 #include "pull.cuh"
 #include "reduce.cuh"
@@ -71,6 +72,57 @@ cudaError_t LaunchKernel(
         return util::GRError(cudaGetLastError(), "advance lb::ExpandKernel launch failed", __FILE__, __LINE__);
     }
     return util::GRError(cudaErrorInvalidValue, "advance: push launcher called with a pull mode", __FILE__, __LINE__);
+}
+
+// The streaming instance of the LB mode (lb_stream.cuh): same scan, then one 1024-thread CTA per SM
+// that stages neighbour-list tiles in shared memory through TMA / cp.async and probes the hot part
+// of the visited map there.  Policy::THREADS must be 1024; callers check StreamEligible first.
+template <typename Policy, typename Problem>
+inline bool StreamEligible(const Args<typename Policy::VertexId, typename Policy::SizeT> &args)
+{
+    return !Problem::MARK_PREDECESSORS && args.type == V2V && args.output != OUT_TOMBSTONE &&
+           args.g.part.log_parts == 0 && args.in_queue != nullptr;
+}
+
+template <typename Policy, typename Problem, typename Functor>
+cudaError_t LaunchStreamKernel(
+    const DeviceInfo &dev,
+    const typename Problem::DataSlice &ds,
+    Args<typename Policy::VertexId, typename Policy::SizeT> args,
+    LbScratch<typename Policy::SizeT> *scratch,
+    unsigned long long edges_hint,
+    unsigned hot_words,                 // words of the visited map mirrored in shared memory (PRE_CULL policies)
+    cudaStream_t stream)
+{
+    if (!scratch) return util::GRError(cudaErrorInvalidValue, "advance LB needs scratch", __FILE__, __LINE__);
+    if (args.in_len + 1 > scratch->scanned.cap)
+        return util::GRError(cudaErrorInvalidValue, "advance LB scratch too small", __FILE__, __LINE__);
+    auto kernel = lb::StreamExpandKernel<Policy, Problem, Functor>;
+    static bool configured = false;     // per instantiation
+    if (!configured) {
+        GR_TRY(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 232448));
+        configured = true;
+    }
+    if (!Policy::PRE_CULL) hot_words = 0;
+    if (hot_words > lb::StreamMaxHotWords<Policy>()) hot_words = lb::StreamMaxHotWords<Policy>();
+    if (++scratch->epoch >= lb::kEpochLimit) {
+        GR_TRY(scratch->tile_desc.Zero(stream));
+        scratch->epoch = 1;
+    }
+    LbScratchView<typename Policy::SizeT> sv;
+    sv.scanned = scratch->scanned.ptr;   sv.row_start = scratch->row_start.ptr;
+    sv.tile_desc = scratch->tile_desc.ptr; sv.part_start = scratch->part_start.ptr; sv.ticket = scratch->ticket.ptr;
+    sv.part_cap = scratch->part_start.cap;
+    sv.epoch = scratch->epoch;
+    unsigned long long scan_tiles = (args.in_len + Policy::SCAN_TILE - 1) / Policy::SCAN_TILE;
+    unsigned scan_grid = (unsigned)(scan_tiles < 1 ? 1 : scan_tiles);
+    lb::ScanKernel<Policy><<<scan_grid, Policy::SCAN_THREADS, 0, stream>>>(args, sv);
+    GR_TRY(cudaGetLastError());
+    unsigned long long tiles = (edges_hint + Policy::TILE_EDGES - 1) / Policy::TILE_EDGES;
+    unsigned grid = (unsigned)(tiles < 1 ? 1 : (tiles < (unsigned long long)dev.sm_count ? tiles : (unsigned long long)dev.sm_count));
+    const size_t smem = lb::StreamHotOffset<Policy>() + sizeof(unsigned) * (size_t)hot_words;
+    kernel<<<grid, Policy::THREADS, smem, stream>>>(ds, args, sv, hot_words);
+    return util::GRError(cudaGetLastError(), "advance lb::StreamExpandKernel launch failed", __FILE__, __LINE__);
 }
 
 // Pull-direction advance (TWC_BACKWARD / LB_BACKWARD share one implementation).

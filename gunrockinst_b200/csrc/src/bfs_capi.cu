@@ -25,9 +25,26 @@ extern "C" int grb_bfs_create(grb_graph_t g, const grb_bfs_config *cfg, grb_bfs_
     *out = nullptr;
     GRB_TRY(cudaSetDevice(g->device()));
     cudaError_t err = cudaSuccess;
+    const bool single = (g->g32 ? g->g32->part.log_parts : g->g64->part.log_parts) == 0;
+    const bool mapped = g->g32 ? g->g32->streams_from_host : g->g64->streams_from_host;
+    const bool symmetric = g->g32 ? g->g32->symmetric : g->g64->symmetric;
+    if (cfg && cfg->direction_optimized && !symmetric) {
+        // the pull direction walks in-edges: a directed graph needs its transpose (the reference's DOBFS
+        // takes an inverse graph, app/dobfs/dobfs_problem.cuh:211-260); built once per graph handle
+        if (single && !mapped) GRB_TRY(g->EnsureTranspose());
+        else fprintf(stderr, "libgunrock (B200 build): direction-optimised BFS on a directed graph that is %s: "
+                             "no inverse graph can be built, the search runs push-only\n",
+                     single ? "read in place from host memory" : "partitioned");
+    }
+    const bool twin = cfg && cfg->degree_order && single && !mapped;
+    if (twin) GRB_TRY(g->EnsureTwin());
     grb_bfs_s *c = new grb_bfs_s();
     c->graph = g;
-    c->runner = g->g32 ? MakeBfsRunner32(g->g32, cfg, g->stream, &err) : MakeBfsRunner64(g->g64, cfg, g->stream, &err);
+    if (twin)
+        c->runner = g->g32 ? MakeBfsRunner32(g->twin32, cfg, g->stream, &err, g->to_new.ptr, g->to_old.ptr)
+                           : MakeBfsRunner64(g->twin64, cfg, g->stream, &err, g->to_new.ptr, g->to_old.ptr);
+    else
+        c->runner = g->g32 ? MakeBfsRunner32(g->g32, cfg, g->stream, &err) : MakeBfsRunner64(g->g64, cfg, g->stream, &err);
     if (!c->runner) { delete c; return (int)(err ? err : cudaErrorUnknown); }
     *out = c;
     return 0;

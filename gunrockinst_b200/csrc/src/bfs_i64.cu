@@ -2,9 +2,10 @@
 // the reference's SizeT is int only, gunrock.h:33-36).
 #include "bfs_runner.cuh"
 
-BfsRunnerBase *MakeBfsRunner64(Csr64 *g, const grb_bfs_config *cfg, cudaStream_t s, cudaError_t *err)
+BfsRunnerBase *MakeBfsRunner64(Csr64 *g, const grb_bfs_config *cfg, cudaStream_t s, cudaError_t *err,
+                               const int *to_new, const int *to_old)
 {
     const bool pred = cfg && cfg->mark_pred;
-    if (pred) return MakeOne<BfsRunner<long long, true, false>>(g, cfg, s, err);
-    return MakeOne<BfsRunner<long long, false, false>>(g, cfg, s, err);
+    if (pred) return MakeOne<BfsRunner<long long, true, false>>(g, cfg, s, err, to_new, to_old);
+    return MakeOne<BfsRunner<long long, false, false>>(g, cfg, s, err, to_new, to_old);
 }

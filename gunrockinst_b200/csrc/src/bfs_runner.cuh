@@ -26,6 +26,11 @@ struct BfsRunner : BfsRunnerBase {
     cudaStream_t stream = 0;
     cudaEvent_t e0 = nullptr, e1 = nullptr, e2 = nullptr;
     bool ready = false;
+    // degree order: the problem runs on the graph's twin; sources are translated on the way in,
+    // labels / predecessors on the way out (lazily: only when somebody asks for them)
+    const int *to_new = nullptr, *to_old = nullptr;
+    gunrock::util::DeviceArray<int> out_labels, out_preds;
+    bool out_valid = false;
 
     ~BfsRunner()
     {
@@ -34,9 +39,11 @@ struct BfsRunner : BfsRunnerBase {
         if (e2) cudaEventDestroy(e2);
     }
 
-    cudaError_t Create(gunrock::graph::DeviceCsr<int, SizeT> *g, const grb_bfs_config *cfg, cudaStream_t s)
+    cudaError_t Create(gunrock::graph::DeviceCsr<int, SizeT> *g, const grb_bfs_config *cfg, cudaStream_t s,
+                       const int *map_to_new = nullptr, const int *map_to_old = nullptr)
     {
         stream = s;
+        to_new = map_to_new; to_old = map_to_old;
         if (cfg) {
             opt.traversal_mode = cfg->traversal_mode;
             opt.direction_optimized = cfg->direction_optimized != 0;
@@ -48,9 +55,12 @@ struct BfsRunner : BfsRunnerBase {
             // launch + counter fetch there), the host-driven loop of stand-alone kernels above (at scale
             // 25 they run the big levels 1.1-1.35x faster: 5 instead of 4 resident CTAs per SM, fewer
             // live registers around the operator bodies); 1: host loop; 2: persistent kernel
+            if (cfg->stream_min_edges == 1) opt.stream_min_edges = 0;                  // streaming advance off
+            else if (cfg->stream_min_edges > 1) opt.stream_min_edges = (unsigned long long)cfg->stream_min_edges;
             opt.host_loop = cfg->host_loop == 1 || (cfg->host_loop == 0 && g->nodes >= (1ll << 24));
         }
         GR_TRY(problem.Init(g, s));
+        problem.src_map = to_new;
         GR_TRY(cudaEventCreate(&e0)); GR_TRY(cudaEventCreate(&e1)); GR_TRY(cudaEventCreate(&e2));
         return cudaSuccess;
     }
@@ -59,6 +69,11 @@ struct BfsRunner : BfsRunnerBase {
     {
         using gunrock::app::VERTEX_FRONTIERS;
         using gunrock::app::EDGE_FRONTIERS;
+        out_valid = false;
+        if (to_new && src >= 0 && (long long)src < problem.graph->nodes) {      // the twin's id of the source
+            GR_TRY(cudaMemcpyAsync(&src, to_new + src, sizeof(int), cudaMemcpyDeviceToHost, stream));
+            GR_TRY(cudaStreamSynchronize(stream));
+        }
         GR_TRY(cudaEventRecord(e0, stream));
         const bool fused_reset = ready && enactor.FusesReset(src, &problem, opt);
         GR_TRY(problem.Reset(src, IDEM ? EDGE_FRONTIERS : VERTEX_FRONTIERS, queue_sizing, fused_reset));
@@ -68,7 +83,7 @@ struct BfsRunner : BfsRunnerBase {
         GR_TRY(cudaEventRecord(e2, stream));
         GR_TRY(cudaEventSynchronize(e2));
         if (IDEM) GR_TRY(enactor.RecountEdgesVisited(&problem));
-        if (labels_host) GR_TRY(problem.Extract(labels_host, preds_host));
+        if (labels_host) GR_TRY(Extract(labels_host, preds_host));
         if (stats) {
             float r = 0, t = 0;
             cudaEventElapsedTime(&r, e0, e1); cudaEventElapsedTime(&t, e1, e2);
@@ -87,6 +102,36 @@ struct BfsRunner : BfsRunnerBase {
         }
         return cudaSuccess;
     }
+    // labels (and predecessors) in the caller's vertex ids, on the device
+    cudaError_t Untwin()
+    {
+        if (!to_new || out_valid) return cudaSuccess;
+        const long long n = problem.graph->nodes;
+        GR_TRY(out_labels.Allocate((size_t)n + 1));
+        if (n) {
+            gunrock::graph::GatherThroughKernel<false><<<gunrock::util::FillGrid((unsigned long long)n), 256, 0, stream>>>(
+                problem.labels.ptr, to_new, to_old, n, out_labels.ptr);
+            GR_TRY(cudaGetLastError());
+            if (MARK_PRED) {
+                GR_TRY(out_preds.Allocate((size_t)n + 1));
+                gunrock::graph::GatherThroughKernel<true><<<gunrock::util::FillGrid((unsigned long long)n), 256, 0, stream>>>(
+                    problem.preds.ptr, to_new, to_old, n, out_preds.ptr);
+                GR_TRY(cudaGetLastError());
+            }
+        }
+        out_valid = true;
+        return cudaSuccess;
+    }
+    // reference: BFSProblem::Extract (bfs_problem.cuh:144-177)
+    cudaError_t Extract(int *labels_host, int *preds_host)
+    {
+        if (!to_new) return problem.Extract(labels_host, preds_host);
+        GR_TRY(Untwin());
+        const size_t n = (size_t)problem.graph->nodes;
+        GR_TRY(out_labels.ToHost(labels_host, n, stream));
+        if (MARK_PRED && preds_host) GR_TRY(out_preds.ToHost(preds_host, n, stream));
+        return cudaStreamSynchronize(stream);
+    }
     // `count` searches; when the persistent kernel can take them, batches of up to kBatch sources run
     // as ONE launch each (no launch, copy or host synchronisation between two searches)
     cudaError_t RunMany(const int *srcs, int count, grb_stats *stats) override
@@ -98,6 +143,7 @@ struct BfsRunner : BfsRunnerBase {
             bool batch = ready && !IDEM && !opt.record_levels && count - done > 1;
             int take = count - done < kBatch ? count - done : kBatch;
             for (int i = 0; batch && i < take; ++i) batch = enactor.FusesReset(srcs[done + i], &problem, opt);
+            out_valid = false;
             if (!batch) {
                 GR_TRY(Run(srcs[done], nullptr, nullptr, stats ? stats + done : nullptr));
                 ++done;
@@ -106,7 +152,9 @@ struct BfsRunner : BfsRunnerBase {
             if constexpr (!IDEM) {
                 std::vector<gunrock::app::bfs::PersistentSummary> sums((size_t)take);
                 GR_TRY(problem.Reset(srcs[done + take - 1], VERTEX_FRONTIERS, queue_sizing, true));
-                GR_TRY(enactor.Enact(&problem, srcs[done + take - 1], opt, true, srcs + done, take, sums.data()));
+                cudaError_t be = enactor.Enact(&problem, srcs[done + take - 1], opt, true, srcs + done, take, sums.data());
+                if (be == cudaErrorCooperativeLaunchTooLarge && !enactor.persistent_ok) continue;   // search by search from here on
+                GR_TRY(be);
                 for (int i = 0; stats && i < take; ++i) {
                     grb_stats *st = stats + done + i;
                     memset(st, 0, sizeof(*st));
@@ -128,18 +176,27 @@ struct BfsRunner : BfsRunnerBase {
         }
         return cudaSuccess;
     }
-    void *DeviceLabels() override { return problem.labels.ptr; }
+    void *DeviceLabels() override
+    {
+        if (!to_new) return problem.labels.ptr;
+        if (Untwin() != cudaSuccess || cudaStreamSynchronize(stream) != cudaSuccess) return nullptr;
+        return out_labels.ptr;
+    }
     const std::vector<gunrock::app::bfs::LevelRecord> &Levels() override { return enactor.levels; }
 };
 
-BfsRunnerBase *MakeBfsRunner32(Csr32 *g, const grb_bfs_config *cfg, cudaStream_t s, cudaError_t *err);
-BfsRunnerBase *MakeBfsRunner64(Csr64 *g, const grb_bfs_config *cfg, cudaStream_t s, cudaError_t *err);
+// to_new / to_old non-NULL: `g` is the degree-ordered twin of the caller's graph
+BfsRunnerBase *MakeBfsRunner32(Csr32 *g, const grb_bfs_config *cfg, cudaStream_t s, cudaError_t *err,
+                               const int *to_new = nullptr, const int *to_old = nullptr);
+BfsRunnerBase *MakeBfsRunner64(Csr64 *g, const grb_bfs_config *cfg, cudaStream_t s, cudaError_t *err,
+                               const int *to_new = nullptr, const int *to_old = nullptr);
 
 template <typename R, typename G>
-static BfsRunnerBase *MakeOne(G *g, const grb_bfs_config *cfg, cudaStream_t s, cudaError_t *err)
+static BfsRunnerBase *MakeOne(G *g, const grb_bfs_config *cfg, cudaStream_t s, cudaError_t *err,
+                              const int *to_new, const int *to_old)
 {
     R *r = new R();
-    *err = r->Create(g, cfg, s);
+    *err = r->Create(g, cfg, s, to_new, to_old);
     if (*err != cudaSuccess) { delete r; return nullptr; }
     return r;
 }

@@ -3,7 +3,7 @@
 // (graphs past 2^31 entries, i.e. R-MAT scale 27 on one or two devices).
 #pragma once
 #include <cstdint>
-#include "../gunrock/graph/csr.cuh"
+#include "../gunrock/graph/build.cuh"
 
 typedef gunrock::graph::DeviceCsr<int, int>       Csr32;
 typedef gunrock::graph::DeviceCsr<int, long long> Csr64;
@@ -13,10 +13,35 @@ struct grb_graph_s {
     Csr32 *g32 = nullptr;
     Csr64 *g64 = nullptr;
     cudaStream_t stream = 0;
+    // degree-ordered twin (graph/build.cuh), built on first use by a BFS context that asks for it
+    Csr32 *twin32 = nullptr;
+    Csr64 *twin64 = nullptr;
+    gunrock::util::DeviceArray<int> to_new, to_old;     // caller's id -> twin id and back
     ~grb_graph_s()
     {
+        delete twin32; delete twin64;
         delete g32; delete g64;
         if (stream) cudaStreamDestroy(stream);
+    }
+    bool has_twin() const { return twin32 || twin64; }
+    cudaError_t EnsureTwin()
+    {
+        if (has_twin()) {       // a transpose attached to the graph after the twin was built
+            if (twin32 && !twin32->HasInverse() && g32->HasInverse()) return gunrock::graph::BuildTranspose(*twin32, stream);
+            if (twin64 && !twin64->HasInverse() && g64->HasInverse()) return gunrock::graph::BuildTranspose(*twin64, stream);
+            return cudaSuccess;
+        }
+        cudaError_t e;
+        if (g32) { twin32 = new Csr32(); e = gunrock::graph::BuildDegreeOrdered(*g32, *twin32, to_new, to_old, stream); }
+        else     { twin64 = new Csr64(); e = gunrock::graph::BuildDegreeOrdered(*g64, *twin64, to_new, to_old, stream); }
+        if (e != cudaSuccess) { delete twin32; delete twin64; twin32 = nullptr; twin64 = nullptr; }
+        return e;
+    }
+    // transpose of a directed graph (the pull direction's inverse graph)
+    cudaError_t EnsureTranspose()
+    {
+        if (g32) return (g32->symmetric || g32->csc_offsets.size) ? cudaSuccess : gunrock::graph::BuildTranspose(*g32, stream);
+        return (g64->symmetric || g64->csc_offsets.size) ? cudaSuccess : gunrock::graph::BuildTranspose(*g64, stream);
     }
     long long nodes() const { return g32 ? g32->nodes : g64->nodes; }
     long long local_nodes() const { return g32 ? g32->local_nodes : g64->local_nodes; }

@@ -74,6 +74,57 @@ extern "C" int grb_graph_from_host_mapped(int device, int64_t nodes, int64_t edg
                          force_offset_bytes, true, out);
 }
 
+extern "C" int grb_graph_build_transpose(grb_graph_t g)
+{
+    if (!g) return (int)cudaErrorInvalidValue;
+    GRB_TRY(cudaSetDevice(g->device()));
+    GRB_TRY(g->EnsureTranspose());
+    return 0;
+}
+
+// CSR == its transpose?  (graph/build.cuh: both are canonical sorted CSRs of the same multiset iff equal)
+template <typename G>
+static cudaError_t CheckSymmetric(G &g, cudaStream_t s, int *out)
+{
+    using namespace gunrock;
+    *out = 0;
+    if (g.part.log_parts != 0 || g.streams_from_host)
+        return util::GRError(cudaErrorInvalidValue, "symmetry check: resident single-device graphs only", __FILE__, __LINE__);
+    G t;
+    t.nodes = t.local_nodes = g.nodes; t.edges = g.edges; t.device = g.device;
+    // transpose into a scratch object: borrow the forward arrays, keep the result in t.csc_*
+    t.row_offsets.Borrow(g.row_offsets.ptr, g.row_offsets.size);
+    t.col_indices.Borrow(g.col_indices.ptr, g.col_indices.size);
+    GR_TRY(graph::BuildTranspose(t, s));
+    util::DeviceArray<unsigned long long> diff;
+    GR_TRY(diff.Allocate(1));
+    GR_TRY(diff.Zero(s));
+    // the forward rows must be sorted for an element-wise comparison: sort a copy through the same path
+    G f;
+    f.nodes = f.local_nodes = g.nodes; f.edges = g.edges; f.device = g.device;
+    f.row_offsets.Borrow(t.csc_offsets.ptr, t.csc_offsets.size);
+    f.col_indices.Borrow(t.csc_indices.ptr, t.csc_indices.size);
+    GR_TRY(graph::BuildTranspose(f, s));        // transpose of the transpose = the forward graph, rows sorted
+    graph::CountDifferencesKernel<<<util::FillGrid((unsigned long long)g.edges + (unsigned long long)g.nodes + 1), 256, 0, s>>>(
+        f.csc_offsets.ptr, t.csc_offsets.ptr, (unsigned long long)g.nodes + 1,
+        f.csc_indices.ptr, t.csc_indices.ptr, (unsigned long long)g.edges, diff.ptr);
+    GR_TRY(cudaGetLastError());
+    unsigned long long h = 1;
+    GR_TRY(cudaMemcpyAsync(&h, diff.ptr, sizeof(h), cudaMemcpyDeviceToHost, s));
+    GR_TRY(cudaStreamSynchronize(s));
+    *out = h == 0 ? 1 : 0;
+    return cudaSuccess;
+}
+
+extern "C" int grb_graph_check_symmetric(grb_graph_t g, int *symmetric_out)
+{
+    if (!g || !symmetric_out) return (int)cudaErrorInvalidValue;
+    GRB_TRY(cudaSetDevice(g->device()));
+    if (g->g32) GRB_TRY(CheckSymmetric(*g->g32, g->stream, symmetric_out));
+    else        GRB_TRY(CheckSymmetric(*g->g64, g->stream, symmetric_out));
+    return 0;
+}
+
 extern "C" int grb_graph_get_info(grb_graph_t g, grb_graph_info *info)
 {
     if (!g || !info) return (int)cudaErrorInvalidValue;

@@ -83,6 +83,14 @@ int grb_graph_rmat(int device, int scale, int64_t edges, uint64_t seed, int undi
                    int log_parts, int rank, uint64_t weight_seed,
                    int force_offset_bytes, grb_graph_t *out);
 
+/* build the transpose (CSC) of a directed resident graph, the inverse graph the pull direction of a
+ * direction-optimising BFS walks (reference: the inverse Csr handed to DOBFSProblem::Init,
+ * app/dobfs/dobfs_problem.cuh:211-260, tests/dobfs/test_dobfs.cu:477-560).  No-op on a symmetric
+ * graph; grb_bfs_create does this on demand.  Single-device resident graphs. */
+int  grb_graph_build_transpose(grb_graph_t g);
+/* symmetric_out = 1 iff the CSR equals its transpose as a multiset of (row, col) entries -- what the
+ * `symmetric` promise of grb_graph_from_host means.  Costs a sort of the edge list. */
+int  grb_graph_check_symmetric(grb_graph_t g, int *symmetric_out);
 int  grb_graph_get_info(grb_graph_t g, grb_graph_info *info);
 /* copy the resident CSR back (row_offsets in the graph's offset width) */
 int  grb_graph_download(grb_graph_t g, void *row_offsets, int32_t *col_indices, uint32_t *weights);
@@ -132,6 +140,13 @@ typedef struct {
     int32_t host_loop;            /* 0: by size (one cooperative kernel below 2^24 vertices, host-driven
                                      above); 1: one launch set + counter fetch per level, driven by
                                      the host; 2: whole level loop in one cooperative kernel */
+    int32_t degree_order;         /* != 0: search the graph's degree-ordered twin (same graph, vertices
+                                     renumbered by descending degree, built once per graph handle and kept
+                                     next to it: + one CSR of device memory).  Sources, labels and
+                                     predecessors stay in the caller's ids.  Resident single-device graphs. */
+    int32_t stream_min_edges;     /* host-driven loop: push levels with at least this many frontier edges take the
+                                     streaming advance (TMA-staged neighbour tiles, hot part of the visited map in
+                                     shared memory); 0: library default (2^20), 1: never */
 } grb_bfs_config;
 
 typedef struct grb_bfs_s *grb_bfs_t;

@@ -177,9 +177,10 @@ PR_TOL = 1e-6
 
 
 def _check_pr(ranks, st, want, it):
-    scale = max(1.0, float(np.abs(want).max()))
-    err = float(np.max(np.abs(ranks - want))) if want.size else 0.0
-    return st["iterations"] == it and err <= PR_TOL * scale, (st["iterations"], it, err)
+    # per vertex, against the vertex's own value (no graph-wide scale): BASELINE.json north_star
+    err = np.abs(ranks - want)
+    worst = float(np.max(err - PR_TOL * np.maximum(1.0, np.abs(want)))) if want.size else -1.0
+    return st["iterations"] == it and worst <= 0.0, (st["iterations"], it, float(err.max()) if want.size else 0.0)
 
 
 @pytest.mark.parametrize("name", ["bips98_606", "chesapeake", "test_cc", "test_pr"])
@@ -212,7 +213,7 @@ def test_pagerank_world1_rmat(gr, orc, scale):
     assert st["iterations"] > 3 and st["valid_nodes"] == int(np.count_nonzero(np.diff(ro)))
     single, _, st1 = gr.pagerank(g)                     # the single-device push formulation, same graph
     assert st1["iterations"] == st["iterations"]
-    assert np.max(np.abs(single - pr.gather())) <= PR_TOL * max(1.0, float(want.max()))
+    assert np.all(np.abs(single - pr.gather()) <= PR_TOL * np.maximum(1.0, np.abs(want)))
     pr.close()
 
 

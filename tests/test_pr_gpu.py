@@ -1,6 +1,7 @@
 """GPU: PageRank through the C ABI against the oracle's fp64 restatement of the reference's
-functor semantics.  Tolerance (BASELINE.json north_star): 1e-6 per vertex, absolute, on the
-un-normalised ranks; the same number of power iterations must be executed."""
+functor semantics.  Tolerance (BASELINE.json north_star): 1e-6 per vertex on the un-normalised
+ranks -- |got[v] - want[v]| <= 1e-6 * max(1, |want[v]|), every vertex against its own value, no
+graph-wide scale -- and the same number of power iterations must be executed."""
 import numpy as np
 import pytest
 
@@ -10,6 +11,14 @@ pytestmark = pytest.mark.gpu
 TOL = 1e-6
 
 
+def assert_per_vertex(got, want, tol=TOL):
+    """every vertex within tol of its own reference value (relative above 1, absolute below)"""
+    err = np.abs(np.asarray(got, dtype=np.float64) - want)
+    bound = tol * np.maximum(1.0, np.abs(want))
+    bad = np.nonzero(err > bound)[0]
+    assert bad.size == 0, (int(bad.size), int(bad[0]), float(err[bad[0]]), float(want[bad[0]]))
+
+
 def _check(gr, orc, ro, co, symmetric, **kw):
     src = kw.get("src", -1)
     want, it = orc.pagerank(ro, co, kw.get("delta", 0.85), kw.get("threshold", 1e-6), kw.get("max_iter", 1000), src)
@@ -17,8 +26,7 @@ def _check(gr, orc, ro, co, symmetric, **kw):
     ranks, srt, st = gr.pagerank(g, src=src, delta=kw.get("delta", 0.85), threshold=kw.get("threshold", 1e-6),
                                  max_iter=kw.get("max_iter", 1000), want_sorted=True)
     assert st["iterations"] == it
-    scale = max(1.0, float(np.abs(want).max()))
-    assert np.max(np.abs(ranks - want)) <= TOL * scale, np.max(np.abs(ranks - want))
+    assert_per_vertex(ranks, want)
     ids, sr = srt
     assert sorted(ids.tolist()) == list(range(ro.size - 1))
     assert np.all(np.diff(sr) <= 0)                                    # descending

@@ -159,6 +159,54 @@ def level_bytes(rec, offset_bytes, nodes):
 # ----------------------------------------------------------------------------------------
 # reference arm: the reference's CPU BFS on the host cores
 # ----------------------------------------------------------------------------------------
+def synthesize(scale, path):
+    """`bench.py --synthesize SCALE PATH` (a child process of the reference arm): write the seeded R-MAT CSR
+    -- the same arrays oracle.rmat_csr yields, built by the device generator in seconds where a GPU exists --
+    to PATH.ro.npy / PATH.co.npy and exit.  The process that times the reference never loads libgunrock.so."""
+    import numpy as np
+    ro = co = None
+    source = "oracle generator (CPU)"
+    try:
+        import gunrockinst_b200 as gr
+        if gr.device_count() > 0:
+            g = gr.Graph.rmat(scale)
+            ro, co = g.download()
+            g.close()
+            source = "device generator in a child process that exited before timing (same seeded CSR as oracle.rmat_csr)"
+    except Exception:
+        ro = None
+    if ro is None:
+        import oracle
+        oracle.build()
+        ro, co = oracle.rmat_csr(scale)
+    np.save(path + ".ro.npy", ro.astype(np.int64))
+    np.save(path + ".co.npy", np.ascontiguousarray(co, dtype=np.int32))
+    with open(path + ".src", "w") as f:
+        f.write(source)
+
+
+def load_synthetic_csr(scale):
+    """-> (row_offsets, col, how): the reference arm's input, produced by a child process (see synthesize)"""
+    import subprocess
+    import tempfile
+    import numpy as np
+    base = "/dev/shm" if os.path.isdir("/dev/shm") and os.access("/dev/shm", os.W_OK) else tempfile.gettempdir()
+    path = os.path.join(base, "grb_bench_rmat_s%d_%d" % (scale, os.getpid()))
+    try:
+        subprocess.check_call([sys.executable, os.path.abspath(__file__), "--synthesize", str(scale), path],
+                              stdout=subprocess.DEVNULL)
+        ro = np.load(path + ".ro.npy", mmap_mode="r")
+        co = np.load(path + ".co.npy", mmap_mode="r")
+        how = open(path + ".src").read()
+    finally:
+        for ext in (".ro.npy", ".co.npy", ".src"):      # the mappings stay valid after the unlink
+            try:
+                os.unlink(path + ext)
+            except OSError:
+                pass
+    return ro, co, how
+
+
 def run_reference(args, rank, world):
     if rank != 0:
         return
@@ -167,23 +215,12 @@ def run_reference(args, rank, world):
     oracle.build()
     scale = args.scale
     t0 = time.time()
-    graph_source = "oracle generator (CPU)"
-    ro = co = None
-    try:        # input synthesis only: the seeded device generator yields the identical CSR in seconds
-        import gunrockinst_b200 as gr
-        if gr.device_count() > 0:
-            g = gr.Graph.rmat(scale)
-            ro, co = g.download()
-            g.close()
-            graph_source = "device generator (input synthesis only; same seeded CSR as oracle.rmat_csr)"
-    except Exception:
-        ro = None
-    if ro is None:
-        ro, co = oracle.rmat_csr(scale)
+    ro, co, graph_source = load_synthetic_csr(scale)
     sources = pick_sources(ro, N_SOURCES, 1234 + scale)
     sampler = oracle.BfsSampler(ro, co)
-    # bounded sample: each step scans at most `cap` neighbour entries of the search
-    cap = args.ref_edge_cap
+    # whole searches where one takes well under a second (scale <= 24); above that a bounded sample: each
+    # step scans at most `cap` neighbour entries of the search, and the line says which fraction that is
+    cap = args.ref_edge_cap if args.ref_edge_cap >= 0 else (0 if scale <= 24 else 50_000_000)
     for i in range(args.warmup):
         sampler.run(sources[i % len(sources)], cap)
     edges = 0
@@ -193,7 +230,12 @@ def run_reference(args, rank, world):
         edges += e
         secs += t
     value = edges / secs / 1e9 if secs > 0 else 0.0
-    sample = "first <= %d scanned neighbour entries of each of %d searches (serial FIFO BFS)" % (cap, args.steps)
+    if cap:
+        sample = "first <= %d scanned neighbour entries of each of %d searches (serial FIFO BFS)" % (cap, args.steps)
+        fraction = min(1.0, cap / max(int(co.size), 1))
+    else:
+        sample = "%d complete searches (serial FIFO BFS, tests/bfs/test_bfs.cu:258-322 restated in oracle/oracle.c)" % args.steps
+        fraction = 1.0
     line = {
         "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * secs / max(args.steps, 1),
@@ -201,6 +243,7 @@ def run_reference(args, rank, world):
         "dtype": "int32", "data": "synthetic",
         "config": workload_config(args, scale, int(ro.size - 1), int(co.size)),
         "cpu_baseline": {"value": value, "unit": UNIT, "cores": 1, "kind": "port", "sample": sample,
+                         "sample_fraction": fraction, "step_is_a_whole_search": not cap,
                          "cores_available": os.cpu_count(), "graph_source": graph_source},
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0, "setup_s": round(time.time() - t0 - secs, 2),
@@ -218,6 +261,120 @@ def workload_config(args, scale, nodes, edges):
             "rmat_abcd": [0.55, 0.2, 0.2, 0.05], "seed": 42 + scale, "sources": N_SOURCES,
             "l2_policy": "inputs larger than L2 (CSR %.2f GB vs 126 MB L2); labels/bitmaps are re-initialised "
                          "every step" % ((4.0 * edges + 4.0 * nodes) / 1e9)}
+
+
+# ----------------------------------------------------------------------------------------
+# the other single-device BASELINE configs at full size, each checked against the oracle
+# ----------------------------------------------------------------------------------------
+def run_full_size_configs(args, peak):
+    """-> {"s25": {"dobfs": .., "topdown": ..}, "c3_sssp_s24": .., "c4_cc_s25": .., "c4_pr_s25": ..}: device time
+    (CUDA events inside the library, best of 3), throughput, algorithmic bytes over that time against the measured HBM
+    peak, and `parity` against the CPU oracle on the identical CSR (test infrastructure: the checker only)."""
+    import numpy as np
+    import gunrockinst_b200 as gr
+    out = {}
+    check = not args.no_cpu
+
+    def guarded(name, fn):
+        t0 = time.time()
+        try:
+            rec = fn()
+        except Exception as exc:            # never lose the headline over an extra record
+            rec = {"error": "%s: %s" % (type(exc).__name__, str(exc)[:300])}
+        rec["wall_s"] = round(time.time() - t0, 1)
+        out[name] = rec
+
+    def best(run, reps=3):
+        top = None
+        for _ in range(reps):
+            r = run()
+            if top is None or r[-1]["elapsed_ms"] < top[-1]["elapsed_ms"]:
+                top = r
+        return top
+
+    def rate(st, ms):
+        return {"ms": ms, "algo_gbs": st["algo_bytes"] / ms / 1e6, "roofline_frac": st["algo_bytes"] / ms / 1e6 / peak}
+
+    # ---- R-MAT scale 25: BFS (north star), CC and PageRank (configs[3]) share one graph ----------------------------
+    g25 = ro = co = None
+    try:
+        g25 = gr.Graph.rmat(25)
+        if check:
+            import oracle
+            oracle.build()
+            ro, co = g25.download()
+    except Exception as exc:
+        out["s25"] = {"error": str(exc)[:300]}
+
+    def bfs25():
+        rec = {"graph": {"nodes": g25.nodes, "directed_edges": g25.edges}, "source": 0,
+               "layout": "degree-ordered twin of the graph (grb_bfs_config.degree_order); labels in the caller's ids"}
+        want = oracle.bfs(ro, co, 0) if check else None
+        for key, mode in (("dobfs", dict(direction_optimized=True, degree_order=True)),
+                          ("topdown", dict(traversal_mode=1, host_loop=1, degree_order=True))):
+            b = gr.Bfs(g25, **mode)
+            labels, _, _ = b.run(0)
+            _, _, st = best(lambda: b.run(0, want_labels=False))
+            r = rate(st, st["elapsed_ms"])
+            r.update(gteps=st["edges_visited"] / st["elapsed_ms"] / 1e6, edges_inspected=st["edges_inspected"],
+                     levels=[st["push_levels"], st["pull_levels"]], gpu_launches=st["gpu_launches"],
+                     parity=(bool(np.array_equal(labels, want)) if check else None))
+            rec[key] = r
+            b.close()
+        return rec
+
+    def cc25():
+        gr.cc(g25)
+        labels, k, st = best(lambda: gr.cc(g25))
+        r = rate(st, st["elapsed_ms"])
+        r.update(components=int(k), gpu_launches=st["gpu_launches"])
+        if check:
+            want, ncomp = oracle.cc(ro, co)
+            r["parity"] = bool(np.array_equal(labels, want) and k == ncomp)
+        return r
+
+    def pr25():
+        gr.pagerank(g25, max_iter=2)
+        ranks, _, st = gr.pagerank(g25, delta=0.85, threshold=1e-6, max_iter=1000)
+        r = rate(st, st["elapsed_ms"])
+        r.update(sweeps=st["iterations"], ms_per_sweep=st["elapsed_ms"] / max(st["iterations"], 1),
+                 rank_sum=float(ranks.sum()), rank_max=float(ranks.max()),
+                 parity_note="PageRank is unpinned by the reference's own tests (stale golden, SURVEY.md section 4); "
+                             "checked against the fp64 restatement of its functors: per-vertex 1e-6 after 5 sweeps here, "
+                             "to convergence at scale 22 in tests/test_pr_gpu.py")
+        if check:
+            got, _, _ = gr.pagerank(g25, delta=0.85, threshold=1e-6, max_iter=5)
+            want = oracle.pagerank(ro, co, 0.85, 1e-6, 5, -1)[0]
+            err = np.abs(got - want)
+            r["max_abs_diff_after_5_sweeps"] = float(err.max())
+            r["parity"] = bool(np.all(err <= 1e-6 * np.maximum(1.0, np.abs(want))))
+        return r
+
+    if g25 is not None:
+        guarded("s25", bfs25)
+        guarded("c4_cc_s25", cc25)
+        guarded("c4_pr_s25", pr25)
+        g25.close()
+        ro = co = None
+        gr.release_cached_memory()
+
+    def sssp24():
+        g = gr.Graph.rmat(24, weight_seed=7)
+        gr.sssp(g, 0)
+        dist, _, st = best(lambda: gr.sssp(g, 0))
+        r = rate(st, st["elapsed_ms"])
+        r.update(graph={"nodes": g.nodes, "directed_edges": g.edges, "weights": "symmetric uint32 1..64"},
+                 iterations=st["iterations"], relaxations=st["edges_inspected"])
+        if check:
+            r2, c2, w2 = g.download(want_weights=True)
+            want, _ = oracle.sssp(r2, c2, w2, 0)
+            r["parity"] = bool(np.array_equal(dist, want))
+        g.close()
+        return r
+
+    guarded("c3_sssp_s24", sssp24)
+    gr.release_cached_memory()
+    return out
 
 
 # ----------------------------------------------------------------------------------------
@@ -394,6 +551,11 @@ def run_single(args):
     }
     bfs.close()
     g.close()
+    if not args.no_configs:
+        gr.release_cached_memory()
+        t_cfg = time.time()
+        line["configs"] = run_full_size_configs(args, peak)
+        line["configs"]["wall_s"] = round(time.time() - t_cfg, 1)
     print(json.dumps(line), flush=True)
 
 
@@ -406,13 +568,22 @@ def main():
     ap.add_argument("--scale", type=int, default=0, help="R-MAT scale (default: 22 on one device, 27 partitioned)")
     ap.add_argument("--e2e-steps", type=int, default=8)
     ap.add_argument("--cpu-seconds", type=float, default=12.0)
-    ap.add_argument("--ref-edge-cap", type=int, default=20_000_000)
+    ap.add_argument("--ref-edge-cap", type=int, default=-1,
+                    help="reference arm: scan at most this many neighbour entries per step (0: whole searches; "
+                         "default: whole searches up to scale 24, 50 M entries above)")
+    ap.add_argument("--synthesize", nargs=2, metavar=("SCALE", "PATH"), help=argparse.SUPPRESS)
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--no-configs", action="store_true",
+                    help="skip the full-size records of the other single-device BASELINE configs (scale-25 BFS / CC / "
+                         "PageRank, scale-24 SSSP, each with its oracle check: several minutes)")
     ap.add_argument("--exchange", default="peer", choices=["peer", "nccl"],
                     help="partitioned runs: peer-memory stores over NVLink (default) or NCCL collectives")
     ap.add_argument("--partitioned", action="store_true",
                     help="use the partitioned driver even on one device (the 1-device point of a scale-27 scaling table)")
     args = ap.parse_args()
+    if args.synthesize:
+        synthesize(int(args.synthesize[0]), args.synthesize[1])
+        return
     world = env_int("WORLD_SIZE", 1)
     rank = env_int("RANK", 0)
     if world > 1:

@@ -29,6 +29,11 @@ def version():
     return _capi.lib().grb_version().decode()
 
 
+def release_cached_memory():
+    """hand the library's cached device / pinned blocks back to the driver (grb_release_cached_memory)"""
+    _capi.lib().grb_release_cached_memory()
+
+
 def device_count():
     return int(_capi.lib().grb_device_count())
 

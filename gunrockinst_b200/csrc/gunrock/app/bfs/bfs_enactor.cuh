@@ -38,6 +38,7 @@
 #include <cstdio>
 #include "bfs_functor.cuh"
 #include "../enactor_base.cuh"
+#include "../../graph/build.cuh"
 #include "bfs_persistent.cuh"
 
 namespace gunrock {
@@ -143,6 +144,7 @@ class BFSEnactor : public EnactorBase {
     typedef oprtr::advance::KernelPolicy<Problem, 1024, 4, 1, true, false>  IdemStreamPolicy;
     // reference: END_BITMASK_CULL = 5 (bfs_enactor.cuh:594); the word-atomic mask stays exact, so keep it on
     typedef oprtr::filter::KernelPolicy<Problem, 256, GRB_FILTER_IPT, GRB_FILTER_CTAS, -1> FilterPolicy;
+    typedef oprtr::filter::KernelPolicy<Problem, 1024, 4, 1, -1> StreamFilterPolicy;   // filter/stream_kernel.cuh
 
     oprtr::advance::LbScratch<SizeT> lb_scratch;
     std::vector<LevelRecord> levels;
@@ -208,17 +210,38 @@ class BFSEnactor : public EnactorBase {
         levels.clear();
         edges_visited = 0;
         if (src < 0 || (long long)src >= problem->graph->nodes) return cudaSuccess;
-        if constexpr (Problem::ENABLE_IDEMPOTENCE) return EnactIdempotent(problem, opt);
-        else {
+        if constexpr (Problem::ENABLE_IDEMPOTENCE) {
+            GR_TRY(EnactIdempotent(problem, opt));
+            return GatherToCallerIds(problem);
+        } else {
             if (sources && count > 0) {
                 if (!reset_on_device)
                     return util::GRError(cudaErrorInvalidValue, "BFSEnactor: a batch needs the device-side reset",
                                          __FILE__, __LINE__);
                 return EnactPersistentMany(problem, sources, count, opt, summaries);
             }
-            return (opt.host_loop || !persistent_ok) ? EnactFused(problem, opt)
-                                                     : EnactPersistent(problem, opt, reset_on_device);
+            if (opt.host_loop || !persistent_ok) {
+                GR_TRY(EnactFused(problem, opt));
+                return GatherToCallerIds(problem);
+            }
+            return EnactPersistent(problem, opt, reset_on_device);
         }
+    }
+
+    // degree-ordered twin, host-driven loops: the result in the caller's vertex ids (the persistent kernel
+    // ends every search with the same gather)
+    cudaError_t GatherToCallerIds(Problem *problem)
+    {
+        if (!problem->src_map) return cudaSuccess;
+        const long long n = problem->graph->nodes;
+        if (n == 0) return cudaSuccess;
+        graph::GatherThroughKernel<false><<<util::FillGrid((unsigned long long)n), 256, 0, stream>>>(
+            problem->labels.ptr, problem->src_map, problem->dst_map, n, problem->out_labels.ptr);
+        if (Problem::MARK_PREDECESSORS)
+            graph::GatherThroughKernel<true><<<util::FillGrid((unsigned long long)n), 256, 0, stream>>>(
+                problem->preds.ptr, problem->src_map, problem->dst_map, n, problem->out_preds.ptr);
+        ++enactor_stats.launches;
+        return util::GRError(cudaGetLastError(), "GatherThroughKernel failed", __FILE__, __LINE__);
     }
 
     // recount edges_visited from the labels (idempotent mode cannot track it: duplicates)
@@ -350,6 +373,9 @@ class BFSEnactor : public EnactorBase {
         P.sources = many_count ? d_sources.ptr : nullptr;
         P.num_sources = many_count;
         P.src_map = many_count ? problem->src_map : nullptr;
+        P.to_new = problem->src_map; P.to_old = problem->dst_map;
+        P.out_labels = problem->src_map ? problem->out_labels.ptr : nullptr;
+        P.out_preds = (problem->src_map && Problem::MARK_PREDECESSORS) ? problem->out_preds.ptr : nullptr;
         P.do_reset = reset_on_device ? 1 : 0;
         P.mask_words = (unsigned long long)problem->visited_mask.size;
         P.can_pull = can_pull ? 1 : 0;
@@ -376,7 +402,8 @@ class BFSEnactor : public EnactorBase {
             if (many_count) return cudaErrorCooperativeLaunchTooLarge;      // the caller re-runs the batch search by search
             if (reset_on_device) GR_TRY(problem->FillState(problem->src));
             GR_TRY(ResetBase());
-            return EnactFused(problem, opt);
+            GR_TRY(EnactFused(problem, opt));
+            return GatherToCallerIds(problem);
         }
         enactor_stats.launches = 1;
         GR_TRY(cudaMemcpyAsync(h_summary.ptr, d_summary.ptr, sizeof(PersistentSummary) * (size_t)searches,
@@ -593,7 +620,18 @@ class BFSEnactor : public EnactorBase {
             fa.queue_index = frontier_attribute.queue_index;
             fa.iteration = level + 1;
             fa.compact = true;
-            GR_TRY((oprtr::filter::LaunchKernel<FilterPolicy, Problem, BfsFunctor>(dev.sm_count, ds, fa, stream)));
+            bool filter_streamed = false;
+            if constexpr (Problem::ENABLE_IDEMPOTENCE && !Problem::MARK_PREDECESSORS) {
+                if (streamed && oprtr::filter::StreamEligible<StreamFilterPolicy, Problem>(fa, g.part.log_parts)) {
+                    filter_streamed = true;
+                    const unsigned long long words = (unsigned long long)((g.nodes + 31) / 32);
+                    const unsigned cap = oprtr::filter::StreamMaxHotWords<StreamFilterPolicy>();
+                    GR_TRY((oprtr::filter::LaunchStreamKernel<StreamFilterPolicy, Problem, BfsFunctor>(
+                        dev.sm_count, ds, fa, (unsigned)(words < cap ? words : cap), stream)));
+                }
+            }
+            if (!filter_streamed)
+                GR_TRY((oprtr::filter::LaunchKernel<FilterPolicy, Problem, BfsFunctor>(dev.sm_count, ds, fa, stream)));
             if (opt.record_levels) GR_TRY(cudaEventRecord(ev_c, stream));
             // one fetch covers both slots (advance wrote queue_index, filter queue_index + 1)
             oprtr::LevelCounters ca, cf;
@@ -613,7 +651,7 @@ class BFSEnactor : public EnactorBase {
                 LevelRecord ra, rf;
                 ra.level = level; ra.pull = streamed ? 5 : (mode == oprtr::advance::LB) ? 2 : 0;
                 ra.frontier = F; ra.edges = ca.edges; ra.discovered = ca.out_len; ra.candidates = 0; ra.switch_ms = 0;
-                rf.level = level; rf.pull = 4;
+                rf.level = level; rf.pull = filter_streamed ? 6 : 4;
                 rf.frontier = ca.out_len; rf.edges = 0; rf.discovered = cf.out_len; rf.candidates = 0; rf.switch_ms = 0;
                 GR_TRY(cudaEventElapsedTime(&ra.ms, ev_a, ev_b));
                 GR_TRY(cudaEventElapsedTime(&rf.ms, ev_b, ev_c));

@@ -29,6 +29,15 @@ struct BFSFunctor {
         return util::BitTestAndSet(problem->d_visited_mask, problem->BitPos(d_id));
     }
 
+    // optional fifth member, used by the streaming advance: == active && CondEdge(...), with the claim issued
+    // under a predicate so that the claims of a thread's entries overlap (util::AtomicOrIf)
+    static __device__ __forceinline__ bool CondEdgeIf(
+        bool active, VertexId s_id, VertexId d_id, const DataSlice *problem, SizeT e_id = 0, SizeT e_id_in = 0)
+    {
+        if (ProblemData::ENABLE_IDEMPOTENCE) return active;
+        return util::BitTestAndSetIf(active, problem->d_visited_mask, problem->BitPos(d_id));
+    }
+
     // the edge won `d_id`: record depth (and parent)
     static __device__ __forceinline__ void ApplyEdge(
         VertexId s_id, VertexId d_id, const DataSlice *problem, SizeT e_id = 0, SizeT e_id_in = 0)

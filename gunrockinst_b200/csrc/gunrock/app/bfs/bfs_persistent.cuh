@@ -69,6 +69,8 @@ struct PersistentParams {
     int      num_sources;                           //     launch (needs do_reset); summary[i] describes search i
     const VertexId *src_map;                        // optional: sources[] are ids of the caller's graph, the graph
                                                     //     here is its degree-ordered twin (src_map[v] = id here)
+    const VertexId *to_new, *to_old;                // twin: every search ends by gathering its labels (and predecessors)
+    VertexId *out_labels, *out_preds;               //     back into the caller's ids (NULL: not a twin)
     int      do_reset;                              // 1: the kernel also does Problem::Reset's device work
     unsigned long long mask_words;                  // words of the visited bitmap (do_reset)
     int      can_pull;
@@ -375,6 +377,18 @@ PersistentKernel(const __grid_constant__ typename Problem::DataSlice ds0,
         ++qi;
         if (pull) cur_map ^= 1; else sel ^= 1;
         ++level;
+    }
+    // degree-ordered twin: the search's result in the caller's vertex ids (every label store of the last
+    // level is behind a grid-wide barrier; the next search's reset is behind the one that ends this search)
+    if (P.out_labels && !aborted) {
+        for (unsigned long long v = gtid; v < n; v += gthreads) {
+            const VertexId t = P.to_new[v];
+            P.out_labels[v] = util::LoadCG(ds.d_labels + t);
+            if constexpr (Problem::MARK_PREDECESSORS) {
+                const VertexId p = util::LoadCG(ds.d_preds + t);
+                P.out_preds[v] = p >= 0 ? P.to_old[p] : p;
+            }
+        }
     }
     if (leader) {
         if (P.summary[si].overflow) sum.overflow = 1;  // raised by the bitmap -> queue conversion

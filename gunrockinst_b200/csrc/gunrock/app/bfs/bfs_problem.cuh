@@ -87,6 +87,18 @@ struct BFSProblem : ProblemBase<_VertexId, _SizeT> {
     // the graph is the degree-ordered twin of the caller's graph: caller's id -> id here (device);
     // applied by the persistent kernel to the sources of a batch (single runs translate on the host)
     const VertexId *src_map = nullptr;
+    // ... and what every search ends with in that case: labels (and predecessors) gathered back into the
+    // caller's ids, out_labels[v] = labels[src_map[v]] (predecessor VALUES translated through dst_map)
+    const VertexId *dst_map = nullptr;
+    util::DeviceArray<VertexId> out_labels, out_preds;
+    cudaError_t SetTwinMaps(const VertexId *to_new, const VertexId *to_old)
+    {
+        src_map = to_new; dst_map = to_old;
+        if (!to_new) return cudaSuccess;
+        GR_TRY(out_labels.Allocate((size_t)this->graph->nodes + 1));
+        if (MARK_PREDECESSORS) GR_TRY(out_preds.Allocate((size_t)this->graph->nodes + 1));
+        return cudaSuccess;
+    }
     unsigned long long src_degree = 0;
     VertexId src = 0;
 

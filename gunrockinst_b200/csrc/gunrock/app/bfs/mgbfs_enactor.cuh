@@ -295,7 +295,8 @@ class MGBFSEnactor : public EnactorBase {
     {
         ++epoch;
         *h_status.ptr = 0;
-        ExchangeCountersKernel<<<1, 32 * kMaxPeers, 0, stream>>>(peers, Counters(), epoch, h_all.ptr, h_status.ptr);
+        ExchangeCountersKernel<<<1, 32 * kMaxPeers, 0, stream>>>(peers, Counters(), epoch, h_all.ptr, h_status.ptr,
+                                                                 PeerComm::BudgetFromEnv());
         GR_TRY(cudaGetLastError());
         ++enactor_stats.launches;
         // the kernel's last store is the status word in pinned host memory: polling it spares the
@@ -319,7 +320,7 @@ class MGBFSEnactor : public EnactorBase {
     {
         if (peers.parts == 1) return cudaSuccess;
         ++bar_count;
-        PeerBarrierKernel<<<1, 32 * kMaxPeers, 0, stream>>>(peers, bar_count);
+        PeerBarrierKernel<<<1, 32 * kMaxPeers, 0, stream>>>(peers, bar_count, PeerComm::BudgetFromEnv());
         ++enactor_stats.launches;
         return cudaGetLastError();
     }

@@ -25,6 +25,7 @@
 // waiter reads flags with acquire loads and fences before the data is consumed.
 #pragma once
 #include "../../oprtr/work_progress.cuh"
+#include <cstdlib>
 #include "../../util/device_intrinsics.cuh"
 
 namespace gunrock {
@@ -88,7 +89,8 @@ constexpr unsigned long long kWaitBudgetNs = 4000000000ull;      // 4 s
 // `h_all` (pinned host) in rank order.
 static __global__ void __launch_bounds__(32 * kMaxPeers)
 ExchangeCountersKernel(MailboxTable pt, const oprtr::LevelCounters *mine, unsigned long long epoch,
-                       oprtr::LevelCounters *h_all, unsigned long long *h_status)
+                       oprtr::LevelCounters *h_all, unsigned long long *h_status,
+                       unsigned long long budget_ns = kWaitBudgetNs)
 {
     const int p = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int par = (int)(epoch & 1);
@@ -106,7 +108,7 @@ ExchangeCountersKernel(MailboxTable pt, const oprtr::LevelCounters *mine, unsign
         // ... and wait for peer p's post into MY mailbox
         Mailbox *own = pt.mailbox[pt.rank];
         bool ok = true;
-        if (lane == 0) ok = WaitAtLeast(&own->flag[par][p], epoch, kWaitBudgetNs);
+        if (lane == 0) ok = WaitAtLeast(&own->flag[par][p], epoch, budget_ns);
         ok = __shfl_sync(0xffffffffu, ok, 0);
         if (!ok) { if (lane == 0) { s_bad = 1; own->timed_out = epoch; } }
         __threadfence_system();
@@ -115,20 +117,27 @@ ExchangeCountersKernel(MailboxTable pt, const oprtr::LevelCounters *mine, unsign
             *reinterpret_cast<const volatile unsigned long long *>(got + lane);
     }
     __syncthreads();
-    if (threadIdx.x == 0) { __threadfence_system(); *h_status = s_bad ? ~0ull : epoch; }
+    // a mid-level barrier (PeerBarrierKernel) that gave up earlier in this level left its mark in the own
+    // mailbox: the level's data may be incomplete, so the exchange that ends the level reports it to the
+    // host -- the mark is sticky, the context stays failed
+    if (threadIdx.x == 0) {
+        const bool late = *reinterpret_cast<const volatile unsigned long long *>(&pt.mailbox[pt.rank]->timed_out) != 0;
+        __threadfence_system();
+        *h_status = (s_bad || late) ? ~0ull : epoch;
+    }
 }
 
 // barrier in the middle of a level (between "scatter my discoveries" and "absorb what I
 // received"): bump my count in every mailbox, wait until every sender's count reached `count`
 static __global__ void __launch_bounds__(32 * kMaxPeers)
-PeerBarrierKernel(MailboxTable pt, unsigned long long count)
+PeerBarrierKernel(MailboxTable pt, unsigned long long count, unsigned long long budget_ns = kWaitBudgetNs)
 {
     const int p = threadIdx.x >> 5, lane = threadIdx.x & 31;
     if (p < pt.parts && lane == 0) {
         __threadfence_system();
         StoreReleaseSys(&pt.mailbox[p]->bar[pt.rank], count);
         Mailbox *own = pt.mailbox[pt.rank];
-        if (!WaitAtLeast(&own->bar[p], count, kWaitBudgetNs)) own->timed_out = count;
+        if (!WaitAtLeast(&own->bar[p], count, budget_ns)) own->timed_out = count;
         __threadfence_system();
     }
 }
@@ -213,10 +222,19 @@ struct PeerComm {
     util::PinnedArray<oprtr::LevelCounters> h_all;
     util::PinnedArray<unsigned long long> h_status;
     unsigned long long epoch = 0, bar_count = 0;
+    unsigned long long budget_ns = kWaitBudgetNs;       // GRB_PEER_TIMEOUT_MS overrides (tests)
     bool ready = false;
+
+    static unsigned long long BudgetFromEnv()
+    {
+        const char *e = getenv("GRB_PEER_TIMEOUT_MS");
+        const long long ms = e ? atoll(e) : 0;
+        return ms > 0 ? (unsigned long long)ms * 1000000ull : kWaitBudgetNs;
+    }
 
     cudaError_t Setup(int parts, int rank, cudaStream_t s)
     {
+        budget_ns = BudgetFromEnv();
         if (parts > kMaxPeers) return util::GRError(cudaErrorInvalidValue, "peer exchange supports up to 8 devices", __FILE__, __LINE__);
         GR_TRY(mailbox.Allocate(1));
         GR_TRY(mailbox.Zero(s));
@@ -234,7 +252,7 @@ struct PeerComm {
     {
         ++epoch;
         *h_status.ptr = 0;
-        ExchangeCountersKernel<<<1, 32 * kMaxPeers, 0, s>>>(table, mine, epoch, h_all.ptr, h_status.ptr);
+        ExchangeCountersKernel<<<1, 32 * kMaxPeers, 0, s>>>(table, mine, epoch, h_all.ptr, h_status.ptr, budget_ns);
         GR_TRY(cudaGetLastError());
         volatile unsigned long long *st = h_status.ptr;
         unsigned long long spins = 0;
@@ -248,8 +266,8 @@ struct PeerComm {
     {
         if (table.parts == 1) return cudaSuccess;
         ++bar_count;
-        PeerBarrierKernel<<<1, 32 * kMaxPeers, 0, s>>>(table, bar_count);
-        return cudaGetLastError();
+        PeerBarrierKernel<<<1, 32 * kMaxPeers, 0, s>>>(table, bar_count, budget_ns);
+        return cudaGetLastError();      // a barrier that gives up is reported by the Exchange that ends the level
     }
 };
 

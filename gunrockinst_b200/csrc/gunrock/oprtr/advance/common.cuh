@@ -116,6 +116,23 @@ __device__ __forceinline__ bool VisitEdge(
     return false;
 }
 
+// active && CondEdge(...): through the functor's optional predicated form (CondEdgeIf) when it has one
+template <typename Functor, typename DataSlice, typename VertexId, typename SizeT, typename = void>
+struct CondEdgeIfImpl {
+    static __device__ __forceinline__ bool Call(bool active, VertexId s, VertexId d, const DataSlice *ds, SizeT e, SizeT e_in)
+    {
+        return active && Functor::CondEdge(s, d, ds, e, e_in);
+    }
+};
+template <typename Functor, typename DataSlice, typename VertexId, typename SizeT>
+struct CondEdgeIfImpl<Functor, DataSlice, VertexId, SizeT,
+                      decltype((void)Functor::CondEdgeIf(true, VertexId(), VertexId(), (const DataSlice *)nullptr, SizeT(), SizeT()), void())> {
+    static __device__ __forceinline__ bool Call(bool active, VertexId s, VertexId d, const DataSlice *ds, SizeT e, SizeT e_in)
+    {
+        return Functor::CondEdgeIf(active, s, d, ds, e, e_in);
+    }
+};
+
 // CTA-wide sum + one atomic into a 64-bit counter (CTA-convergent)
 template <int THREADS>
 __device__ __forceinline__ void BlockAccumulate(unsigned long long v, unsigned long long *scratch, unsigned long long *dst)

@@ -375,15 +375,24 @@ __device__ __forceinline__ void ExpandTilesFromImpl(
             for (int r = 0; r < EPT; ++r)
                 if ((word[r] >> (ds.BitPos(nbr[r]) & 31)) & 1u) live[r] = false;
         }
+        // conditions of the thread's entries first, applications afterwards: the conditions' atomics (a
+        // visited-bit claim, a distance minimum) are independent and overlap instead of each waiting for
+        // the previous entry's answer
+        VertexId s_ids[EPT];
+        bool     oks[EPT];
 #pragma unroll
         for (int r = 0; r < EPT; ++r) {
-            bool ok = false;
+            oks[r] = false;
+            s_ids[r] = (VertexId)args.iteration;
             if (live[r]) {
-                VertexId s_id;
-                if constexpr (NEED_SRC) s_id = windowed ? sm.src[item[r]] : SourceOf(args, i0 + item[r]);
-                else                    s_id = (VertexId)args.iteration;
-                ok = VisitEdge<Policy, Problem, Functor>(&ds, s_id, nbr[r], pos[r], (SizeT)(i0 + item[r]));
+                if constexpr (NEED_SRC) s_ids[r] = windowed ? sm.src[item[r]] : SourceOf(args, i0 + item[r]);
+                oks[r] = Functor::CondEdge(s_ids[r], nbr[r], &ds, pos[r], (SizeT)(i0 + item[r]));
             }
+        }
+#pragma unroll
+        for (int r = 0; r < EPT; ++r) {
+            const bool ok = oks[r];
+            if (ok) Functor::ApplyEdge(s_ids[r], nbr[r], &ds, pos[r], (SizeT)(i0 + item[r]));
             if (args.output == OUT_COMPACT) {
                 stager.Push(ok, OutputIsEdges(args.type) ? (VertexId)pos[r] : nbr[r]);
             } else if (args.output == OUT_TOMBSTONE) {

@@ -26,9 +26,12 @@
 //    228 KB an SM has) answer ~80 % of the probes of an R-MAT scale-25 search and ~97 % at scale
 //    22.  A stale copy is harmless: a clear bit only sends the edge to the exact global claim.
 //
-// One CTA of Policy::THREADS (1024) threads per SM, persistent over its tiles.  Consumers read
-// four ids per LDS.128, probe, claim through the functor and enqueue through a ballot-aggregated
-// shared-memory stager (one global atomic per ~TILE_EDGES discoveries).
+// One CTA of Policy::THREADS (1024) threads per SM, persistent over its tiles, and no CTA-wide
+// barrier inside the tile loop: warps meet only at the ring's mbarriers (`full`: a tile has landed,
+// `empty`: every warp has left a slot), so they drift up to two tiles apart and one warp's L2
+// round trips overlap the others' work.  Consumers read four ids per LDS.128, probe, issue their
+// claims together (the functor's predicated CondEdgeIf) and enqueue through a per-warp
+// shared-memory stage (one global atomic per ~200 discoveries).
 //
 // Restrictions (the launcher falls back to lb::ExpandKernel otherwise): V2V, OUT_COMPACT or
 // OUT_NONE, !Problem::MARK_PREDECESSORS, a functor that ignores e_id / e_id_in, one device.
@@ -41,14 +44,22 @@ namespace oprtr {
 namespace advance {
 namespace lb {
 
+#ifndef GRB_STREAM_COLD_LOAD
+#define GRB_STREAM_COLD_LOAD util::LoadCG   // visited words outside the hot range: read at L2 (fresh: a claim another SM
+#endif                                      // made in this launch is seen; a stale L1 line would cost an atomic per edge)
 constexpr int kStreamStages  = 4;       // tiles in flight per SM
 constexpr int kStreamMinBulk = 64;      // entries; shorter pieces are packed by their warp
+
+constexpr int kStreamAhead   = 2;       // tiles staged ahead of the one being consumed; the other
+                                        // kStreamStages - kStreamAhead slots let warps drift apart
+constexpr int kStreamWarpStage = 256;   // discoveries a warp collects before it enqueues them (one global atomic)
 
 template <typename Policy>
 struct alignas(128) StreamStorage {
     int                   tile[kStreamStages][Policy::TILE_EDGES];
-    StagerStorage<Policy> stager;
-    unsigned long long    full[kStreamStages];          // mbarriers: tile s is complete
+    int                   wstage[Policy::THREADS / 32][kStreamWarpStage];   // per-warp output staging
+    unsigned long long    full[kStreamStages];          // mbarriers: tile in slot s has landed
+    unsigned long long    empty[kStreamStages];         // mbarriers: every warp has left slot s
     unsigned long long    red[Policy::THREADS / 32 + 1];
     unsigned long long    total;
 };
@@ -60,7 +71,7 @@ constexpr unsigned StreamMaxHotWords() { return (unsigned)((232448 - StreamHotOf
 
 template <typename Policy, typename Problem, typename Functor>
 __global__ void __launch_bounds__(Policy::THREADS, 1)
-StreamExpandKernel(const __grid_constant__ typename Problem::DataSlice ds,
+StreamExpandKernel(const __grid_constant__ typename Problem::DataSlice ds_in,
                    const __grid_constant__ Args<typename Policy::VertexId, typename Policy::SizeT> args,
                    const __grid_constant__ LbScratchView<typename Policy::SizeT> scratch,
                    const unsigned hot_words)
@@ -73,6 +84,11 @@ StreamExpandKernel(const __grid_constant__ typename Problem::DataSlice ds,
     static_assert(TILE % (4 * THREADS) == 0, "a thread consumes whole 16-byte groups");
     static_assert(!Problem::MARK_PREDECESSORS, "the streaming advance hands no source vertex to the functor");
     static_assert(sizeof(VertexId) == 4, "tiles hold 32-bit ids");
+
+    // one device (the launcher checks): a compile-time identity partition drops the owner hash and the
+    // owner-major bit positions from the per-edge code (as in pull::Sweep)
+    typename Problem::DataSlice ds = ds_in;
+    if constexpr (HasPartition<typename Problem::DataSlice>::value) ds.part = graph::Partition();
 
     extern __shared__ __align__(128) unsigned char s_raw[];
     StreamStorage<Policy> &sm = *reinterpret_cast<StreamStorage<Policy> *>(s_raw);
@@ -89,9 +105,8 @@ StreamExpandKernel(const __grid_constant__ typename Problem::DataSlice ds,
     }
     if (tid == 0) {
         sm.total = scratch.scanned[in_len];
-        for (int s = 0; s < N; ++s) util::MbarInit(&sm.full[s], THREADS);
+        for (int s = 0; s < N; ++s) { util::MbarInit(&sm.full[s], THREADS); util::MbarInit(&sm.empty[s], THREADS / 32); }
         util::MbarInitFence();
-        sm.stager.count = 0;
     }
     if constexpr (Policy::PRE_CULL) {
         for (unsigned w = tid; w < hot_words; w += THREADS) s_hot[w] = util::LoadCG(ds.d_visited_mask + w);
@@ -105,8 +120,29 @@ StreamExpandKernel(const __grid_constant__ typename Problem::DataSlice ds,
     }
     const long long my_tiles = num_tiles > cta ? (long long)((num_tiles - cta + nctas - 1) / nctas) : 0;
     const VertexId *col = args.g.col_indices;
-    Stager<Policy> stager(sm.stager, args, slot_out);
     unsigned long long my_edges = 0;            // thread 0 only
+    unsigned long long my_degree = 0;           // TRACK_OUT_DEGREE: out-degrees of the vertices this thread enqueued
+    int *wstage = sm.wstage[util::WarpId()];
+    unsigned wcount = 0;                        // warp-uniform: entries in wstage
+    // warp-convergent: the warp's staged discoveries leave for the output frontier as one coalesced run
+    auto flush_warp = [&]() {
+        if (wcount == 0) return;
+        unsigned long long base = 0;
+        if (lane == 0) base = atomicAdd(&slot_out->out_len, (unsigned long long)wcount);
+        base = __shfl_sync(util::kFullMask, base, 0);
+        __syncwarp();
+        for (unsigned k = lane; k < wcount; k += 32) {
+            const VertexId u = wstage[k];
+            if (base + k < args.out_cap) args.out_queue[base + k] = u;
+            else slot_out->overflow = 1;
+            if constexpr (Policy::TRACK_OUT_DEGREE) {
+                const long long row = args.g.part.Local(u);
+                my_degree += (unsigned long long)(args.g.row_offsets[row + 1] - args.g.row_offsets[row]);
+            }
+        }
+        __syncwarp();
+        wcount = 0;
+    };
 
     // ---- staging ---------------------------------------------------------------------------------------
     // items [i0, i0 + cnt) overlap tile k of this CTA
@@ -202,20 +238,26 @@ StreamExpandKernel(const __grid_constant__ typename Problem::DataSlice ds,
                     word[i] = 0;
                     if (live[i])
                         word[i] = ((unsigned)v[i] < hot_bits) ? s_hot[(unsigned)v[i] >> 5]
-                                                              : util::LoadCA(ds.d_visited_mask + (ds.BitPos(v[i]) >> 5));
+                                                              : GRB_STREAM_COLD_LOAD(ds.d_visited_mask + (ds.BitPos(v[i]) >> 5));
                 }
 #pragma unroll
                 for (int i = 0; i < 4; ++i)
                     if ((word[i] >> (ds.BitPos(v[i]) & 31)) & 1u) live[i] = false;
             }
+            // all four conditions first: their claims (one global atomic each in BFS) are independent and
+            // travel together; a thread that waited for each answer before asking the next question spent
+            // four L2 round trips per tile on a level whose frontier discovers most of its neighbours
             bool ok[4];
 #pragma unroll
+            for (int i = 0; i < 4; ++i)
+                ok[i] = CondEdgeIfImpl<Functor, typename Problem::DataSlice, VertexId, SizeT>::Call(
+                    live[i], (VertexId)args.iteration, v[i], &ds, (SizeT)0, (SizeT)0);
+#pragma unroll
             for (int i = 0; i < 4; ++i) {
-                ok[i] = false;
                 if (live[i]) {
-                    ok[i] = VisitEdge<Policy, Problem, Functor>(&ds, (VertexId)args.iteration, v[i], (SizeT)0, (SizeT)0);
                     // claimed now or found claimed: either way nobody in this CTA needs to ask again
                     if (Policy::PRE_CULL && (unsigned)v[i] < hot_bits) atomicOr(s_hot + ((unsigned)v[i] >> 5), 1u << (v[i] & 31));
+                    if (ok[i]) Functor::ApplyEdge((VertexId)args.iteration, v[i], &ds, (SizeT)0, (SizeT)0);
                 }
             }
             if (args.output == OUT_COMPACT) {
@@ -224,44 +266,52 @@ StreamExpandKernel(const __grid_constant__ typename Problem::DataSlice ds,
                 for (int i = 0; i < 4; ++i) bal[i] = __ballot_sync(util::kFullMask, ok[i]);
                 const unsigned tot = __popc(bal[0]) + __popc(bal[1]) + __popc(bal[2]) + __popc(bal[3]);
                 if (tot) {                                          // warp-uniform
-                    unsigned at = 0;
-                    if (lane == 0) at = atomicAdd(&sm.stager.count, tot);
-                    at = __shfl_sync(util::kFullMask, at, 0);
+                    if (wcount + tot > (unsigned)kStreamWarpStage) flush_warp();
                     const unsigned below = (1u << lane) - 1;
+                    unsigned at = wcount;
 #pragma unroll
                     for (int i = 0; i < 4; ++i) {
-                        if (ok[i]) sm.stager.stage[at + __popc(bal[i] & below)] = v[i];
+                        if (ok[i]) wstage[at + __popc(bal[i] & below)] = v[i];
                         at += __popc(bal[i]);
                     }
+                    wcount += tot;
                 }
             }
         }
     };
 
-    // ---- the pipeline: tile k is consumed while tiles k+1 .. k+N-1 are in flight ----------------------------
+    // ---- the pipeline: tile k is consumed while tiles k+1 .. k+AHEAD are in flight.  No CTA-wide barrier inside:
+    // a thread stages its share of tile k+AHEAD once every warp has left the slot's previous tenant (tile
+    // k+AHEAD-N, `empty`), waits for its own tile on `full`, so warps drift up to N-AHEAD tiles apart and one
+    // warp's L2 round trips (cold probes, claims) overlap the others' work. -----------------------------------
+    constexpr int AHEAD = kStreamAhead;
+    static_assert(AHEAD >= 1 && AHEAD < N, "ring depth");
     long long b_i0 = 0, b_cnt = 0, p_i0 = 0, p_cnt = 0;
     ScanT p_s = 0, p_e = 0;
     SizeT p_rs = 0;
-    for (long long ks = 0; ks < N - 1 && ks < my_tiles; ++ks) {
+    for (long long ks = 0; ks < AHEAD && ks < my_tiles; ++ks) {
         load_bounds(ks, p_i0, p_cnt);
         load_piece(p_i0, p_cnt, tid, p_s, p_e, p_rs);
         issue(ks, p_i0, p_cnt, p_s, p_e, p_rs);
     }
-    if (N - 1 < my_tiles) { load_bounds(N - 1, p_i0, p_cnt); load_piece(p_i0, p_cnt, tid, p_s, p_e, p_rs); }
-    if (N < my_tiles) load_bounds(N, b_i0, b_cnt);
+    if (AHEAD < my_tiles) { load_bounds(AHEAD, p_i0, p_cnt); load_piece(p_i0, p_cnt, tid, p_s, p_e, p_rs); }
+    if (AHEAD + 1 < my_tiles) load_bounds(AHEAD + 1, b_i0, b_cnt);
     for (long long k = 0; k < my_tiles; ++k) {
-        __syncthreads();                        // everybody has left tile k-1: its ring slot and the stager count are stable
-        if (args.output == OUT_COMPACT) stager.FlushIfNeededSynced(TILE);
-        const long long ks = k + N - 1;
-        if (ks < my_tiles) issue(ks, p_i0, p_cnt, p_s, p_e, p_rs);
+        const long long ks = k + AHEAD;
+        if (ks < my_tiles) {
+            if (ks >= N) util::MbarWait(&sm.empty[ks % N], (unsigned)(((ks / N) - 1) & 1));
+            issue(ks, p_i0, p_cnt, p_s, p_e, p_rs);
+        }
         if (ks + 1 < my_tiles) { p_i0 = b_i0; p_cnt = b_cnt; load_piece(p_i0, p_cnt, tid, p_s, p_e, p_rs); }
         if (ks + 2 < my_tiles) load_bounds(ks + 2, b_i0, b_cnt);
         util::MbarWait(&sm.full[k % N], (unsigned)((k / N) & 1));
         consume(k);
+        __syncwarp();
+        if (lane == 0) util::MbarArrive(&sm.empty[k % N]);
     }
-    if (args.output == OUT_COMPACT) stager.Flush();
+    if (args.output == OUT_COMPACT) flush_warp();
     BlockAccumulate<THREADS>(my_edges, sm.red, &slot_out->edges);
-    if constexpr (Policy::TRACK_OUT_DEGREE) BlockAccumulate<THREADS>(stager.out_degree, sm.red, &slot_out->out_degree);
+    if constexpr (Policy::TRACK_OUT_DEGREE) BlockAccumulate<THREADS>(my_degree, sm.red, &slot_out->out_degree);
 }
 
 }  // namespace lb

@@ -113,5 +113,23 @@ __device__ __forceinline__ bool BitTestAndSet(unsigned *bitmap, unsigned long lo
     return (old & bit) == 0;
 }
 
+// Predicated forms: the atomic is issued under a predicate instead of inside a branch, so that a thread
+// that claims several bits in a row has all its atomics in flight at once (inside `if` bodies the
+// compiler tests every answer before it issues the next atomic: one L2 round trip per claim).
+// AtomicOrIf: the word before the OR, or `bit` itself (= "was already set") when `p` is false.
+__device__ __forceinline__ unsigned AtomicOrIf(bool p, unsigned *addr, unsigned bit)
+{
+    unsigned old = bit;
+    asm volatile("{\n .reg .pred q;\n setp.ne.u32 q, %3, 0;\n @q atom.global.or.b32 %0, [%1], %2;\n}\n"
+                 : "+r"(old) : "l"(addr), "r"(bit), "r"((unsigned)p) : "memory");
+    return old;
+}
+// true iff `p` and THIS call changed the bit
+__device__ __forceinline__ bool BitTestAndSetIf(bool p, unsigned *bitmap, unsigned long long pos)
+{
+    const unsigned bit = 1u << (pos & 31);
+    return (AtomicOrIf(p, bitmap + (pos >> 5), bit) & bit) == 0;
+}
+
 }  // namespace util
 }  // namespace gunrock

@@ -29,8 +29,6 @@ struct BfsRunner : BfsRunnerBase {
     // degree order: the problem runs on the graph's twin; sources are translated on the way in,
     // labels / predecessors on the way out (lazily: only when somebody asks for them)
     const int *to_new = nullptr, *to_old = nullptr;
-    gunrock::util::DeviceArray<int> out_labels, out_preds;
-    bool out_valid = false;
 
     ~BfsRunner()
     {
@@ -60,7 +58,7 @@ struct BfsRunner : BfsRunnerBase {
             opt.host_loop = cfg->host_loop == 1 || (cfg->host_loop == 0 && g->nodes >= (1ll << 24));
         }
         GR_TRY(problem.Init(g, s));
-        problem.src_map = to_new;
+        GR_TRY(problem.SetTwinMaps(to_new, to_old));
         GR_TRY(cudaEventCreate(&e0)); GR_TRY(cudaEventCreate(&e1)); GR_TRY(cudaEventCreate(&e2));
         return cudaSuccess;
     }
@@ -69,7 +67,6 @@ struct BfsRunner : BfsRunnerBase {
     {
         using gunrock::app::VERTEX_FRONTIERS;
         using gunrock::app::EDGE_FRONTIERS;
-        out_valid = false;
         if (to_new && src >= 0 && (long long)src < problem.graph->nodes) {      // the twin's id of the source
             GR_TRY(cudaMemcpyAsync(&src, to_new + src, sizeof(int), cudaMemcpyDeviceToHost, stream));
             GR_TRY(cudaStreamSynchronize(stream));
@@ -102,34 +99,14 @@ struct BfsRunner : BfsRunnerBase {
         }
         return cudaSuccess;
     }
-    // labels (and predecessors) in the caller's vertex ids, on the device
-    cudaError_t Untwin()
-    {
-        if (!to_new || out_valid) return cudaSuccess;
-        const long long n = problem.graph->nodes;
-        GR_TRY(out_labels.Allocate((size_t)n + 1));
-        if (n) {
-            gunrock::graph::GatherThroughKernel<false><<<gunrock::util::FillGrid((unsigned long long)n), 256, 0, stream>>>(
-                problem.labels.ptr, to_new, to_old, n, out_labels.ptr);
-            GR_TRY(cudaGetLastError());
-            if (MARK_PRED) {
-                GR_TRY(out_preds.Allocate((size_t)n + 1));
-                gunrock::graph::GatherThroughKernel<true><<<gunrock::util::FillGrid((unsigned long long)n), 256, 0, stream>>>(
-                    problem.preds.ptr, to_new, to_old, n, out_preds.ptr);
-                GR_TRY(cudaGetLastError());
-            }
-        }
-        out_valid = true;
-        return cudaSuccess;
-    }
-    // reference: BFSProblem::Extract (bfs_problem.cuh:144-177)
+    // reference: BFSProblem::Extract (bfs_problem.cuh:144-177); on a twin the search itself ended with the
+    // gather into the caller's ids (bfs_enactor.cuh / bfs_persistent.cuh)
     cudaError_t Extract(int *labels_host, int *preds_host)
     {
         if (!to_new) return problem.Extract(labels_host, preds_host);
-        GR_TRY(Untwin());
         const size_t n = (size_t)problem.graph->nodes;
-        GR_TRY(out_labels.ToHost(labels_host, n, stream));
-        if (MARK_PRED && preds_host) GR_TRY(out_preds.ToHost(preds_host, n, stream));
+        GR_TRY(problem.out_labels.ToHost(labels_host, n, stream));
+        if (MARK_PRED && preds_host) GR_TRY(problem.out_preds.ToHost(preds_host, n, stream));
         return cudaStreamSynchronize(stream);
     }
     // `count` searches; when the persistent kernel can take them, batches of up to kBatch sources run
@@ -143,8 +120,7 @@ struct BfsRunner : BfsRunnerBase {
             bool batch = ready && !IDEM && !opt.record_levels && count - done > 1;
             int take = count - done < kBatch ? count - done : kBatch;
             for (int i = 0; batch && i < take; ++i) batch = enactor.FusesReset(srcs[done + i], &problem, opt);
-            out_valid = false;
-            if (!batch) {
+                if (!batch) {
                 GR_TRY(Run(srcs[done], nullptr, nullptr, stats ? stats + done : nullptr));
                 ++done;
                 continue;
@@ -176,12 +152,7 @@ struct BfsRunner : BfsRunnerBase {
         }
         return cudaSuccess;
     }
-    void *DeviceLabels() override
-    {
-        if (!to_new) return problem.labels.ptr;
-        if (Untwin() != cudaSuccess || cudaStreamSynchronize(stream) != cudaSuccess) return nullptr;
-        return out_labels.ptr;
-    }
+    void *DeviceLabels() override { return to_new ? problem.out_labels.ptr : problem.labels.ptr; }
     const std::vector<gunrock::app::bfs::LevelRecord> &Levels() override { return enactor.levels; }
 };
 

@@ -350,7 +350,8 @@ def test_streaming_advance_matches_oracle(gr, orc, scale, mode):
         if not mode.get("idempotence") and not mode.get("direction_optimized"):
             # a top-down search inspects every entry of the visited rows exactly once
             assert sum(r["edges"] for r in lv) == st["edges_visited"]
-    assert streamed > 0, mode
+    if scale >= 16 or mode.get("traversal_mode") == 1:          # small graphs: only the LB-always modes reach the LB levels
+        assert streamed > 0, mode
     bfs.close()
     g.close()
 

@@ -188,7 +188,7 @@ class Bfs:
         _capi.check(L.grb_bfs_levels(self._h, None, 0, C.byref(cnt)), "grb_bfs_levels")
         arr = (LevelRecord * max(cnt.value, 1))()
         _capi.check(L.grb_bfs_levels(self._h, arr, cnt.value, C.byref(cnt)), "grb_bfs_levels")
-        kinds = {0: "push-twc", 1: "pull", 2: "push-lb", 3: "push-small", 4: "filter", 5: "push-stream"}
+        kinds = {0: "push-twc", 1: "pull", 2: "push-lb", 3: "push-small", 4: "filter", 5: "push-stream", 6: "filter-stream"}
         return [dict(level=r.level, kind=kinds.get(r.kind, str(r.kind)), frontier=r.frontier, edges=r.edges,
                      discovered=r.discovered, candidates=r.candidates, ms=r.ms, switch_ms=r.switch_ms) for r in arr[:cnt.value]]
 

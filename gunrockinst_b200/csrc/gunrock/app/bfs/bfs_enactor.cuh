@@ -139,12 +139,10 @@ class BFSEnactor : public EnactorBase {
     typedef oprtr::advance::KernelPolicy<Problem, 256, 4, GRB_LB_CTAS, true, true>   AdvancePolicy;
     typedef oprtr::advance::KernelPolicy<Problem, 256, 4, 5, true, false>  IdemAdvancePolicy;
     typedef oprtr::advance::KernelPolicy<Problem, 256, 4, GRB_PULL_CTAS, false, false> PullPolicy;
-    // streaming advance: one 1024-thread CTA per SM, tiles of 4096 entries staged in shared memory
-    typedef oprtr::advance::KernelPolicy<Problem, 1024, 4, 1, true, true>   StreamPolicy;
-    typedef oprtr::advance::KernelPolicy<Problem, 1024, 4, 1, true, false>  IdemStreamPolicy;
+    // streaming advance (lb_stream.cuh): one 1024-thread CTA per SM, 8 producer + 24 consumer warps, 6144-entry tiles
+    typedef oprtr::advance::KernelPolicy<Problem, 1024, 6, 1, true, true>   StreamPolicy;
     // reference: END_BITMASK_CULL = 5 (bfs_enactor.cuh:594); the word-atomic mask stays exact, so keep it on
     typedef oprtr::filter::KernelPolicy<Problem, 256, GRB_FILTER_IPT, GRB_FILTER_CTAS, -1> FilterPolicy;
-    typedef oprtr::filter::KernelPolicy<Problem, 1024, 4, 1, -1> StreamFilterPolicy;   // filter/stream_kernel.cuh
 
     oprtr::advance::LbScratch<SizeT> lb_scratch;
     std::vector<LevelRecord> levels;
@@ -508,9 +506,11 @@ class BFSEnactor : public EnactorBase {
                 if constexpr (!Problem::MARK_PREDECESSORS) {
                     AdvArgs a = PushArgs(problem, level);
                     if (mode == oprtr::advance::LB && opt.stream_min_edges && frontier_edges >= opt.stream_min_edges &&
+                        (frontier_edges >= 8ull * F || opt.stream_min_edges <= 2) &&      // lists of ~1 entry: a warp per 32 items is latency
                         oprtr::advance::StreamEligible<StreamPolicy, Problem>(a)) {
                         kind = 5;
                         streamed = true;
+                        ++enactor_stats.launches;          // scan + expand + harvest
                         GR_TRY((oprtr::advance::LaunchStreamKernel<StreamPolicy, Problem, BfsFunctor>(
                             dev, ds, a, &lb_scratch, frontier_edges, HotWords<StreamPolicy>(problem), stream)));
                     }
@@ -592,18 +592,8 @@ class BFSEnactor : public EnactorBase {
                                          (level == 0 && problem->src_degree >= opt.lb_min_edges)) ? oprtr::advance::LB
                                       : oprtr::advance::TWC_FORWARD;
             if (opt.record_levels) GR_TRY(cudaEventRecord(ev_a, stream));
-            bool streamed = false;
-            if constexpr (!Problem::MARK_PREDECESSORS) {
-                if (mode == oprtr::advance::LB && opt.stream_min_edges && F >= (opt.stream_min_edges >> 4) &&
-                    oprtr::advance::StreamEligible<IdemStreamPolicy, Problem>(a)) {
-                    streamed = true;
-                    GR_TRY((oprtr::advance::LaunchStreamKernel<IdemStreamPolicy, Problem, BfsFunctor>(
-                        dev, ds, a, &lb_scratch, (unsigned long long)g.edges, HotWords<IdemStreamPolicy>(problem), stream)));
-                }
-            }
-            if (!streamed)
-                GR_TRY((oprtr::advance::LaunchKernel<IdemAdvancePolicy, Problem, BfsFunctor>(
-                    mode, dev, ds, a, &lb_scratch, (unsigned long long)g.edges, stream)));
+            GR_TRY((oprtr::advance::LaunchKernel<IdemAdvancePolicy, Problem, BfsFunctor>(
+                mode, dev, ds, a, &lb_scratch, (unsigned long long)g.edges, stream)));
             if (opt.record_levels) GR_TRY(cudaEventRecord(ev_b, stream));
             enactor_stats.launches += (mode == oprtr::advance::LB) ? 3 : 2;
             frontier_attribute.queue_index++;
@@ -620,18 +610,7 @@ class BFSEnactor : public EnactorBase {
             fa.queue_index = frontier_attribute.queue_index;
             fa.iteration = level + 1;
             fa.compact = true;
-            bool filter_streamed = false;
-            if constexpr (Problem::ENABLE_IDEMPOTENCE && !Problem::MARK_PREDECESSORS) {
-                if (streamed && oprtr::filter::StreamEligible<StreamFilterPolicy, Problem>(fa, g.part.log_parts)) {
-                    filter_streamed = true;
-                    const unsigned long long words = (unsigned long long)((g.nodes + 31) / 32);
-                    const unsigned cap = oprtr::filter::StreamMaxHotWords<StreamFilterPolicy>();
-                    GR_TRY((oprtr::filter::LaunchStreamKernel<StreamFilterPolicy, Problem, BfsFunctor>(
-                        dev.sm_count, ds, fa, (unsigned)(words < cap ? words : cap), stream)));
-                }
-            }
-            if (!filter_streamed)
-                GR_TRY((oprtr::filter::LaunchKernel<FilterPolicy, Problem, BfsFunctor>(dev.sm_count, ds, fa, stream)));
+            GR_TRY((oprtr::filter::LaunchKernel<FilterPolicy, Problem, BfsFunctor>(dev.sm_count, ds, fa, stream)));
             if (opt.record_levels) GR_TRY(cudaEventRecord(ev_c, stream));
             // one fetch covers both slots (advance wrote queue_index, filter queue_index + 1)
             oprtr::LevelCounters ca, cf;
@@ -649,9 +628,9 @@ class BFSEnactor : public EnactorBase {
                 // two records per level: the advance (every neighbour emitted) and the filter that culls and
                 // compacts them (kind 4: frontier = items read, discovered = items kept)
                 LevelRecord ra, rf;
-                ra.level = level; ra.pull = streamed ? 5 : (mode == oprtr::advance::LB) ? 2 : 0;
+                ra.level = level; ra.pull = (mode == oprtr::advance::LB) ? 2 : 0;
                 ra.frontier = F; ra.edges = ca.edges; ra.discovered = ca.out_len; ra.candidates = 0; ra.switch_ms = 0;
-                rf.level = level; rf.pull = filter_streamed ? 6 : 4;
+                rf.level = level; rf.pull = 4;
                 rf.frontier = ca.out_len; rf.edges = 0; rf.discovered = cf.out_len; rf.candidates = 0; rf.switch_ms = 0;
                 GR_TRY(cudaEventElapsedTime(&ra.ms, ev_a, ev_b));
                 GR_TRY(cudaEventElapsedTime(&rf.ms, ev_b, ev_c));

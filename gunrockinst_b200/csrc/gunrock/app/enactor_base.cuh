@@ -9,7 +9,6 @@
 #pragma once
 #include "../oprtr/advance/kernel.cuh"
 #include "../oprtr/filter/kernel.cuh"
-#include "../oprtr/filter/stream_kernel.cuh"
 
 namespace gunrock {
 namespace app {

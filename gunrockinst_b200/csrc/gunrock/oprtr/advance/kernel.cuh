@@ -75,13 +75,13 @@ cudaError_t LaunchKernel(
 }
 
 // The streaming instance of the LB mode (lb_stream.cuh): same scan, then one 1024-thread CTA per SM
-// that stages neighbour-list tiles in shared memory through TMA / cp.async and probes the hot part
-// of the visited map there.  Policy::THREADS must be 1024; callers check StreamEligible first.
+// whose producer warps stage dense neighbour-id tiles in shared memory through TMA / cp.async and whose
+// consumer warps probe the hot part of the visited map there.  Policy::THREADS must be 1024; callers check StreamEligible first.
 template <typename Policy, typename Problem>
 inline bool StreamEligible(const Args<typename Policy::VertexId, typename Policy::SizeT> &args)
 {
-    return !Problem::MARK_PREDECESSORS && args.type == V2V && args.output != OUT_TOMBSTONE &&
-           args.g.part.log_parts == 0 && args.in_queue != nullptr;
+    return !Problem::MARK_PREDECESSORS && !Problem::ENABLE_IDEMPOTENCE && Policy::PRE_CULL && args.type == V2V &&
+           args.output != OUT_TOMBSTONE && args.g.part.log_parts == 0 && args.in_queue != nullptr;
 }
 
 template <typename Policy, typename Problem, typename Functor>
@@ -118,10 +118,20 @@ cudaError_t LaunchStreamKernel(
     unsigned scan_grid = (unsigned)(scan_tiles < 1 ? 1 : scan_tiles);
     lb::ScanKernel<Policy><<<scan_grid, Policy::SCAN_THREADS, 0, stream>>>(args, sv);
     GR_TRY(cudaGetLastError());
+    // the visited mask as it is before the level: HarvestKernel reads the winners off the difference
+    const unsigned long long words = (unsigned long long)((args.g.nodes + 31) / 32);
+    GR_TRY(scratch->mask_before.Allocate((size_t)words + 4));
+    GR_TRY(cudaMemcpyAsync(scratch->mask_before.ptr, ds.d_visited_mask, sizeof(unsigned) * (size_t)words, cudaMemcpyDeviceToDevice, stream));
+    // one CTA per SM, each taking every gridDim.x-th tile
     unsigned long long tiles = (edges_hint + Policy::TILE_EDGES - 1) / Policy::TILE_EDGES;
     unsigned grid = (unsigned)(tiles < 1 ? 1 : (tiles < (unsigned long long)dev.sm_count ? tiles : (unsigned long long)dev.sm_count));
-    const size_t smem = lb::StreamHotOffset<Policy>() + sizeof(unsigned) * (size_t)hot_words;
+    const size_t smem = lb::StreamHotOffset<Policy>() + sizeof(unsigned) * (size_t)((hot_words + 3u) & ~3u);
     kernel<<<grid, Policy::THREADS, smem, stream>>>(ds, args, sv, hot_words);
+    GR_TRY(cudaGetLastError());
+    unsigned long long hctas = (words + 255) / 256;                          // a warp per 32 words, 8 warps per CTA
+    const unsigned long long hmax = (unsigned long long)dev.sm_count * 8ull;
+    lb::HarvestKernel<Policy, Problem, Functor><<<(unsigned)(hctas < 1 ? 1 : (hctas < hmax ? hctas : hmax)), 256, 0, stream>>>(
+        ds, args, scratch->mask_before.ptr, words);
     return util::GRError(cudaGetLastError(), "advance lb::StreamExpandKernel launch failed", __FILE__, __LINE__);
 }
 

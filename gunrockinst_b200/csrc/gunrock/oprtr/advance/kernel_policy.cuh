@@ -96,6 +96,7 @@ struct LbScratch {
     util::DeviceArray<unsigned long long> tile_desc;   // look-back descriptors of the scan
     util::DeviceArray<long long>          part_start;  // [max_tiles + 1] first item of each edge tile
     util::DeviceArray<unsigned>           ticket;      // scan tiles are handed out in arrival order
+    util::DeviceArray<unsigned>           mask_before; // streaming instance: the visited mask before the level (lazily sized)
     unsigned epoch = 0;                                // tags descriptors => no memset per call
 
     cudaError_t Allocate(size_t max_items, size_t max_edges, int scan_tile, int tile_edges, cudaStream_t s)

@@ -4,37 +4,49 @@
 // Replaces the same reference pipeline as lb.cuh (gunrock/oprtr/edge_map_partitioned/
 // kernel.cuh:242-559, RelaxPartitionedEdges2: every thread fetches its neighbour id with a
 // scalar (texture) load and probes / claims it in global memory).  What bounds that shape on a
-// B200 is not DRAM but the L1 wavefront rate: one 128-byte line per lane for the random probe of
-// the visited map (tools/probe_micro.cu: 334 G probes/s against 1650 G ids/s of plain
-// streaming).  This kernel removes both per-edge global accesses from the SM's load/store path:
+// B200 is not DRAM: it is the L1 wavefront rate of the random probe of the visited map (one
+// 128-byte line per lane; tools/probe_micro.cu, profiles/r02b_probe_micro_s25.json: 334 G probes/s
+// against 1660 G ids/s of plain streaming), ~100 instructions per edge of owner lookup and
+// staging in lb::ExpandKernel, and the latency of three dependent round trips (neighbour id ->
+// visited word -> claim) per edge with nothing to overlap them.  This kernel splits the work
+// between producer and consumer warps of one 1024-thread CTA per SM:
 //
-//  * neighbour-list tiles are STAGED IN SHARED MEMORY by the copy engines.  A tile is
-//    TILE_EDGES consecutive entries of the scanned frontier's edge space (the split points come
-//    from lb::ScanKernel, as for lb::ExpandKernel); it is made of pieces of neighbour lists.  A
-//    piece of >= kStreamMinBulk entries arrives by ONE TMA 1-D bulk copy (cp.async.bulk, SASS
-//    UBLKCP) issued by the thread that owns the piece -- the piece is rotated by up to three
-//    slots inside its own slot range so that shared and global addresses agree modulo 16 bytes,
-//    the <= 9 entries around the aligned run travel as 4-byte cp.async (LDGSTS); shorter pieces
-//    are packed by their warp, coalesced, also with cp.async.  kStreamStages tiles are in flight
-//    per SM; one mbarrier per ring slot collects the TMA transaction bytes and one deferred
-//    arrival per thread (cp.async.mbarrier.arrive), so consumers wait on exactly one word.
-//    Descriptors of the tile after next are prefetched into registers, so no thread ever waits
-//    for a dependent global load between two tiles.
-//  * the visited map of the HOT vertices -- ids below hot_words * 32 -- is copied into shared
-//    memory when the CTA starts and probed there.  On the degree-ordered twin of a graph
-//    (graph/build.cuh) the hot vertices are the highest-degree ones: 1 M bits (128 KB of the
-//    228 KB an SM has) answer ~80 % of the probes of an R-MAT scale-25 search and ~97 % at scale
-//    22.  A stale copy is harmless: a clear bit only sends the edge to the exact global claim.
-//
-// One CTA of Policy::THREADS (1024) threads per SM, persistent over its tiles, and no CTA-wide
-// barrier inside the tile loop: warps meet only at the ring's mbarriers (`full`: a tile has landed,
-// `empty`: every warp has left a slot), so they drift up to two tiles apart and one warp's L2
-// round trips overlap the others' work.  Consumers read four ids per LDS.128, probe, issue their
-// claims together (the functor's predicated CondEdgeIf) and enqueue through a per-warp
-// shared-memory stage (one global atomic per ~200 discoveries).
+//  * PRODUCER WARPS (8) turn the scanned frontier into DENSE TILES OF NEIGHBOUR IDS IN SHARED
+//    MEMORY.  A tile is TILE_EDGES consecutive entries of the frontier's edge space (split points
+//    from lb::ScanKernel, as for lb::ExpandKernel), made of pieces of neighbour lists; the
+//    producers share a tile's items round-robin (lane <-> item) and only issue copies, they
+//    never wait for data.  A piece of >= 32 entries arrives by ONE TMA 1-D bulk copy
+//    (cp.async.bulk, SASS UBLKCP) issued by the lane that owns it -- the piece is rotated by up
+//    to three slots inside its own slot range so that shared and global addresses agree modulo
+//    16 bytes (a tile is a bag of ids: their order is irrelevant), the <= 9 entries around the
+//    aligned run travel as 4-byte cp.async (LDGSTS).  Shorter pieces are flattened: a start-flag
+//    bitmap of the batch (one word per lane, in registers) and its popcount prefix give every
+//    slot its owner with two shuffles and a popc, and consecutive lanes copy consecutive entries
+//    with cp.async.  One mbarrier per ring slot collects the TMA transaction bytes and one
+//    deferred arrival per producer lane (cp.async.mbarrier.arrive).
+//  * CONSUMER WARPS (24) wait on that one word, read eight ids per lane with two LDS.128, free
+//    the slot, and probe: the visited map of the HOT vertices -- ids below hot_words * 32 -- lives
+//    in shared memory (fetched by TMA bulk copies when the CTA starts), the other words are read
+//    at L2, all eight under complementary predicates with no branch.  On the degree-ordered twin
+//    of a graph (graph/build.cuh) the hot vertices are the highest-degree ones and answer most
+//    probes of an R-MAT search without touching the L1 / L2 path.  A stale copy is harmless: a
+//    clear bit only makes the vertex a candidate.
+//  * CLAIMS ARE REDUCTIONS, WINNERS ARE HARVESTED.  The claim of BFS is the flip of the vertex's bit in
+//    Problem's visited mask (BFSFunctor::CondEdge: atomicOr, the caller whose call changed the bit
+//    wins).  Waiting for that answer -- and then storing the label, staging the vertex and looking up
+//    its degree -- is a chain of dependent L2 round trips that cost two thirds of a level
+//    (3.2 ms against 1.3 ms without it at scale 25).  Here a neighbour that
+//    looks unvisited gets its bit set by a fire-and-forget reduction (RED.OR on the global word, and
+//    on the shared copy for a hot vertex, so that an SM asks once), nothing in the streaming loop
+//    depends on memory beyond the probe, and the WINNERS of the level are read off afterwards by
+//    HarvestKernel: the bits that are set now and were not before the level (a snapshot of the mask
+//    taken by the launcher) -- each exactly once, in vertex order, so Functor::ApplyEdge (the label
+//    store), the output frontier and the out-degree sum become coalesced passes over 1 bit per
+//    vertex instead of random accesses per discovery.  The output frontier comes out sorted.
 //
 // Restrictions (the launcher falls back to lb::ExpandKernel otherwise): V2V, OUT_COMPACT or
-// OUT_NONE, !Problem::MARK_PREDECESSORS, a functor that ignores e_id / e_id_in, one device.
+// OUT_NONE, !Problem::MARK_PREDECESSORS, !Problem::ENABLE_IDEMPOTENCE (the functor's claim must be
+// the visited bit), a functor that ignores s_id / e_id / e_id_in in ApplyEdge, one device.
 #pragma once
 #include "lb.cuh"
 #include "../../util/async_copy.cuh"
@@ -44,30 +56,46 @@ namespace oprtr {
 namespace advance {
 namespace lb {
 
-#ifndef GRB_STREAM_COLD_LOAD
-#define GRB_STREAM_COLD_LOAD util::LoadCG   // visited words outside the hot range: read at L2 (fresh: a claim another SM
-#endif                                      // made in this launch is seen; a stale L1 line would cost an atomic per edge)
-constexpr int kStreamStages  = 4;       // tiles in flight per SM
-constexpr int kStreamMinBulk = 64;      // entries; shorter pieces are packed by their warp
-
-constexpr int kStreamAhead   = 2;       // tiles staged ahead of the one being consumed; the other
-                                        // kStreamStages - kStreamAhead slots let warps drift apart
-constexpr int kStreamWarpStage = 256;   // discoveries a warp collects before it enqueues them (one global atomic)
+constexpr int kStreamProducers = 8;         // producer warps; the other warps of the CTA consume
+constexpr int kStreamStages    = 3;         // tiles in the ring
+constexpr int kStreamRefresh   = 4;         // tiles between two fetches of the hot words
+constexpr int kStreamLong      = 32;        // pieces of at least this many entries travel by TMA bulk copy
+constexpr unsigned kStreamHotCap = 49152;   // words: 1.5 M bits; beyond that the L1 that is left starves the cold probes
 
 template <typename Policy>
 struct alignas(128) StreamStorage {
-    int                   tile[kStreamStages][Policy::TILE_EDGES];
-    int                   wstage[Policy::THREADS / 32][kStreamWarpStage];   // per-warp output staging
-    unsigned long long    full[kStreamStages];          // mbarriers: tile in slot s has landed
-    unsigned long long    empty[kStreamStages];         // mbarriers: every warp has left slot s
+    static const int CONSUMERS = Policy::THREADS / 32 - kStreamProducers;
+    int                   tile[kStreamStages][Policy::TILE_EDGES];          // the ring
+    long long             base[kStreamProducers][32];                       // batch of short pieces: CSR position of slot 0 of
+    int                   dbase[kStreamProducers][32];                      //   ranked piece r minus its prefix; same for its tile slot
+    unsigned              flags[kStreamProducers][32];                      //   start flags
+    unsigned long long    full[kStreamStages];                              // mbarriers: tile in slot s has landed
+    unsigned long long    empty[kStreamStages];                             // mbarriers: every consumer has read slot s
     unsigned long long    red[Policy::THREADS / 32 + 1];
     unsigned long long    total;
+    unsigned long long    bar;                                              // mbarrier of the hot-map bulk copy
 };
 template <typename Policy>
 constexpr size_t StreamHotOffset() { return (sizeof(StreamStorage<Policy>) + 127) & ~(size_t)127; }
 // shared memory left for the hot part of the visited map, in 32-bit words
 template <typename Policy>
-constexpr unsigned StreamMaxHotWords() { return (unsigned)((232448 - StreamHotOffset<Policy>()) / 4) & ~31u; }
+constexpr unsigned StreamMaxHotWords()
+{
+    const unsigned fit = (unsigned)((232448 - StreamHotOffset<Policy>()) / 4) & ~31u;
+    return fit < kStreamHotCap ? fit : kStreamHotCap;
+}
+
+// the visited word of a vertex: from the shared copy when `hot`, else from L2 when `cold` (fresh: a bit another SM set in
+// this launch is seen, which spares a reduction); ~0 ("visited") when neither.  Two loads under complementary predicates
+// into one register: no branch, so a lane's eight probes are in flight together.
+__device__ __forceinline__ unsigned ProbeVisitedWord(bool hot, bool cold, unsigned shared_addr, const unsigned *global_addr)
+{
+    unsigned w = 0xffffffffu;
+    asm volatile("{\n .reg .pred ph, pc;\n setp.ne.u32 ph, %3, 0;\n setp.ne.u32 pc, %4, 0;\n"
+                 " @ph ld.shared.u32 %0, [%1];\n @pc ld.global.cg.u32 %0, [%2];\n}\n"
+                 : "+r"(w) : "r"(shared_addr), "l"(global_addr), "r"((unsigned)hot), "r"((unsigned)cold) : "memory");
+    return w;
+}
 
 template <typename Policy, typename Problem, typename Functor>
 __global__ void __launch_bounds__(Policy::THREADS, 1)
@@ -79,23 +107,26 @@ StreamExpandKernel(const __grid_constant__ typename Problem::DataSlice ds_in,
     typedef typename Policy::VertexId VertexId;
     typedef typename Policy::SizeT    SizeT;
     typedef unsigned long long        ScanT;
-    constexpr int THREADS = Policy::THREADS, TILE = Policy::TILE_EDGES, N = kStreamStages;
-    constexpr int QUADS = TILE / (4 * THREADS);
-    static_assert(TILE % (4 * THREADS) == 0, "a thread consumes whole 16-byte groups");
+    constexpr int THREADS = Policy::THREADS, WARPS = THREADS / 32, TILE = Policy::TILE_EDGES, N = kStreamStages;
+    constexpr int PW = kStreamProducers, CW = WARPS - PW;
+    static_assert(TILE == CW * 32 * 8, "a consumer lane takes eight ids of every tile");
     static_assert(!Problem::MARK_PREDECESSORS, "the streaming advance hands no source vertex to the functor");
+    static_assert(Policy::PRE_CULL, "the streaming advance culls against Problem's visited bitmask");
     static_assert(sizeof(VertexId) == 4, "tiles hold 32-bit ids");
 
     // one device (the launcher checks): a compile-time identity partition drops the owner hash and the
-    // owner-major bit positions from the per-edge code (as in pull::Sweep)
+    // owner-major bit positions from the per-edge code (as in pull::Sweep): bit position of vertex v is v
     typename Problem::DataSlice ds = ds_in;
     if constexpr (HasPartition<typename Problem::DataSlice>::value) ds.part = graph::Partition();
 
     extern __shared__ __align__(128) unsigned char s_raw[];
     StreamStorage<Policy> &sm = *reinterpret_cast<StreamStorage<Policy> *>(s_raw);
     unsigned *s_hot = reinterpret_cast<unsigned *>(s_raw + StreamHotOffset<Policy>());
+    const unsigned s_hot_addr = util::SharedAddr(s_hot);
     const unsigned hot_bits = hot_words << 5;
-    const int tid = threadIdx.x, lane = util::LaneId();
+    const int tid = threadIdx.x, lane = util::LaneId(), warp = util::WarpId();
     const unsigned cta = blockIdx.x, nctas = gridDim.x;
+    const unsigned below = (1u << lane) - 1;
 
     const unsigned long long in_len = args.d_in_len ? *args.d_in_len : args.in_len;
     LevelCounters *slot_out = args.slots + ((args.queue_index + 1) & 3);
@@ -105,13 +136,24 @@ StreamExpandKernel(const __grid_constant__ typename Problem::DataSlice ds_in,
     }
     if (tid == 0) {
         sm.total = scratch.scanned[in_len];
-        for (int s = 0; s < N; ++s) { util::MbarInit(&sm.full[s], THREADS); util::MbarInit(&sm.empty[s], THREADS / 32); }
+        util::MbarInit(&sm.bar, 1);
+        for (int s = 0; s < N; ++s) { util::MbarInit(&sm.full[s], PW * 32); util::MbarInit(&sm.empty[s], CW); }
         util::MbarInitFence();
     }
-    if constexpr (Policy::PRE_CULL) {
-        for (unsigned w = tid; w < hot_words; w += THREADS) s_hot[w] = util::LoadCG(ds.d_visited_mask + w);
-    }
     __syncthreads();
+    if (hot_words) {
+        if (tid == 0) {                         // the hot words of the visited map: TMA 1-D bulk copies, 32 KB each
+            // (whole 16-byte groups: the map's allocation is padded, bits past the last vertex are never probed)
+            const unsigned copy_words = (hot_words + 3u) & ~3u;
+            util::MbarExpectTx(&sm.bar, copy_words * 4u);
+            for (unsigned w = 0; w < copy_words; w += 8192) {
+                const unsigned cnt = copy_words - w < 8192u ? copy_words - w : 8192u;
+                util::BulkCopyG2S(s_hot + w, ds.d_visited_mask + w, cnt * 4u, &sm.bar);
+            }
+            util::MbarArrive(&sm.bar);
+        }
+        if (warp >= PW) util::MbarWait(&sm.bar, 0);             // only the consumers read it
+    }
     const ScanT total = sm.total;
     unsigned long long num_tiles = (total + TILE - 1) / TILE;
     if (num_tiles > scratch.part_cap) {         // a frontier with duplicates expanded past the scratch
@@ -120,198 +162,231 @@ StreamExpandKernel(const __grid_constant__ typename Problem::DataSlice ds_in,
     }
     const long long my_tiles = num_tiles > cta ? (long long)((num_tiles - cta + nctas - 1) / nctas) : 0;
     const VertexId *col = args.g.col_indices;
-    unsigned long long my_edges = 0;            // thread 0 only
-    unsigned long long my_degree = 0;           // TRACK_OUT_DEGREE: out-degrees of the vertices this thread enqueued
-    int *wstage = sm.wstage[util::WarpId()];
-    unsigned wcount = 0;                        // warp-uniform: entries in wstage
-    // warp-convergent: the warp's staged discoveries leave for the output frontier as one coalesced run
-    auto flush_warp = [&]() {
-        if (wcount == 0) return;
-        unsigned long long base = 0;
-        if (lane == 0) base = atomicAdd(&slot_out->out_len, (unsigned long long)wcount);
-        base = __shfl_sync(util::kFullMask, base, 0);
-        __syncwarp();
-        for (unsigned k = lane; k < wcount; k += 32) {
-            const VertexId u = wstage[k];
-            if (base + k < args.out_cap) args.out_queue[base + k] = u;
-            else slot_out->overflow = 1;
-            if constexpr (Policy::TRACK_OUT_DEGREE) {
-                const long long row = args.g.part.Local(u);
-                my_degree += (unsigned long long)(args.g.row_offsets[row + 1] - args.g.row_offsets[row]);
-            }
-        }
-        __syncwarp();
-        wcount = 0;
-    };
+    unsigned long long my_edges = 0;            // one consumer thread
 
-    // ---- staging ---------------------------------------------------------------------------------------
-    // items [i0, i0 + cnt) overlap tile k of this CTA
-    auto load_bounds = [&](long long k, long long &i0, long long &cnt) {
-        const unsigned long long t = cta + (unsigned long long)k * nctas;
-        i0 = scratch.part_start[t];
-        const long long i1 = (t + 1 < num_tiles) ? scratch.part_start[t + 1] : (long long)in_len - 1;
-        cnt = i1 - i0 + 1;
-    };
-    // item i0 + j: its range of the frontier's edge space and the CSR position of its first entry
-    auto load_piece = [&](long long i0, long long cnt, long long j, ScanT &s, ScanT &e, SizeT &rs) {
-        s = 0; e = 0; rs = 0;
-        if (j < cnt) {
-            s  = scratch.scanned[i0 + j];
-            e  = scratch.scanned[i0 + j + 1];
-            rs = scratch.row_start[i0 + j];
-        }
-    };
-    // warp-convergent: copy this lane's piece (len entries from col + pos) to slots [d, d + len) of buf
-    auto stage_piece = [&](int *buf, unsigned long long *bar, int d, SizeT pos, int len) {
-        const bool is_long = len >= kStreamMinBulk;
-        if (is_long) {
-            // rotate the piece inside its slot range so that slot and CSR position agree modulo 4:
-            // entries [0, main) go to slots d + shift ..., the last `shift` entries to slots d ...
-            const int shift = (int)((pos - (SizeT)d) & 3);
-            const int main_cnt = len - shift;
-            const int head = (int)((4 - (int)(pos & 3)) & 3);       // entries before col's next 16-byte boundary
-            const int bulk = (main_cnt - head) & ~3;
-            int *dst = buf + d + shift;
-            const VertexId *src = col + pos;
-            for (int k = 0; k < head; ++k) util::CpAsync4(dst + k, src + k);
-            if (bulk > 0) {
-                util::MbarExpectTx(bar, (unsigned)bulk * 4u);
-                util::BulkCopyG2S(dst + head, src + head, (unsigned)bulk * 4u, bar);
+    if (warp < PW) {
+        // ================================ producers ==========================================================
+        // tile k of this CTA is global tile cta + k * nctas and lives in ring slot k % N; all producers work on the same
+        // tile, its items dealt round-robin to their lanes.  Nothing here waits for data.
+        auto tile_items = [&](long long k, long long &i0, long long &i1) {
+            i0 = 0; i1 = -1;
+            if (k < my_tiles) {
+                const unsigned long long t = cta + (unsigned long long)k * nctas;
+                i0 = scratch.part_start[t];
+                i1 = (t + 1 < num_tiles) ? scratch.part_start[t + 1] : (long long)in_len - 1;     // inclusive
             }
-            for (int k = head + bulk; k < main_cnt; ++k) util::CpAsync4(dst + k, src + k);
-            for (int k = main_cnt; k < len; ++k) util::CpAsync4(buf + d + (k - main_cnt), src + k);
-        }
-        // short pieces of the warp: packed, so that consecutive lanes copy consecutive entries
-        const int slen = is_long ? 0 : len;
-        const int incl = util::WarpInclusiveSum(slen);
-        const int T = __shfl_sync(util::kFullMask, incl, 31);
-        const int pre = incl - slen;
-        for (int x0 = 0; x0 < T; x0 += 32) {
-            const int x = x0 + lane;
-            int lo = 0;                                             // last lane whose exclusive prefix is <= x
-#pragma unroll
-            for (int step = 16; step > 0; step >>= 1) {
-                const int cand = lo + step;
-                const int pc = __shfl_sync(util::kFullMask, pre, cand & 31);
-                if (cand < 32 && pc <= x) lo = cand;
+        };
+        auto item_desc = [&](long long i, long long i1, ScanT &s, ScanT &e, SizeT &rs) {
+            s = 0; e = 0; rs = 0;
+            if (i <= i1) { s = scratch.scanned[i]; e = scratch.scanned[i + 1]; rs = scratch.row_start[i]; }
+        };
+        long long i0, i1, n_i0, n_i1;
+        unsigned refresh_phase = 0;             // thread 0: completed fetches of the hot words (phase 0 is the first one)
+        tile_items(0, i0, i1);
+        for (long long k = 0; k < my_tiles; ++k) {
+            const unsigned long long t = cta + (unsigned long long)k * nctas;
+            const ScanT tile_start = t * TILE;
+            const ScanT tile_end = (total - tile_start < (ScanT)TILE) ? total : tile_start + TILE;
+            int *buf = sm.tile[k % N];
+            unsigned long long *bar = &sm.full[k % N];
+            tile_items(k + 1, n_i0, n_i1);                      // requested now, needed for the next tile
+            ScanT s, e, ns, ne;
+            SizeT rs, nrs;
+            item_desc(i0 + warp + PW * lane, i1, s, e, rs);
+            // every kStreamRefresh tiles the shared copy of the hot words is fetched again (nobody waits for it: a word that
+            // is overwritten with an older value only costs a reduction): what the other SMs have discovered meanwhile stops
+            // being "unvisited" here, which is most of what a hot vertex costs -- without it every SM flips every hot vertex
+            // itself, ~150 reductions per vertex instead of a few
+            if (hot_words && tid == 0 && k > 0 && (k % kStreamRefresh) == 0 && util::MbarTryWait(&sm.bar, refresh_phase & 1u)) {
+                ++refresh_phase;
+                const unsigned copy_words = (hot_words + 3u) & ~3u;
+                util::MbarExpectTx(&sm.bar, copy_words * 4u);
+                for (unsigned w = 0; w < copy_words; w += 8192) {
+                    const unsigned cnt = copy_words - w < 8192u ? copy_words - w : 8192u;
+                    util::BulkCopyG2S(s_hot + w, ds.d_visited_mask + w, cnt * 4u, &sm.bar);
+                }
+                util::MbarArrive(&sm.bar);
             }
-            const int od = __shfl_sync(util::kFullMask, d, lo), opre = __shfl_sync(util::kFullMask, pre, lo);
-            const long long opos = __shfl_sync(util::kFullMask, (long long)pos, lo);
-            if (x < T) util::CpAsync4(buf + od + (x - opre), col + opos + (x - opre));
-        }
-    };
-    // stage tile k into ring slot k % N; (s, e, rs) describe item i0 + tid (prefetched)
-    auto issue = [&](long long k, long long i0, long long cnt, ScanT s, ScanT e, SizeT rs) {
-        const unsigned long long t = cta + (unsigned long long)k * nctas;
-        const ScanT tile_start = t * TILE;
-        const ScanT tile_end = (total - tile_start < (ScanT)TILE) ? total : tile_start + TILE;
-        int *buf = sm.tile[k % N];
-        unsigned long long *bar = &sm.full[k % N];
-        for (long long j0 = 0; j0 == 0 || j0 < cnt; j0 += THREADS) {       // one round unless > THREADS items overlap the tile
-            if (j0 > 0) load_piece(i0, cnt, j0 + tid, s, e, rs);
-            const ScanT b = s > tile_start ? s : tile_start, en = e < tile_end ? e : tile_end;
-            const int len = (j0 + tid < cnt && en > b) ? (int)(en - b) : 0;
-            stage_piece(buf, bar, (int)(b - tile_start), rs + (SizeT)(b - s), len);
-        }
-        util::MbarArriveOnCpAsync(bar);
-        if (tid == 0) my_edges += tile_end - tile_start;
-    };
-
-    // ---- consumption -----------------------------------------------------------------------------------
-    auto consume = [&](long long k) {
-        const unsigned long long t = cta + (unsigned long long)k * nctas;
-        const ScanT tile_start = t * TILE;
-        const int tile_edges = (int)((total - tile_start < (ScanT)TILE) ? (total - tile_start) : (ScanT)TILE);
-        const int4 *t4 = reinterpret_cast<const int4 *>(sm.tile[k % N]);
+            // every consumer has read the slot's previous tenant (which also means that tenant's phase of `full` is over)
+            if (k >= N) util::MbarWait(&sm.empty[k % N], (unsigned)(((k / N) - 1) & 1));
+            for (long long ib = i0; ib <= i1; ib += 32 * PW) {
+                // items are dealt round-robin to the producers, so that a tile of a few dozen long lists keeps all of them busy
+                // (a warp issues its lanes' bulk copies one after the other)
+                const long long i = ib + warp + PW * lane;
+                item_desc(i + 32 * PW, i1, ns, ne, nrs);        // this producer's next batch, requested before this one is issued
+                // lane <-> item: its range of the frontier's edge space clipped to the tile, where that starts in the CSR
+                // and in the tile
+                const ScanT b = s > tile_start ? s : tile_start, en = e < tile_end ? e : tile_end;
+                const int len = (i <= i1 && en > b) ? (int)(en - b) : 0;
+                const long long pos = (long long)rs + (long long)(b - s);
+                const int d = (int)(b - tile_start);
+                if (len >= kStreamLong) {
+                    // rotate the piece inside its slot range so that slot and CSR position agree modulo 4:
+                    // entries [0, main) go to slots d + shift ..., the last `shift` entries to slots d ...
+                    const int shift = (int)((pos - (long long)d) & 3);
+                    const int main_cnt = len - shift;
+                    const int head = (int)((4 - (int)(pos & 3)) & 3);       // entries before col's next 16-byte boundary
+                    const int bulk = (main_cnt - head) & ~3;
+                    int *dst = buf + d + shift;
+                    const VertexId *src = col + pos;
+                    util::MbarExpectTx(bar, (unsigned)bulk * 4u);           // len >= 32: bulk > 0
+                    util::BulkCopyG2S(dst + head, src + head, (unsigned)bulk * 4u, bar);
+                    // the <= 3 entries before the aligned run and the <= 6 behind it (no loops: lanes differ)
 #pragma unroll
-        for (int r = 0; r < QUADS; ++r) {
-            const int qi = r * THREADS + tid;
-            const int4 q = t4[qi];
-            const VertexId v[4] = {q.x, q.y, q.z, q.w};
-            bool live[4];
+                    for (int x = 0; x < 3; ++x)
+                        if (x < head) util::CpAsync4(dst + x, src + x);
 #pragma unroll
-            for (int i = 0; i < 4; ++i) live[i] = qi * 4 + i < tile_edges;
-            if constexpr (Policy::PRE_CULL) {
-                unsigned word[4];
+                    for (int y = 0; y < 6; ++y) {
+                        const int x = head + bulk + y;
+                        if (x < len) util::CpAsync4(x < main_cnt ? dst + x : buf + d + (x - main_cnt), src + x);
+                    }
+                }
+                __syncwarp();
+                // short pieces, flattened: slot x of the batch belongs to the piece whose start flag is the last one at or
+                // before x; flag word w sits in lane w's register, so is the number of flags before it
+                const int slen = len < kStreamLong ? len : 0;
+                const unsigned nz = __ballot_sync(util::kFullMask, slen > 0);
+                if (nz) {
+                    const int incl = util::WarpInclusiveSum(slen);
+                    const int T = __shfl_sync(util::kFullMask, incl, 31);   // <= 31 * 32: 31 flag words
+                    const int pre = incl - slen;
+                    sm.flags[warp][lane] = 0;
+                    __syncwarp();
+                    if (slen > 0) {
+                        atomicOr(&sm.flags[warp][pre >> 5], 1u << (pre & 31));
+                        const int r = __popc(nz & below);
+                        sm.base[warp][r] = pos - pre;
+                        sm.dbase[warp][r] = d - pre;
+                    }
+                    __syncwarp();
+                    const unsigned fw = sm.flags[warp][lane];
+                    const int fc = __popc(fw);
+                    const int fpre = util::WarpInclusiveSum(fc) - fc;
+                    for (int x0 = 0; x0 < T; x0 += 32) {
+                        const int w = x0 >> 5;                              // warp-uniform
+                        const unsigned word = __shfl_sync(util::kFullMask, fw, w);
+                        const int wp = __shfl_sync(util::kFullMask, fpre, w);
+                        const int x = x0 + lane;
+                        if (x < T) {
+                            const int rank = wp + __popc(word & (0xffffffffu >> (31 - lane))) - 1;
+                            util::CpAsync4(buf + (sm.dbase[warp][rank] + x), col + (sm.base[warp][rank] + x));
+                        }
+                    }
+                    __syncwarp();                                           // flags / base are rewritten by the next batch
+                }
+                s = ns; e = ne; rs = nrs;
+            }
+            util::MbarArriveOnCpAsync(bar);     // fires when this lane's cp.asyncs have landed; bulk bytes are counted by the barrier
+            i0 = n_i0; i1 = n_i1;
+        }
+    } else {
+        // ================================ consumers ==========================================================
+        const int cw = warp - PW;
+        unsigned *vmask = ds.d_visited_mask;
+        // a consumer reads tile k + 1 into registers (and frees its slot) BEFORE it works on tile k: the slot is back
+        // with the producers one tile earlier
+        const int qa_i = cw * 64 + lane, qb_i = qa_i + 32;
+        int4 qa = make_int4(0, 0, 0, 0), qb = qa;
+        auto take = [&](long long k) {
+            util::MbarWait(&sm.full[k % N], (unsigned)((k / N) & 1));
+            const int4 *t4 = reinterpret_cast<const int4 *>(sm.tile[k % N]);
+            qa = t4[qa_i]; qb = t4[qb_i];
+            __syncwarp();
+            if (lane == 0) util::MbarArrive(&sm.empty[k % N]);          // the ids are in registers: the slot is free
+        };
+        if (my_tiles > 0) take(0);
+        for (long long k = 0; k < my_tiles; ++k) {
+            const unsigned long long t = cta + (unsigned long long)k * nctas;
+            const ScanT tile_start = t * TILE;
+            const int tile_edges = (int)((total - tile_start < (ScanT)TILE) ? (total - tile_start) : (ScanT)TILE);
+            if (tid == PW * 32) my_edges += (unsigned long long)tile_edges;
+            const VertexId v[8] = {qa.x, qa.y, qa.z, qa.w, qb.x, qb.y, qb.z, qb.w};
+            if (k + 1 < my_tiles) take(k + 1);
+            unsigned valid = 0xffu;
+            if (tile_edges < TILE) {                                    // the level's last tile
+                valid = 0;
 #pragma unroll
                 for (int i = 0; i < 4; ++i) {
-                    word[i] = 0;
-                    if (live[i])
-                        word[i] = ((unsigned)v[i] < hot_bits) ? s_hot[(unsigned)v[i] >> 5]
-                                                              : GRB_STREAM_COLD_LOAD(ds.d_visited_mask + (ds.BitPos(v[i]) >> 5));
-                }
-#pragma unroll
-                for (int i = 0; i < 4; ++i)
-                    if ((word[i] >> (ds.BitPos(v[i]) & 31)) & 1u) live[i] = false;
-            }
-            // all four conditions first: their claims (one global atomic each in BFS) are independent and
-            // travel together; a thread that waited for each answer before asking the next question spent
-            // four L2 round trips per tile on a level whose frontier discovers most of its neighbours
-            bool ok[4];
-#pragma unroll
-            for (int i = 0; i < 4; ++i)
-                ok[i] = CondEdgeIfImpl<Functor, typename Problem::DataSlice, VertexId, SizeT>::Call(
-                    live[i], (VertexId)args.iteration, v[i], &ds, (SizeT)0, (SizeT)0);
-#pragma unroll
-            for (int i = 0; i < 4; ++i) {
-                if (live[i]) {
-                    // claimed now or found claimed: either way nobody in this CTA needs to ask again
-                    if (Policy::PRE_CULL && (unsigned)v[i] < hot_bits) atomicOr(s_hot + ((unsigned)v[i] >> 5), 1u << (v[i] & 31));
-                    if (ok[i]) Functor::ApplyEdge((VertexId)args.iteration, v[i], &ds, (SizeT)0, (SizeT)0);
+                    valid |= (unsigned)(qa_i * 4 + i < tile_edges) << i;
+                    valid |= (unsigned)(qb_i * 4 + i < tile_edges) << (4 + i);
                 }
             }
-            if (args.output == OUT_COMPACT) {
-                unsigned bal[4];
+            // ---- probe: eight words in flight per lane
+            unsigned word[8];
 #pragma unroll
-                for (int i = 0; i < 4; ++i) bal[i] = __ballot_sync(util::kFullMask, ok[i]);
-                const unsigned tot = __popc(bal[0]) + __popc(bal[1]) + __popc(bal[2]) + __popc(bal[3]);
-                if (tot) {                                          // warp-uniform
-                    if (wcount + tot > (unsigned)kStreamWarpStage) flush_warp();
-                    const unsigned below = (1u << lane) - 1;
-                    unsigned at = wcount;
+            for (int i = 0; i < 8; ++i) {
+                const bool ok = (valid >> i) & 1u, hot = (unsigned)v[i] < hot_bits;
+                const unsigned wi = (unsigned)v[i] >> 5;
+                word[i] = ProbeVisitedWord(ok && hot, ok && !hot, s_hot_addr + wi * 4u, vmask + wi);
+            }
+            unsigned live = 0;
 #pragma unroll
-                    for (int i = 0; i < 4; ++i) {
-                        if (ok[i]) wstage[at + __popc(bal[i] & below)] = v[i];
-                        at += __popc(bal[i]);
-                    }
-                    wcount += tot;
-                }
+            for (int i = 0; i < 8; ++i) live |= (((word[i] >> (v[i] & 31)) & 1u) ^ 1u) << i;       // ~0u: not valid
+            // ---- claim: reductions without a return value, nothing waits for them; HarvestKernel finds the winners
+            while (live) {
+                const int i = __ffs(live) - 1;
+                live &= live - 1;
+                const VertexId x = (i & 4) ? ((i & 2) ? ((i & 1) ? v[7] : v[6]) : ((i & 1) ? v[5] : v[4]))
+                                           : ((i & 2) ? ((i & 1) ? v[3] : v[2]) : ((i & 1) ? v[1] : v[0]));
+                const unsigned bit = 1u << (x & 31), wi = (unsigned)x >> 5;
+                if ((unsigned)x < hot_bits) atomicOr(s_hot + wi, bit);  // this SM asks once
+                atomicOr(vmask + wi, bit);
             }
         }
-    };
-
-    // ---- the pipeline: tile k is consumed while tiles k+1 .. k+AHEAD are in flight.  No CTA-wide barrier inside:
-    // a thread stages its share of tile k+AHEAD once every warp has left the slot's previous tenant (tile
-    // k+AHEAD-N, `empty`), waits for its own tile on `full`, so warps drift up to N-AHEAD tiles apart and one
-    // warp's L2 round trips (cold probes, claims) overlap the others' work. -----------------------------------
-    constexpr int AHEAD = kStreamAhead;
-    static_assert(AHEAD >= 1 && AHEAD < N, "ring depth");
-    long long b_i0 = 0, b_cnt = 0, p_i0 = 0, p_cnt = 0;
-    ScanT p_s = 0, p_e = 0;
-    SizeT p_rs = 0;
-    for (long long ks = 0; ks < AHEAD && ks < my_tiles; ++ks) {
-        load_bounds(ks, p_i0, p_cnt);
-        load_piece(p_i0, p_cnt, tid, p_s, p_e, p_rs);
-        issue(ks, p_i0, p_cnt, p_s, p_e, p_rs);
     }
-    if (AHEAD < my_tiles) { load_bounds(AHEAD, p_i0, p_cnt); load_piece(p_i0, p_cnt, tid, p_s, p_e, p_rs); }
-    if (AHEAD + 1 < my_tiles) load_bounds(AHEAD + 1, b_i0, b_cnt);
-    for (long long k = 0; k < my_tiles; ++k) {
-        const long long ks = k + AHEAD;
-        if (ks < my_tiles) {
-            if (ks >= N) util::MbarWait(&sm.empty[ks % N], (unsigned)(((ks / N) - 1) & 1));
-            issue(ks, p_i0, p_cnt, p_s, p_e, p_rs);
-        }
-        if (ks + 1 < my_tiles) { p_i0 = b_i0; p_cnt = b_cnt; load_piece(p_i0, p_cnt, tid, p_s, p_e, p_rs); }
-        if (ks + 2 < my_tiles) load_bounds(ks + 2, b_i0, b_cnt);
-        util::MbarWait(&sm.full[k % N], (unsigned)((k / N) & 1));
-        consume(k);
-        __syncwarp();
-        if (lane == 0) util::MbarArrive(&sm.empty[k % N]);
-    }
-    if (args.output == OUT_COMPACT) flush_warp();
     BlockAccumulate<THREADS>(my_edges, sm.red, &slot_out->edges);
-    if constexpr (Policy::TRACK_OUT_DEGREE) BlockAccumulate<THREADS>(my_degree, sm.red, &slot_out->out_degree);
+}
+
+// The winners of a streamed level: every vertex whose bit is set in the visited mask now and was not in the snapshot
+// taken before the level.  Each exactly once and in vertex order.  A warp takes 32 words of the mask at a time (lane <->
+// word for the counts, lane <-> vertex of word j for the work), so Functor::ApplyEdge (BFS: the label store), the output
+// frontier and the row-offset reads of the out-degree sum are coalesced; one global atomic per 1024 vertices scanned.
+template <typename Policy, typename Problem, typename Functor>
+__global__ void __launch_bounds__(256)
+HarvestKernel(const __grid_constant__ typename Problem::DataSlice ds_in,
+              const __grid_constant__ Args<typename Policy::VertexId, typename Policy::SizeT> args,
+              const unsigned *before, unsigned long long words)
+{
+    typedef typename Policy::VertexId VertexId;
+    typedef typename Policy::SizeT    SizeT;
+    constexpr int THREADS = 256;
+    typename Problem::DataSlice ds = ds_in;
+    if constexpr (HasPartition<typename Problem::DataSlice>::value) ds.part = graph::Partition();
+    __shared__ unsigned long long s_red[THREADS / 32 + 1];
+    LevelCounters *slot_out = args.slots + ((args.queue_index + 1) & 3);
+    const int lane = util::LaneId();
+    const unsigned below = (1u << lane) - 1;
+    const unsigned long long groups = (words + 31) / 32;
+    const unsigned long long gw = ((unsigned long long)blockIdx.x * THREADS + threadIdx.x) >> 5;
+    const unsigned long long nw = ((unsigned long long)gridDim.x * THREADS) >> 5;
+    unsigned long long my_degree = 0;
+    for (unsigned long long g = gw; g < groups; g += nw) {
+        const unsigned long long w = g * 32 + lane;
+        const unsigned bits = (w < words) ? (util::LoadCG(ds.d_visited_mask + w) & ~before[w]) : 0u;
+        const unsigned cnt = (unsigned)__popc(bits);
+        const unsigned incl = util::WarpInclusiveSum(cnt);
+        const unsigned tot = __shfl_sync(util::kFullMask, incl, 31);
+        if (tot == 0) continue;                                 // warp-uniform
+        unsigned long long base = 0;
+        if (lane == 0) base = atomicAdd(&slot_out->out_len, (unsigned long long)tot);
+        base = __shfl_sync(util::kFullMask, base, 0);
+        for (int j = 0; j < 32; ++j) {
+            const unsigned wj = __shfl_sync(util::kFullMask, bits, j);
+            const unsigned pj = __shfl_sync(util::kFullMask, incl - cnt, j);
+            if (wj == 0) continue;                              // warp-uniform
+            if ((wj >> lane) & 1u) {
+                const VertexId v = (VertexId)(((g * 32 + j) << 5) + lane);
+                Functor::ApplyEdge((VertexId)args.iteration, v, &ds, (SizeT)0, (SizeT)0);
+                if (args.output == OUT_COMPACT) {
+                    const unsigned long long at = base + pj + __popc(wj & below);
+                    if (at < args.out_cap) args.out_queue[at] = v; else slot_out->overflow = 1;
+                }
+                if constexpr (Policy::TRACK_OUT_DEGREE)
+                    my_degree += (unsigned long long)(args.g.row_offsets[(long long)v + 1] - args.g.row_offsets[v]);
+            }
+        }
+    }
+    if constexpr (Policy::TRACK_OUT_DEGREE) BlockAccumulate<THREADS>(my_degree, s_red, &slot_out->out_degree);
 }
 
 }  // namespace lb

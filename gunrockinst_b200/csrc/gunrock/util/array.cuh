@@ -51,6 +51,7 @@ class BlockCache {
                 *out = it->second.back();
                 it->second.pop_back();
                 cached_ -= cls;
+                held_[dev] -= cls;
                 *got = cls;
                 return cudaSuccess;
             }
@@ -65,13 +66,18 @@ class BlockCache {
         return e;
     }
 
+    // Callers hand a block back only after the work that used it has completed (every Release() in this
+    // library sits behind a stream / device synchronisation of its owner): blocks carry no stream or event,
+    // so a block given back while a kernel still uses it would be a use-after-free for the next taker.
     void Give(void *p, size_t cls, int dev)
     {
         if (!p) return;
         if (enabled_) {
             std::lock_guard<std::mutex> lock(mu_);
-            if (cached_ + cls <= Limit()) {
-                free_[std::make_pair(pinned_ ? 0 : dev, cls)].push_back(p);
+            const int key = pinned_ ? 0 : dev;
+            if (held_[key] + cls <= Limit(key)) {
+                free_[std::make_pair(key, cls)].push_back(p);
+                held_[key] += cls;
                 cached_ += cls;
                 return;
             }
@@ -85,6 +91,7 @@ class BlockCache {
         for (auto &kv : free_)
             for (void *p : kv.second) Free(p, kv.first.first);
         free_.clear();
+        held_.clear();
         cached_ = 0;
     }
     size_t CachedBytes() { std::lock_guard<std::mutex> lock(mu_); return cached_; }
@@ -108,19 +115,30 @@ class BlockCache {
         cudaFree(p);
         if (cur != dev) cudaSetDevice(cur);
     }
-    size_t Limit()
+    // most bytes the cache keeps per device: GRB_POOL_LIMIT_MB, else a quarter of THAT device's memory (other
+    // allocators in the process -- torch, NCCL, the caller -- need the rest); 1 GB of pinned host memory
+    size_t Limit(int dev)
     {
-        if (limit_ == 0) {
-            if (pinned_) limit_ = (size_t)1 << 30;
-            else {
-                size_t free_b = 0, total_b = 0;
-                limit_ = (cudaMemGetInfo(&free_b, &total_b) == cudaSuccess && total_b) ? total_b / 2 : ((size_t)8 << 30);
-            }
+        auto it = limit_.find(dev);
+        if (it != limit_.end()) return it->second;
+        size_t lim;
+        const char *e = getenv("GRB_POOL_LIMIT_MB");
+        if (e && atoll(e) > 0) lim = (size_t)atoll(e) << 20;
+        else if (pinned_) lim = (size_t)1 << 30;
+        else {
+            int cur = 0;
+            cudaGetDevice(&cur);
+            if (cur != dev) cudaSetDevice(dev);
+            size_t free_b = 0, total_b = 0;
+            lim = (cudaMemGetInfo(&free_b, &total_b) == cudaSuccess && total_b) ? total_b / 4 : ((size_t)8 << 30);
+            if (cur != dev) cudaSetDevice(cur);
         }
-        return limit_;
+        limit_[dev] = lim;
+        return lim;
     }
     bool   pinned_, enabled_ = true;
-    size_t cached_ = 0, limit_ = 0;
+    size_t cached_ = 0;
+    std::map<int, size_t> limit_, held_;
     std::mutex mu_;
     std::map<std::pair<int, size_t>, std::vector<void *>> free_;
 };

@@ -252,11 +252,13 @@ def run_reference(args, rank, world):
 
 
 def workload_config(args, scale, nodes, edges):
-    if args.gpus == 1:
+    if args.gpus == 1 and not getattr(args, "partitioned", False):
         w = "direction-optimising BFS, R-MAT scale %d edgefactor 16 undirected (BASELINE configs[1])" % scale
     else:
-        w = ("BFS, R-MAT scale %d edgefactor 16 undirected, 1D vertex-partitioned over %d devices, "
-             "per-level NCCL frontier exchange (BASELINE configs[4])" % (scale, args.gpus))
+        exch = ("NCCL all-to-all / all-gather of the frontier bitmaps" if getattr(args, "exchange", "peer") == "nccl"
+                else "stores into peer memory over NVLink from the producing kernels (the NCCL all-to-all is --exchange nccl)")
+        w = ("BFS, R-MAT scale %d edgefactor 16 undirected, 1D vertex-partitioned over %d device%s, per-level frontier "
+             "exchange: %s (BASELINE configs[4])" % (scale, args.gpus, "" if args.gpus == 1 else "s", exch))
     return {"workload": w, "scale": scale, "edgefactor": 16, "nodes": nodes, "directed_edges": edges,
             "rmat_abcd": [0.55, 0.2, 0.2, 0.05], "seed": 42 + scale, "sources": N_SOURCES,
             "l2_policy": "inputs larger than L2 (CSR %.2f GB vs 126 MB L2); labels/bitmaps are re-initialised "
@@ -578,6 +580,8 @@ def main():
                          "PageRank, scale-24 SSSP, each with its oracle check: several minutes)")
     ap.add_argument("--exchange", default="peer", choices=["peer", "nccl"],
                     help="partitioned runs: peer-memory stores over NVLink (default) or NCCL collectives")
+    ap.add_argument("--no-single-ref", action="store_true",
+                    help="partitioned runs: skip the single-device search of the same graph on rank 0 (reference point + parity)")
     ap.add_argument("--partitioned", action="store_true",
                     help="use the partitioned driver even on one device (the 1-device point of a scale-27 scaling table)")
     args = ap.parse_args()
@@ -588,6 +592,11 @@ def main():
     rank = env_int("RANK", 0)
     if world > 1:
         args.gpus = world
+    # launched by torchrun (the scaling run: N = 1, 2, 4, 8 back to back): every point is the SAME workload, the scale-27
+    # partitioned search, so that the 1-device point is the one the others are compared with.  A plain `python bench.py`
+    # stays BASELINE configs[1] (scale 22 on one device).
+    if "RANK" in os.environ and "WORLD_SIZE" in os.environ and "LOCAL_RANK" in os.environ:
+        args.partitioned = True             # (the reference arm times the same graph: its config has to match)
     if args.scale <= 0:
         args.scale = 22 if (args.gpus == 1 and not args.partitioned) else 27
     if args.impl == "reference":

@@ -138,10 +138,19 @@ class DeviceEngine:
                                           exchange_ms=r.exchange_ms))
         return out
 
-    def labels(self):
-        out = np.empty(self.local_nodes, dtype=np.int32)
-        _capi.check(_capi.lib().grb_mgbfs_labels(self._h, out.ctypes.data_as(C.c_void_p)), "grb_mgbfs_labels")
-        return out
+    def labels(self, copy=True):
+        """this rank's depths -> host.  The landing buffer is page-locked and allocated once (a fresh pageable array per
+        call made the download crawl at 3-4 GB/s with eight ranks contending); copy=False returns a view of it that the
+        next call overwrites."""
+        if getattr(self, "_labels_pinned", None) is None:
+            self._labels_pinned = torch.empty(max(self.local_nodes, 1), dtype=torch.int32, pin_memory=True)
+        _capi.check(_capi.lib().grb_mgbfs_labels(self._h, C.c_void_p(self._labels_pinned.data_ptr())), "grb_mgbfs_labels")
+        view = self._labels_pinned.numpy()[:self.local_nodes]
+        return view.copy() if copy else view
+
+    def device_labels(self):
+        """torch view (no copy) of this rank's depths on the device"""
+        return self._tensor(5, self.local_nodes, "<i4")
 
     # timing hooks (CUDA events on the stream every step and collective is ordered on)
     def stream_context(self):
@@ -605,9 +614,50 @@ def bench(args, rank, world, workload_config, ClockSampler, pick_sources, measur
         sources = _pick_sources(g, eng, 64, 1234 + scale)
         clocks = ClockSampler(local)
         warm = max(args.warmup, 3)
+        dev = eng.device
+        # ---- the same graph, unpartitioned, on ONE device (rank 0): the 1-device point every scaling figure of this line
+        # refers to, and the labels the partitioned search has to reproduce
+        single, ref_labels, oracle_parity = None, None, None
+        if not getattr(args, "no_single_ref", False) and scale <= 27:
+            if rank == 0:
+                try:
+                    from . import Bfs, release_cached_memory
+                    t_s = time.time()
+                    gfull = g if world == 1 else Graph.rmat(scale, 16, device=local)
+                    sb = Bfs(gfull, direction_optimized=True)
+                    s_stream = torch.cuda.ExternalStream(gfull.stream(), device=dev)
+                    for i in range(3):
+                        sb.run(sources[i % len(sources)], want_labels=False)
+                    s_steps = max(1, min(args.steps, 64))
+                    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                    torch.cuda.synchronize()
+                    a.record(s_stream)
+                    s_stats = sb.run_many([sources[i % len(sources)] for i in range(s_steps)])
+                    b.record(s_stream)
+                    torch.cuda.synchronize()
+                    s_ms = a.elapsed_time(b)
+                    s_edges = sum(x["edges_visited"] for x in s_stats)
+                    sb.run(sources[0], want_labels=False)
+                    ref_labels = torch.as_tensor(_RawCuda(sb.device_labels(), eng.nodes, "<i4"), device=dev).clone()
+                    single = {"gteps": s_edges / (s_ms * 1e-3) / 1e9, "ms_per_search": s_ms / s_steps, "searches": s_steps,
+                              "graph": "the same seeded R-MAT scale %d, unpartitioned, resident on device 0" % scale,
+                              "api": "grb_bfs_run_many (direction-optimising)", "setup_s": round(time.time() - t_s, 1)}
+                    if scale <= 24 and not getattr(args, "no_cpu", False):
+                        import oracle                       # the checker only
+                        oracle.build()
+                        ro, co = gfull.download()
+                        oracle_parity = bool(np.array_equal(ref_labels.cpu().numpy(), oracle.bfs(ro, co, sources[0])))
+                        del ro, co
+                    sb.close()
+                    if world > 1:
+                        gfull.close()
+                    release_cached_memory()
+                except Exception as exc:                    # never lose the line over the reference point
+                    single = {"error": "%s: %s" % (type(exc).__name__, str(exc)[:300])}
+                    ref_labels = None
+            dist.barrier()
         for i in range(warm):
             bfs.run(sources[i % len(sources)])
-        dev = eng.device
         dist.barrier()
         torch.cuda.synchronize()
         clocks.start()
@@ -660,15 +710,43 @@ def bench(args, rank, world, workload_config, ClockSampler, pick_sources, measur
         dist.all_reduce(pms, op=dist.ReduceOp.MAX)
         pull_ms = float(pms.item())
 
-        # end to end for a resident partitioned graph: source in, this rank's labels out to the host
+        # ---- parity of the partitioned search: depths of sources[0] gathered on rank 0 (device side, NCCL) against the
+        # single-device search of the same graph (and, up to scale 24, that one against the CPU oracle)
+        parity = None
+        bfs.run(sources[0])
+        mine = eng.device_labels()
+        parts = [torch.empty_like(mine) for _ in range(world)] if rank == 0 else None
+        if world > 1:
+            dist.gather(mine, parts, dst=0)
+        elif rank == 0:
+            parts = [mine]
+        if rank == 0:
+            got = torch.empty(eng.nodes, dtype=torch.int32, device=dev)
+            for r, lab in enumerate(parts):
+                got[torch.as_tensor(global_ids(eng.local_nodes, lp, r), device=dev)] = lab
+            reached = got >= 0
+            hist = torch.bincount(got[reached].to(torch.int64)).cpu().tolist()
+            parity = {"source": int(sources[0]), "reached": int(reached.sum().item()),
+                      "sum_of_depths": int(got[reached].to(torch.int64).sum().item()), "depth_histogram": hist,
+                      "equals_single_device_search": (bool(torch.equal(got, ref_labels)) if ref_labels is not None else None),
+                      "single_device_search_equals_cpu_oracle": oracle_parity,
+                      "how": "depths of every rank gathered on rank 0 over NCCL and compared on the device with the labels "
+                             "of grb_bfs_run on the unpartitioned graph"}
+            parity["ok"] = parity["equals_single_device_search"]
+            del got, parts
+        ref_labels = None
+
+        # end to end for a resident partitioned graph: source in, this rank's labels out to the host (page-locked landing
+        # buffer, reused)
         torch.cuda.synchronize()
         dist.barrier()
         e2e_steps = max(1, min(args.steps, args.e2e_steps))
+        eng.labels(copy=False)
         t0 = time.perf_counter()
         e2e_edges = 0
         for i in range(e2e_steps):
             st = bfs.run(sources[i % len(sources)])
-            eng.labels()
+            eng.labels(copy=False)
             e2e_edges += st["edges_visited"]
         torch.cuda.synchronize()
         te = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device=dev)
@@ -705,9 +783,13 @@ def bench(args, rank, world, workload_config, ClockSampler, pick_sources, measur
                                      "(events on the stream, max over ranks); compute and exchange time per search "
                                      "are split in `exchange`"},
                 "cpu_baseline": None,
+                "single_device_same_graph": single,
+                "speedup_vs_single_device": (value / single["gteps"]) if single and single.get("gteps") else None,
+                "parity": parity,
                 "e2e": {"value": e2e_edges / max(e2e_s, 1e-9) / 1e9, "unit": "GTEPS", "h2d_bytes_per_step": 4,
                         "d2h_bytes_per_step": 4 * eng.local_nodes * world, "steps": e2e_steps,
-                        "api": "PartitionedBfs.run + labels download on every rank (graph resident, partitioned)"},
+                        "api": "PartitionedBfs.run + labels download on every rank into a reused page-locked buffer "
+                               "(graph resident, partitioned; no graph upload inside the step)"},
                 "gpu_launches": launches_all, "clocks": clocks.summary(),
                 "graph500_gteps": value / 2.0, "edges_inspected_per_search": inspected / max(args.steps, 1),
                 "setup_s": round(time.time() - t_setup, 1),

@@ -232,3 +232,61 @@ extern "C" int grb_test_filter(int device, int64_t nodes, int compact, const int
     GRB_TRY(cudaStreamSynchronize(s));
     return 0;
 }
+
+// ---- the near/far split on its own (priority_queue::Bisect; reference: gunrock/priority_queue/kernel.cuh:404-503) ----
+#include "../gunrock/priority_queue/kernel.cuh"
+namespace {
+struct ScoreProblem {
+    typedef int VertexId;
+    typedef int SizeT;
+    typedef int Value;
+    struct DataSlice { const unsigned *score; };
+};
+struct ScoreFunctor {
+    static __device__ __forceinline__ unsigned ComputePriorityScore(int v, const ScoreProblem::DataSlice *p) { return p->score[v]; }
+};
+}  // namespace
+
+extern "C" int grb_test_bisect(int device, int64_t nodes, const uint32_t *scores, const int32_t *in_items, int64_t in_len,
+                               int in_is_far, uint32_t lower, uint32_t upper, uint32_t *far_mark /* in/out, (nodes+31)/32 words */,
+                               int32_t *near_out, int64_t near_cap, int64_t *near_len,
+                               int32_t *far_out, int64_t far_cap, int64_t *far_len, uint32_t *min_far_score)
+{
+    using namespace gunrock;
+    if (nodes < 0 || in_len < 0 || near_cap < 0 || far_cap < 0 || !scores || !far_mark) return (int)cudaErrorInvalidValue;
+    int rc = grb_select_device(device);
+    if (rc) return rc;
+    cudaStream_t s = 0;
+    const size_t words = (size_t)(nodes + 31) / 32;
+    util::DeviceArray<unsigned> d_score, d_mark;
+    util::DeviceArray<int> d_in, d_near, d_far;
+    oprtr::WorkProgress wp;
+    oprtr::advance::DeviceInfo dev;
+    GRB_TRY(dev.Query(device));
+    GRB_TRY(wp.Setup(s));
+    GRB_TRY(d_score.FromHost(scores, (size_t)nodes, s));
+    GRB_TRY(d_mark.FromHost(far_mark, words, s));
+    GRB_TRY(d_in.FromHost(in_items, (size_t)in_len, s));
+    GRB_TRY(d_near.Allocate((size_t)near_cap + 1));
+    GRB_TRY(d_far.Allocate((size_t)far_cap + 1));
+    ScoreProblem::DataSlice ds;
+    ds.score = d_score.ptr;
+    priority_queue::BisectArgs<int> a;
+    a.in = d_in.ptr; a.in_len = (unsigned long long)in_len; a.d_in_len = nullptr;
+    a.near_out = d_near.ptr; a.near_cap = (unsigned long long)near_cap;
+    a.far_out = d_far.ptr; a.far_base = 0; a.far_cap = (unsigned long long)far_cap;
+    a.far_mark = d_mark.ptr; a.in_is_far = in_is_far != 0;
+    a.lower = lower; a.upper = upper;
+    a.slots = wp.d_slots.ptr; a.queue_index = 0;
+    GRB_TRY((priority_queue::Bisect<ScoreProblem, ScoreFunctor>(dev.sm_count, ds, a, s)));
+    oprtr::LevelCounters c;
+    GRB_TRY(wp.Fetch(1, c, s));
+    if (near_len) *near_len = c.overflow ? -1 : (int64_t)c.out_len;
+    if (far_len) *far_len = c.overflow ? -1 : (int64_t)c.aux0;
+    if (min_far_score) *min_far_score = c.aux1 ? ~(uint32_t)c.aux1 : 0xffffffffu;
+    if (near_out) GRB_TRY(d_near.ToHost(near_out, (size_t)(c.out_len < (unsigned long long)near_cap ? c.out_len : (unsigned long long)near_cap), s));
+    if (far_out) GRB_TRY(d_far.ToHost(far_out, (size_t)(c.aux0 < (unsigned long long)far_cap ? c.aux0 : (unsigned long long)far_cap), s));
+    GRB_TRY(d_mark.ToHost(far_mark, words, s));
+    GRB_TRY(cudaStreamSynchronize(s));
+    return 0;
+}

@@ -211,6 +211,15 @@ int grb_test_filter(int device, int64_t nodes, int compact,
                     const int32_t *in_queue, int64_t in_len,
                     int32_t *out_queue, int64_t out_cap, int64_t *out_len,
                     int32_t *dst_hits);
+/* The near/far split of the priority queue on its own (priority_queue::Bisect; replaces the reference's
+ * gunrock/priority_queue/kernel.cuh:404-503 Bisect / RemoveInvalid): items whose score (scores[item]) is below
+ * `lower` are dropped, those in [lower, upper) go to near_out, the others to far_out unless their bit in far_mark
+ * is already set (in_is_far = 0) -- or, when the input IS a far pile (in_is_far = 1), leaving items clear their bit.
+ * far_mark is read and written back; min_far_score receives the smallest score sent to the far pile (~0 if none). */
+int grb_test_bisect(int device, int64_t nodes, const uint32_t *scores, const int32_t *in_items, int64_t in_len,
+                    int in_is_far, uint32_t lower, uint32_t upper, uint32_t *far_mark,
+                    int32_t *near_out, int64_t near_cap, int64_t *near_len,
+                    int32_t *far_out, int64_t far_cap, int64_t *far_len, uint32_t *min_far_score);
 
 /* ---- 1D-partitioned BFS, one device per process -----------------------------------
  * No reference counterpart (the reference's multi-GPU path is a TODO,

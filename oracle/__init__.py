@@ -39,6 +39,10 @@ def lib():
         L.orc_market_read.restype = C.c_int
         L.orc_market_read.argtypes = [C.c_char_p, C.c_int, C.c_int, C.c_int, p, p, p, p, p]
         L.orc_free.argtypes = [p]
+        L.orc_csr_cache_write.restype = C.c_int
+        L.orc_csr_cache_write.argtypes = [C.c_char_p, i64, i64, p, p, p]
+        L.orc_csr_cache_read.restype = C.c_int
+        L.orc_csr_cache_read.argtypes = [C.c_char_p, C.c_int, p, p, p, p, p]
         L.orc_random_node.restype = i32
         L.orc_random_node.argtypes = [i32]
         L.orc_largest_degree_node.restype = i32
@@ -116,6 +120,40 @@ def market_read(path, undirected=True, reversed_=False, load_values=True):
     for q in (pr, pc, pv):
         L.orc_free(q)
     ro, co, vo = coo_to_csr(n.value, rows, cols, vals)
+    return n.value, ro, co, vo
+
+
+def csr_cache_name(market_path, undirected=True, reversed_=False, directory=None):
+    """the reference's cache file of a built graph (graphio/market.cuh:312-326): .<name>_{undirected,reversed,
+    nonreversed}_csr next to the .mtx, or in `directory`"""
+    d, f = os.path.split(os.path.abspath(market_path))
+    kind = "undirected" if undirected else ("reversed" if reversed_ else "nonreversed")
+    return os.path.join(directory or d, ".%s_%s_csr" % (f, kind))
+
+
+def csr_cache_write(path, row_offsets, col, values=None):
+    """the reference's text CSR (csr.cuh:140-176)"""
+    ro, co = _offs(row_offsets), _cols(col)
+    v = np.ascontiguousarray(values, dtype=np.int64) if values is not None else None
+    rc = lib().orc_csr_cache_write(os.fsencode(path), ro.size - 1, co.size, _ptr(ro), _ptr(co), _ptr(v))
+    if rc != 0:
+        raise IOError("orc_csr_cache_write(%s) failed: %d" % (path, rc))
+
+
+def csr_cache_read(path, load_values=False):
+    """-> (n, row_offsets int64[n+1], col int32[m], values int64[m] or None) (csr.cuh:182-232)"""
+    L = lib()
+    n, m = C.c_int64(), C.c_int64()
+    pr, pc, pv = C.c_void_p(), C.c_void_p(), C.c_void_p()
+    rc = L.orc_csr_cache_read(os.fsencode(path), int(load_values), C.byref(n), C.byref(m), C.byref(pr), C.byref(pc), C.byref(pv))
+    if rc != 0:
+        raise IOError("orc_csr_cache_read(%s) failed: %d" % (path, rc))
+    ro = np.ctypeslib.as_array(C.cast(pr, C.POINTER(C.c_int64)), shape=(n.value + 1,)).copy()
+    co = np.ctypeslib.as_array(C.cast(pc, C.POINTER(C.c_int32)), shape=(max(m.value, 1),))[:m.value].copy()
+    vo = np.ctypeslib.as_array(C.cast(pv, C.POINTER(C.c_int64)), shape=(max(m.value, 1),))[:m.value].copy() if pv.value else None
+    for q in (pr, pc, pv):
+        if q.value:
+            L.orc_free(q)
     return n.value, ro, co, vo
 
 

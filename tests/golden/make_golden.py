@@ -44,6 +44,20 @@ def main():
             np.savez_compressed(out, n=np.int64(n), row_offsets=ro.astype(np.int32), col=col,
                                 vals=vals if vals is not None else np.zeros(0, np.int32))
             print(out, n, col.size)
+    # the text cache of the built CSR, written by the reference's own Csr::WriteToFile (gunrock/csr.cuh:140-176) next to
+    # a scratch copy of the .mtx (graphio/market.cuh:254-326)
+    import shutil
+    import tempfile
+    cdir = os.path.join(HERE, "csr_cache")
+    os.makedirs(cdir, exist_ok=True)
+    with tempfile.TemporaryDirectory() as tmp:
+        for name in ("test_pr", "test_cc", "test_bc"):
+            mtx = os.path.join(tmp, name + ".mtx")
+            shutil.copy(os.path.join(REF, FIXTURES[name]), mtx)
+            for undirected, kind in ((1, "undirected"), (0, "nonreversed")):
+                subprocess.check_call([oracle.REF_GRAPHIO, "market", mtx, str(undirected), os.path.join(tmp, "out.bin")],
+                                      stdout=subprocess.DEVNULL)
+                shutil.copy(os.path.join(tmp, ".%s.mtx_%s_csr" % (name, kind)), os.path.join(cdir, "%s.mtx_%s_csr" % (name, kind)))
     draws = {}
     for n in (7, 7135):
         o = subprocess.check_output([oracle.REF_GRAPHIO, "randomnode", str(n), "8"]).decode().split()

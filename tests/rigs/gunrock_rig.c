@@ -7,6 +7,9 @@
  *   --device=<n>  --undirected  --src=<id|randomize|largestdegree>  --quick[=<0|1>]  --v
  *   --iteration-num=<n>  --idempotence[=<0|1>]  --mark-pred  --queue-sizing=<f>
  *   --traversal-mode=<0|1|2>  --delta-factor=<n> (sssp)  --delta=<f> --error=<f> --max-iter=<n> (pr)
+ *   --csr-cache-dir=<dir>   keep / reuse the reference's text cache of the built CSR (.<file>_undirected_csr /
+ *                           _nonreversed_csr, gunrock/csr.cuh:140-232, graphio/market.cuh:254-262,312-326) in <dir>
+ *                           (the reference writes it next to the .mtx; a scratch directory here)
  *
  * TEST INFRASTRUCTURE, not product: the graph is loaded by the oracle's restatement of the
  * reference reader (graphio/market.cuh:139-183, csr.cuh:247-340), the GPU side runs through the
@@ -39,6 +42,9 @@ int64_t orc_cc(int64_t n, const eid_t *ro, const vid_t *col, vid_t *labels);
 int     orc_pagerank(int64_t n, const eid_t *ro, const vid_t *col, double delta, double threshold, int max_iter,
                      vid_t src, double *rank);
 void    orc_free(void *p);
+int     orc_csr_cache_write(const char *path, int64_t n, int64_t m, const eid_t *row_offsets, const vid_t *col, const int64_t *vals);
+int     orc_csr_cache_read(const char *path, int load_values, int64_t *n_out, int64_t *m_out, eid_t **row_offsets, vid_t **col,
+                           int64_t **vals);
 double  orc_now_seconds(void);
 
 static const char *opt_value(int argc, char **argv, const char *name)
@@ -101,21 +107,43 @@ int main(int argc, char **argv)
     const int want_weights = strcmp(prim, "sssp") == 0;
     if (strcmp(gtype, "market") == 0) {
         if (argc < 4) { usage(); return 1; }
-        int64_t ncoo = 0, *vals = NULL;
-        vid_t *rows = NULL, *cols = NULL;
-        if (orc_market_read(argv[3], undirected || is_dobfs, 0, want_weights, &n, &ncoo, &rows, &cols, &vals)) {
-            fprintf(stderr, "cannot read %s\n", argv[3]);
-            return 1;
+        const int sym_read = undirected || is_dobfs;
+        /* the reference's cache of the built CSR (market.cuh:254-262: read it if it is there, else build and write it) */
+        char cache[1024];
+        cache[0] = 0;
+        const char *cdir = opt_value(argc, argv, "csr-cache-dir");
+        if (cdir && cdir[0]) {
+            const char *base = strrchr(argv[3], '/');
+            base = base ? base + 1 : argv[3];
+            snprintf(cache, sizeof(cache), "%s/.%s_%s_csr", cdir, base, sym_read ? "undirected" : "nonreversed");
         }
-        ro = (eid_t *)malloc(sizeof(eid_t) * (size_t)(n + 1));
-        co = (vid_t *)malloc(sizeof(vid_t) * (size_t)(ncoo > 0 ? ncoo : 1));
-        int64_t *vo = want_weights ? (int64_t *)malloc(sizeof(int64_t) * (size_t)(ncoo > 0 ? ncoo : 1)) : NULL;
-        m = orc_coo_to_csr(n, ncoo, rows, cols, vals, ro, co, vo);
-        if (want_weights) {
-            w = (uint32_t *)malloc(sizeof(uint32_t) * (size_t)(m > 0 ? m : 1));
-            for (int64_t e = 0; e < m; ++e) w[e] = vals ? (uint32_t)vo[e] : 1u;
+        int64_t *cv = NULL;
+        if (cache[0] && orc_csr_cache_read(cache, want_weights, &n, &m, &ro, &co, &cv) == 0) {
+            printf("  Reading directly from previously stored CSR arrays ...\n");
+            if (want_weights) {
+                w = (uint32_t *)malloc(sizeof(uint32_t) * (size_t)(m > 0 ? m : 1));
+                for (int64_t e = 0; e < m; ++e) w[e] = cv ? (uint32_t)cv[e] : 1u;
+            }
+            orc_free(cv);
+        } else {
+            int64_t ncoo = 0, *vals = NULL;
+            vid_t *rows = NULL, *cols = NULL;
+            if (orc_market_read(argv[3], sym_read, 0, want_weights, &n, &ncoo, &rows, &cols, &vals)) {
+                fprintf(stderr, "cannot read %s\n", argv[3]);
+                return 1;
+            }
+            ro = (eid_t *)malloc(sizeof(eid_t) * (size_t)(n + 1));
+            co = (vid_t *)malloc(sizeof(vid_t) * (size_t)(ncoo > 0 ? ncoo : 1));
+            int64_t *vo = want_weights ? (int64_t *)malloc(sizeof(int64_t) * (size_t)(ncoo > 0 ? ncoo : 1)) : NULL;
+            m = orc_coo_to_csr(n, ncoo, rows, cols, vals, ro, co, vo);
+            if (want_weights) {
+                w = (uint32_t *)malloc(sizeof(uint32_t) * (size_t)(m > 0 ? m : 1));
+                for (int64_t e = 0; e < m; ++e) w[e] = vals ? (uint32_t)vo[e] : 1u;
+            }
+            if (cache[0] && orc_csr_cache_write(cache, n, m, ro, co, want_weights ? vo : NULL) == 0)
+                printf("  Stored the CSR arrays in %s\n", cache);
+            orc_free(rows); orc_free(cols); orc_free(vals); free(vo);
         }
-        orc_free(rows); orc_free(cols); orc_free(vals); free(vo);
     } else if (strcmp(gtype, "rmat") == 0) {
         const int scale = opt_flag(argc, argv, "rmat_scale", 10);
         const int ef = opt_flag(argc, argv, "rmat_edgefactor", 16);

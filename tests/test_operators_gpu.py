@@ -212,3 +212,72 @@ def test_filter_identity_frontier_and_overflow(gr):
     assert np.array_equal(np.sort(out), np.arange(0, n, 2)) and dh.sum() == n // 2
     _, out_len, _ = run_filter(gr, n, 1, np.arange(n), 10)
     assert out_len == -1
+
+
+# ---- priority queue: the near/far split stand-alone (reference: gunrock/priority_queue/kernel.cuh:404-503) ----------
+def run_bisect(gr, n, scores, items, in_is_far, lower, upper, mark, cap=None):
+    import ctypes as C
+    from gunrockinst_b200 import _capi
+    items = np.ascontiguousarray(items, dtype=np.int32)
+    scores = np.ascontiguousarray(scores, dtype=np.uint32)
+    mark = np.ascontiguousarray(mark, dtype=np.uint32).copy()
+    cap = items.size + 4 if cap is None else cap
+    near = np.empty(cap + 1, dtype=np.int32)
+    far = np.empty(cap + 1, dtype=np.int32)
+    nl, fl, mf = C.c_int64(), C.c_int64(), C.c_uint32()
+    rc = _capi.lib().grb_test_bisect(0, n, scores.ctypes.data_as(C.c_void_p), items.ctypes.data_as(C.c_void_p), items.size,
+                                     int(in_is_far), lower, upper, mark.ctypes.data_as(C.c_void_p),
+                                     near.ctypes.data_as(C.c_void_p), cap, C.byref(nl),
+                                     far.ctypes.data_as(C.c_void_p), cap, C.byref(fl), C.byref(mf))
+    assert rc == 0
+    return near[:max(nl.value, 0)], nl.value, far[:max(fl.value, 0)], fl.value, mark, mf.value
+
+
+@pytest.mark.parametrize("size", [0, 1, 1023, 1024, 50000])
+@pytest.mark.parametrize("in_is_far", [False, True])
+def test_near_far_split_contract(gr, size, in_is_far):
+    n = 7000
+    rng = np.random.RandomState(31 * size + int(in_is_far))
+    scores = rng.randint(0, 100, n).astype(np.uint32)
+    lower, upper = 20, 60
+    words = (n + 31) // 32
+    if in_is_far:
+        # the input is a far pile: distinct members, all marked; holes (-1) left by earlier splits
+        items = rng.permutation(n)[:size].astype(np.int32)
+        mark = np.zeros(words, np.uint32)
+        np.bitwise_or.at(mark, items >> 5, (np.uint32(1) << (items & 31).astype(np.uint32)))
+        if size > 10:
+            items[rng.randint(0, size, size // 10)] = -1
+    else:
+        # a frontier with duplicates and holes; some vertices already sit in the far pile
+        items = rng.randint(-1, n, size).astype(np.int32)
+        already = rng.permutation(n)[:n // 5]
+        mark = np.zeros(words, np.uint32)
+        np.bitwise_or.at(mark, already >> 5, (np.uint32(1) << (already & 31).astype(np.uint32)))
+    mark0 = mark.copy()
+    near, nl, far, fl, mark_after, min_far = run_bisect(gr, n, scores, items, in_is_far, lower, upper, mark)
+    live = items[items >= 0]
+    sc = scores[live]
+    want_near = live[(sc >= lower) & (sc < upper)]
+    marked0 = ((mark0[live >> 5] >> (live & 31).astype(np.uint32)) & 1).astype(bool)
+    far_cands = live[sc >= upper]
+    if in_is_far:
+        want_far = far_cands                                    # stays in the pile
+        want_mark = mark0.copy()                                # ... and every item that left it clears its bit
+        gone = live[sc < upper]
+        np.bitwise_and.at(want_mark, gone >> 5, ~(np.uint32(1) << (gone & 31).astype(np.uint32)))
+    else:
+        want_far = np.unique(far_cands[~marked0[sc >= upper]])  # one copy of every vertex not in the pile yet
+        want_mark = mark0.copy()
+        np.bitwise_or.at(want_mark, want_far >> 5, (np.uint32(1) << (want_far & 31).astype(np.uint32)))
+    assert nl == want_near.size and np.array_equal(np.sort(near), np.sort(want_near))
+    assert fl == want_far.size and np.array_equal(np.sort(far), np.sort(want_far))
+    assert np.array_equal(mark_after, want_mark)
+    assert min_far == (int(scores[want_far].min()) if want_far.size else 0xFFFFFFFF)
+
+
+def test_near_far_split_reports_overflow(gr):
+    n = 4000
+    scores = np.full(n, 5, np.uint32)
+    _, nl, _, fl, _, _ = run_bisect(gr, n, scores, np.arange(n), False, 0, 10, np.zeros((n + 31) // 32, np.uint32), cap=100)
+    assert nl == -1

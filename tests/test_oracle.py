@@ -197,3 +197,21 @@ def test_bc_and_topk_goldens():
     assert np.allclose(oracle.bc(pro, pco, -1)[0], [0, 3, 4, 3, 0])
     ids, ind, outd = oracle.topk([0, 3, 6, 9, 11, 14, 15, 15], [0, 1, 2, 5, 7, 9, 12, 15], 3)
     assert ids.tolist() == [2, 4, 0] and ind.tolist() == [3, 2, 1] and outd.tolist() == [3, 3, 3]
+
+
+# ---- the reference's text cache of a built CSR (gunrock/csr.cuh:140-232) -------------------------------------------
+@pytest.mark.parametrize("name", ["test_pr", "test_cc", "test_bc"])
+@pytest.mark.parametrize("kind", ["undirected", "nonreversed"])
+def test_csr_cache_matches_reference_writer(orc, tmp_path, name, kind):
+    """tests/golden/csr_cache/* were written by the reference's own Csr::WriteToFile (make_golden.py): the restated writer
+    reproduces them byte for byte, the restated reader returns the CSR the reference built"""
+    golden = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "csr_cache", "%s.mtx_%s_csr" % (name, kind))
+    n, ro, co, vals = load_golden(name + ("" if kind == "undirected" else "_dir"))
+    n2, ro2, co2, v2 = orc.csr_cache_read(golden, load_values=True)
+    assert n2 == n and np.array_equal(ro2, ro) and np.array_equal(co2, co) and np.array_equal(v2, vals)
+    out = tmp_path / "cache"
+    orc.csr_cache_write(str(out), ro, co, vals)
+    assert out.read_bytes() == open(golden, "rb").read()
+    assert os.path.basename(orc.csr_cache_name("/x/%s.mtx" % name, kind == "undirected")) == ".%s.mtx_%s_csr" % (name, kind)
+    _, _, _, none = orc.csr_cache_read(golden, load_values=False)
+    assert none is None

@@ -73,3 +73,17 @@ def test_edge_cases(gr, orc):
     for ro, co in [([0, 0], []), ([0, 0, 0, 0], []), ([0, 1, 2, 2], [1, 0]), ([0, 1, 1], [1])]:
         ro, co = np.array(ro), np.array(co, dtype=np.int32)
         _check(gr, orc, ro, co, False)
+
+
+def test_rmat_scale22_to_convergence(gr, orc):
+    """BASELINE configs[1]'s graph, run to convergence (threshold 1e-6, ~130 sweeps): same sweep count as the fp64
+    restatement and every vertex within 1e-6 of its own value.  The graph comes from the
+    device generator (the same seeded CSR oracle.rmat_csr builds in minutes on one core)."""
+    g = gr.Graph.rmat(22)
+    ro, co = g.download()
+    ranks, _, st = gr.pagerank(g, delta=0.85, threshold=1e-6, max_iter=1000)
+    g.close()
+    want, it = orc.pagerank(ro, co, 0.85, 1e-6, 1000, -1)
+    assert st["iterations"] == it and it > 50
+    assert_per_vertex(ranks, want)
+    assert abs(float(ranks.sum()) - float(want.sum())) <= 1e-9 * float(want.sum())

@@ -71,3 +71,29 @@ def test_rig_directed_market_bfs(tmp_path):
     _write_mtx(path, 6, [(0, 1), (1, 2), (2, 3), (4, 5)])
     p = subprocess.run([RIG, "bfs", "market", path, "--src=3"], capture_output=True, text=True, timeout=120)
     assert p.returncode == 0 and "Label Validity: CORRECT" in p.stdout, p.stdout + p.stderr
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("prim,flags", [("bfs", ["--undirected"]), ("sssp", ["--undirected"]), ("bfs", [])])
+def test_rig_csr_cache(tmp_path, prim, flags):
+    """--csr-cache-dir: the first run stores the reference's text cache of the built CSR (csr.cuh:140-176), the second one
+    reads it instead of the .mtx (csr.cuh:182-232) -- same graph, same validated result"""
+    _build()
+    rng = np.random.RandomState(11)
+    n = 300
+    edges = [(int(a), int(b)) for a, b in rng.randint(0, n, size=(1500, 2))]
+    vals = [int(v) for v in rng.randint(1, 65, size=len(edges))]
+    path = str(tmp_path / "g.mtx")
+    _write_mtx(path, n, edges, vals if prim == "sssp" else None)
+    cdir = str(tmp_path / "cache")
+    os.makedirs(cdir)
+    cmd = [RIG, prim, "market", path, "--src=1", "--csr-cache-dir=" + cdir] + flags
+    a = subprocess.run(cmd, capture_output=True, text=True, timeout=120)
+    assert a.returncode == 0 and "Stored the CSR arrays" in a.stdout and "TEST PASSED" in a.stdout, a.stdout + a.stderr
+    name = ".g.mtx_%s_csr" % ("undirected" if flags else "nonreversed")
+    assert os.path.exists(os.path.join(cdir, name))
+    os.rename(path, path + ".gone")                             # the second run cannot fall back to the .mtx
+    b = subprocess.run(cmd, capture_output=True, text=True, timeout=120)
+    assert b.returncode == 0 and "Reading directly from previously stored CSR arrays" in b.stdout and "TEST PASSED" in b.stdout, b.stdout + b.stderr
+    line = [l for l in a.stdout.splitlines() if l.startswith("market graph:")]
+    assert line and line == [l for l in b.stdout.splitlines() if l.startswith("market graph:")]

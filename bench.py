@@ -470,10 +470,12 @@ def run_single(args):
         b.close()
         return top
     operators = {
-        "advance_lb": best_launch(dict(traversal_mode=1), ("push-lb", "push-stream"), lambda r: level_bytes(r, osz, n)),
+        "advance_lb": best_launch(dict(traversal_mode=1, degree_order=True), ("push-lb", "push-stream"), lambda r: level_bytes(r, osz, n)),
         "filter": best_launch(dict(idempotence=True), ("filter", "filter-stream"), lambda r: 5 * r["frontier"] + 4 * r["discovered"]),
         "note": "largest launch of each operator in a top-down / an idempotent search from sources[0]; algorithmic "
-                "bytes as in DESIGN.md section 3 (advance: F(4+2o)+5E+8D, filter: 5 in + 4 out)",
+                "bytes as in DESIGN.md section 3 (advance: F(4+2o)+5E+8D, filter: 5 in + 4 out).  The advance runs on the "
+                "degree-ordered twin of the graph (grb_bfs_config.degree_order) and its time covers the whole level: degree "
+                "scan, mask snapshot, StreamExpandKernel and HarvestKernel when `kernel` is push-stream",
     }
 
     # ---- end to end through the reference's entry point, CSR in pinned host memory
@@ -580,6 +582,9 @@ def main():
                          "PageRank, scale-24 SSSP, each with its oracle check: several minutes)")
     ap.add_argument("--exchange", default="peer", choices=["peer", "nccl"],
                     help="partitioned runs: peer-memory stores over NVLink (default) or NCCL collectives")
+    ap.add_argument("--mg-persistent", action="store_true",
+                    help="partitioned runs: the whole search as one cooperative kernel per device (mgbfs_persistent.cuh) "
+                         "instead of the host-driven level loop")
     ap.add_argument("--no-single-ref", action="store_true",
                     help="partitioned runs: skip the single-device search of the same graph on rank 0 (reference point + parity)")
     ap.add_argument("--partitioned", action="store_true",
@@ -588,6 +593,8 @@ def main():
     if args.synthesize:
         synthesize(int(args.synthesize[0]), args.synthesize[1])
         return
+    if args.mg_persistent:
+        os.environ["GRB_MG_PERSISTENT"] = "1"
     world = env_int("WORLD_SIZE", 1)
     rank = env_int("RANK", 0)
     if world > 1:

@@ -28,6 +28,7 @@
 #include <vector>
 #include "bfs_enactor.cuh"
 #include "mgbfs_p2p.cuh"
+#include "mgbfs_persistent.cuh"
 
 namespace gunrock {
 namespace app {
@@ -263,6 +264,18 @@ class MGBFSEnactor : public EnactorBase {
     util::PinnedArray<unsigned long long> h_status;
     unsigned long long epoch = 0, bar_count = 0, global_edges = 0;
     bool p2p_ready = false;
+    // the whole search as one cooperative kernel per device (mgbfs_persistent.cuh)
+    static const int kMaxRecords = 128;
+    util::DeviceArray<oprtr::LevelCounters> d_all;
+    util::DeviceArray<unsigned long long>   d_status;
+    util::DeviceArray<MgLevelRecord>        d_records;
+    util::DeviceArray<MgPersistentSummary>  d_summary;
+    util::PinnedArray<MgLevelRecord>        h_records;
+    util::PinnedArray<MgPersistentSummary>  h_mg_summary;
+    bool persistent_ok = false;
+    int  persistent_grid = 0;
+    typedef void (*PersistentFn)(const DataSlice, const MgPersistentParams<VertexId, SizeT>);
+    static PersistentFn PersistentEntry() { return MgPersistentKernel<AdvancePolicy, PullPolicy, Problem, PushFunctor, PullFunctor>; }
     std::vector<LevelTrace> trace;
     std::vector<cudaEvent_t> events;
 
@@ -288,6 +301,22 @@ class MGBFSEnactor : public EnactorBase {
         peers.recv[r] = problem->recv_map.ptr;
         epoch = bar_count = 0;
         p2p_ready = (peers.parts == 1);
+        GR_TRY(d_all.Allocate(kMaxPeers));
+        GR_TRY(d_status.Allocate(1));
+        GR_TRY(d_records.Allocate(kMaxRecords));
+        GR_TRY(d_summary.Allocate(1));
+        GR_TRY(h_records.Allocate(kMaxRecords));
+        GR_TRY(h_mg_summary.Allocate(1));
+        int coop = 0, per_sm = 0;
+        GR_TRY(cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, dev.device));
+        GR_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, PersistentEntry(), AdvancePolicy::THREADS, 0));
+        if (per_sm > kMgPersistentCtasPerSm) per_sm = kMgPersistentCtasPerSm;
+        // opt-in (GRB_MG_PERSISTENT=1, bench.py --mg-persistent): measured against the host loop below it saves the host
+        // round trip of a level (~15 us) but runs the pull sweep inside a kernel that is register-bound for every phase at
+        // once -- slower on one device at scale 24 (1.06 against 0.70 ms per search), see DESIGN.md section 5
+        const char *pe = getenv("GRB_MG_PERSISTENT");
+        persistent_ok = coop != 0 && per_sm > 0 && pe && pe[0] == '1';
+        persistent_grid = per_sm * dev.sm_count;
         return cudaStreamSynchronize(stream);
     }
 
@@ -333,6 +362,89 @@ class MGBFSEnactor : public EnactorBase {
     }
     void DestroyEvents() { for (cudaEvent_t e : events) cudaEventDestroy(e); events.clear(); }
 
+    // the search as one cooperative kernel (the reset and the seeding of the counters have been issued on the stream)
+    cudaError_t RunPersistent(Problem *problem, bool dopt, double alpha, double beta, bool record, cudaEvent_t ev_start,
+                              size_t &used, SearchStats *out)
+    {
+        typename Problem::Base::Graph &g = *problem->graph;
+        GR_TRY(d_status.Zero(stream));
+        MgPersistentParams<VertexId, SizeT> P;
+        P.g = g.View(); P.ginv = g.InverseView();
+        P.fwd_row_offsets = g.symmetric ? nullptr : g.row_offsets.ptr;
+        for (int i = 0; i < 2; ++i) {
+            P.queues[i] = problem->frontier_queues[i].ptr; P.queue_cap[i] = problem->frontier_elements[i];
+            P.frontier_map[i] = problem->frontier_map[i].ptr;
+        }
+        P.visited = problem->visited_mask.ptr; P.next_map = problem->next_map.ptr; P.recv_map = problem->recv_map.ptr;
+        P.candidates = problem->candidates.ptr; P.head = problem->head.ptr;
+        P.scratch.scanned = lb_scratch.scanned.ptr; P.scratch.row_start = lb_scratch.row_start.ptr;
+        P.scratch.tile_desc = lb_scratch.tile_desc.ptr; P.scratch.part_start = lb_scratch.part_start.ptr;
+        P.scratch.ticket = lb_scratch.ticket.ptr; P.scratch.part_cap = lb_scratch.part_start.cap;
+        P.scratch.epoch = lb_scratch.epoch;
+        P.slots = work_progress.d_slots.ptr;
+        P.peers = peers;
+        P.all = d_all.ptr; P.status = d_status.ptr; P.sent_words = sent_words.ptr;
+        P.records = d_records.ptr; P.max_records = record ? kMaxRecords : 0;
+        P.summary = d_summary.ptr;
+        P.mailbox_epoch = epoch; P.barrier_count = bar_count; P.budget_ns = PeerComm::BudgetFromEnv();
+        P.global_edges = global_edges; P.seg_words = SegWords(problem);
+        P.desc_words = (unsigned long long)lb_scratch.tile_desc.size;
+        P.dopt = dopt ? 1 : 0; P.in_sel = 0;
+        P.alpha = alpha; P.beta = beta; P.lb_min_edges = 4096;
+        DataSlice ds = problem->MakeDataSlice(0);
+        void *kargs[] = {(void *)&ds, (void *)&P};
+        cudaError_t le = getenv("GRB_FAIL_COOP_LAUNCH") ? cudaErrorCooperativeLaunchTooLarge
+                         : cudaLaunchCooperativeKernel((const void *)PersistentEntry(), dim3((unsigned)persistent_grid),
+                                                       dim3(AdvancePolicy::THREADS), kargs, 0, stream);
+        if (le != cudaSuccess) {
+            (void)cudaGetLastError();
+            persistent_ok = false;
+            fprintf(stderr, "libgunrock (B200 build): cooperative launch of the partitioned BFS kernel failed (%s); "
+                            "using the host-driven level loop\n", cudaGetErrorString(le));
+            return cudaErrorCooperativeLaunchTooLarge;
+        }
+        ++enactor_stats.launches;
+        GR_TRY(cudaMemcpyAsync(h_mg_summary.ptr, d_summary.ptr, sizeof(MgPersistentSummary), cudaMemcpyDeviceToHost, stream));
+        if (record)
+            GR_TRY(cudaMemcpyAsync(h_records.ptr, d_records.ptr, sizeof(MgLevelRecord) * kMaxRecords, cudaMemcpyDeviceToHost, stream));
+        cudaEvent_t ev_end = Mark(used);
+        GR_TRY(cudaEventSynchronize(ev_end));
+        const MgPersistentSummary &sum = *h_mg_summary.ptr;
+        epoch = sum.mailbox_epoch; bar_count = sum.barrier_count;
+        lb_scratch.epoch = (unsigned)sum.lb_epoch_end;
+        in_sel = (int)sum.in_sel;
+        if (sum.error == 1)
+            return util::GRError(cudaErrorLaunchTimeout, "peer exchange timed out (a peer stopped or the ranks diverged)", __FILE__, __LINE__);
+        if (sum.error)
+            return util::GRError(cudaErrorInvalidConfiguration, "frontier queue overflow on a partitioned level", __FILE__, __LINE__);
+        if (record) {
+            unsigned long long sent_before = 0;
+            const unsigned long long gather = 4ull * SegWords(problem) * (unsigned long long)(peers.parts - 1);
+            bool was_pull = false;
+            for (unsigned long long i = 0; i < sum.levels && i < (unsigned long long)kMaxRecords; ++i) {
+                const MgLevelRecord &r = h_records.ptr[i];
+                LevelTrace t;
+                t.level = r.level; t.kind = r.kind; t.frontier = r.frontier; t.discovered = r.discovered; t.edges = r.edges;
+                t.max_edges = r.max_edges; t.candidates = r.candidates;
+                t.exchange_bytes = r.kind ? gather * (was_pull ? 1ull : 2ull) : 4ull * (r.sent_words - sent_before);
+                if (peers.parts == 1) t.exchange_bytes = 0;
+                sent_before = r.sent_words;
+                was_pull = r.kind != 0;
+                t.compute_ms = (float)((double)r.ns_compute * 1e-6); t.exchange_ms = (float)((double)r.ns_exchange * 1e-6);
+                trace.push_back(t);
+            }
+        }
+        float ms = 0;
+        cudaEventElapsedTime(&ms, ev_start, ev_end);
+        if (out) {
+            out->elapsed_ms = ms; out->iterations = (long long)sum.levels; out->push_levels = (long long)sum.push_levels;
+            out->pull_levels = (long long)sum.pull_levels; out->launches = enactor_stats.launches;
+            out->edges_visited = sum.edges_visited; out->edges_inspected = sum.edges_inspected;
+            out->exchange_bytes = peers.parts > 1 ? sum.gather_bytes : 0; out->nodes_visited = sum.nodes_visited;
+        }
+        return cudaSuccess;
+    }
+
     // One direction-optimising search; every rank calls it with the same arguments.  The direction
     // rule is the one of BFSEnactor (Beamer's alpha / beta on global frontier figures).
     cudaError_t RunPeer(Problem *problem, VertexId src, bool dopt, double alpha, double beta, bool record, SearchStats *out)
@@ -366,6 +478,13 @@ class MGBFSEnactor : public EnactorBase {
             SeedCountersKernel<SizeT><<<1, 1, 0, stream>>>(Counters(), g.row_offsets.ptr, mine ? (long long)g.part.Local(src) : -1ll);
             GR_TRY(cudaGetLastError());
             enactor_stats.launches += 2;
+        }
+        if (persistent_ok) {
+            cudaError_t pe = RunPersistent(problem, dopt, alpha, beta, record, ev_start, used, out);
+            if (pe != cudaErrorCooperativeLaunchTooLarge) return pe;
+            // co-residency is not available after all: the host loop below runs this and every later search.  (Every
+            // device takes this branch or none: the launch fails for a reason all devices of a box share, and a device
+            // that went ahead alone would time out at its first exchange.)
         }
         GR_TRY(ExchangeCounters());
 

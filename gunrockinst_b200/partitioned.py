@@ -758,6 +758,8 @@ def bench(args, rank, world, workload_config, ClockSampler, pick_sources, measur
             value = edges / (ms * 1e-3) / 1e9
             cfg = workload_config(args, scale, eng.nodes, m_global)
             cfg["partition"] = "1D, owner = low bits XOR hash(local row), %d devices" % world
+            cfg["level_loop"] = ("one cooperative kernel per device (mgbfs_persistent.cuh)" if os.environ.get("GRB_MG_PERSISTENT") == "1"
+                                 else "host-driven (MGBFSEnactor::RunPeer)")
             cfg["exchange"] = ("push: all_to_all of the discovery bitmap; pull: all_gather of the frontier bitmap (NCCL)"
                                if exchange == "nccl" else
                                "peer memory over NVLink (CUDA IPC): pull sweeps store their frontier words on every device, "

@@ -16,11 +16,19 @@ pytestmark = pytest.mark.gpu
 
 @pytest.mark.parametrize("scale", [10, 16])
 @pytest.mark.parametrize("dopt", [False, True])
-@pytest.mark.parametrize("exchange", ["nccl", "peer"])
-def test_world1_matches_oracle(gr, orc, scale, dopt, exchange):
+@pytest.mark.parametrize("exchange", ["nccl", "peer", "peer-persistent"])
+def test_world1_matches_oracle(gr, orc, scale, dopt, exchange, monkeypatch):
+    """"peer-persistent": the whole search as one cooperative kernel (mgbfs_persistent.cuh, GRB_MG_PERSISTENT=1)"""
     from gunrockinst_b200 import partitioned as pt
     ro, co = rmat_graph(orc, scale)
     g = gr.Graph.from_csr(ro, co, symmetric=True)
+    if exchange == "peer-persistent":
+        monkeypatch.setenv("GRB_MG_PERSISTENT", "1")
+        exchange = "peer"
+        persistent = True
+    else:
+        monkeypatch.delenv("GRB_MG_PERSISTENT", raising=False)
+        persistent = False
     eng = pt.DeviceEngine(g)
     bfs = pt.PartitionedBfs(eng, direction_optimized=dopt, exchange=exchange)
     for src in (0, 3, ro.size - 2):
@@ -30,6 +38,8 @@ def test_world1_matches_oracle(gr, orc, scale, dopt, exchange):
         assert st["edges_visited"] == orc.edges_visited(ro, want)
         if dopt and scale >= 16 and src == 0:
             assert any(lv["kind"] == "pull" for lv in st["levels"])
+        if persistent:
+            assert st["gpu_launches"] <= 3             # two seeding kernels + the search
     eng.close()
 
 
@@ -56,18 +66,23 @@ def _worker(rank, world, port, scale, q):
         lp = world.bit_length() - 1
         g = gr.Graph.rmat(scale, 16, device=rank, log_parts=lp, rank=rank)
         eng = pt.DeviceEngine(g)
+        os.environ["GRB_MG_PERSISTENT"] = "1"                   # read when the context is created
+        eng_p = pt.DeviceEngine(g)                              # the search as one cooperative kernel per device
+        os.environ.pop("GRB_MG_PERSISTENT")
         ro, co = oracle.rmat_csr(scale, 16)
         res = []
-        for exchange in ("nccl", "peer", "nccl", "peer"):       # alternating: either path starts from the other's leftovers
+        for e, exchange in ((eng, "nccl"), (eng, "peer"), (eng_p, "peer"), (eng, "nccl"), (eng, "peer"), (eng_p, "peer")):
+            # alternating: either path starts from the other's leftovers
             for dopt in (True, False):
-                bfs = pt.PartitionedBfs(eng, direction_optimized=dopt, exchange=exchange)
+                bfs = pt.PartitionedBfs(e, direction_optimized=dopt, exchange=exchange)
                 for src in (0, 1, 12345 % (1 << scale)):
                     st = bfs.run(src)
-                    labels = pt.gather_labels(eng)
+                    labels = pt.gather_labels(e)
                     want = oracle.bfs(ro, co, src)
                     res.append((bool(np.array_equal(labels, want)),
                                 st["edges_visited"] == oracle.edges_visited(ro, want),
-                                st["exchange_bytes"] > 0))
+                                st["exchange_bytes"] > 0,
+                                e is not eng_p or st["gpu_launches"] <= 3))
         if rank == 0:
             q.put(res)
     finally:

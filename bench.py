@@ -444,6 +444,9 @@ def run_single(args):
     roofline = {"bound": "hbm", "kernel": kernel_names.get(dom, dom), "achieved": achieved, "peak": peak,
                 "unit": "GB/s", "frac": achieved / peak, "peak_source": peak_src,
                 "traffic": ncu_traffic(dom)[0], "traffic_source": ncu_traffic(dom)[1],
+                "traffic_note": "ncu capture of the launches of ONE search (source 0), per launch; algo_bytes_per_launch beside "
+                                "it is the mean over the launches of every timed source: compare each with its own duration, "
+                                "not with each other",
                 "launches_timed": agg[dom]["launches"],
                 "avg_launch_us": 1e3 * agg[dom]["ms"] / max(agg[dom]["launches"], 1),
                 "algo_bytes_per_launch": agg[dom]["bytes"] / max(agg[dom]["launches"], 1),

@@ -41,6 +41,12 @@ __device__ __forceinline__ void MbarArriveOnCpAsync(unsigned long long *bar)
 {
     asm volatile("cp.async.mbarrier.arrive.noinc.shared::cta.b64 [%0];" :: "r"(SharedAddr(bar)) : "memory");
 }
+// as MbarArriveOnCpAsync, for a thread that is NOT one of the arrivals the barrier was initialised with: the pending count
+// goes up by one now and down by one when the thread's cp.asyncs have landed, so the phase cannot complete before that
+__device__ __forceinline__ void MbarJoinOnCpAsync(unsigned long long *bar)
+{
+    asm volatile("cp.async.mbarrier.arrive.shared::cta.b64 [%0];" :: "r"(SharedAddr(bar)) : "memory");
+}
 __device__ __forceinline__ bool MbarTryWait(unsigned long long *bar, unsigned parity)
 {
     unsigned ok;

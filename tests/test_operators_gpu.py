@@ -246,8 +246,8 @@ def test_near_far_split_contract(gr, size, in_is_far):
         items = rng.permutation(n)[:size].astype(np.int32)
         mark = np.zeros(words, np.uint32)
         np.bitwise_or.at(mark, items >> 5, (np.uint32(1) << (items & 31).astype(np.uint32)))
-        if size > 10:
-            items[rng.randint(0, size, size // 10)] = -1
+        if items.size > 10:
+            items[rng.randint(0, items.size, items.size // 10)] = -1
     else:
         # a frontier with duplicates and holes; some vertices already sit in the far pile
         items = rng.randint(-1, n, size).astype(np.int32)

@@ -588,6 +588,8 @@ def main():
     ap.add_argument("--mg-persistent", action="store_true",
                     help="partitioned runs: the whole search as one cooperative kernel per device (mgbfs_persistent.cuh) "
                          "instead of the host-driven level loop")
+    ap.add_argument("--no-e2e-from-host", action="store_true",
+                    help="partitioned runs: skip the end-to-end figure that uploads every rank's slice from host memory")
     ap.add_argument("--no-single-ref", action="store_true",
                     help="partitioned runs: skip the single-device search of the same graph on rank 0 (reference point + parity)")
     ap.add_argument("--partitioned", action="store_true",

@@ -69,6 +69,21 @@ class Graph:
         return g
 
     @classmethod
+    def from_slice(cls, row_offsets, col_indices, global_nodes, log_parts, rank, weights=None, symmetric=True, device=0):
+        """one rank's slice of a 1D-partitioned graph from host arrays (local rows, global neighbour ids): the arrays
+        Graph.rmat(..., log_parts, rank).download() returns"""
+        ro = np.ascontiguousarray(row_offsets)
+        if ro.dtype not in (np.int32, np.int64):
+            ro = ro.astype(np.int64)
+        co = np.ascontiguousarray(col_indices, dtype=np.int32)
+        w = np.ascontiguousarray(weights, dtype=np.uint32) if weights is not None else None
+        h = C.c_void_p()
+        _capi.check(_capi.lib().grb_graph_slice_from_host(
+            device, int(global_nodes), int(log_parts), int(rank), ro.size - 1, co.size, _ptr(ro), ro.dtype.itemsize,
+            _ptr(co), _ptr(w), int(bool(symmetric)), 0, C.byref(h)), "grb_graph_slice_from_host")
+        return cls(h)
+
+    @classmethod
     def rmat(cls, scale, edgefactor=16, seed=None, undirected=True, abcd=RMAT_ABCD, device=0,
              log_parts=0, rank=0, weight_seed=0, force_offset_bytes=0):
         """Seeded R-MAT generated, sorted and de-duplicated on the device; seed defaults to

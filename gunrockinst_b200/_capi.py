@@ -134,6 +134,7 @@ def lib():
     sig("grb_release_cached_memory", None, [])
     sig("grb_graph_from_host", C.c_int, [C.c_int, i64, i64, p, C.c_int, p, p, C.c_int, C.c_int, pp])
     sig("grb_graph_from_host_mapped", C.c_int, [C.c_int, i64, i64, p, C.c_int, p, p, C.c_int, C.c_int, pp])
+    sig("grb_graph_slice_from_host", C.c_int, [C.c_int, i64, C.c_int, C.c_int, i64, i64, p, C.c_int, p, p, C.c_int, C.c_int, pp])
     sig("grb_graph_rmat", C.c_int, [C.c_int, C.c_int, i64, u64, C.c_int, dbl, dbl, dbl, dbl,
                                     C.c_int, C.c_int, u64, C.c_int, pp])
     sig("grb_graph_build_transpose", C.c_int, [p])

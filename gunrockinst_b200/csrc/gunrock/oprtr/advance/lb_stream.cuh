@@ -137,7 +137,7 @@ StreamExpandKernel(const __grid_constant__ typename Problem::DataSlice ds_in,
     if (tid == 0) {
         sm.total = scratch.scanned[in_len];
         util::MbarInit(&sm.bar, 1);
-        for (int s = 0; s < N; ++s) { util::MbarInit(&sm.full[s], PW); util::MbarInit(&sm.empty[s], CW); }
+        for (int s = 0; s < N; ++s) { util::MbarInit(&sm.full[s], PW * 32); util::MbarInit(&sm.empty[s], CW); }
         util::MbarInitFence();
     }
     __syncthreads();
@@ -190,8 +190,6 @@ StreamExpandKernel(const __grid_constant__ typename Problem::DataSlice ds_in,
             int *buf = sm.tile[k % N];
             unsigned long long *bar = &sm.full[k % N];
             tile_items(k + 1, n_i0, n_i1);                      // requested now, needed for the next tile
-            unsigned tile_tx = 0;                               // bytes this lane's bulk copies of the tile bring
-            bool used_cp_async = false;
             ScanT s, e, ns, ne;
             SizeT rs, nrs;
             item_desc(i0 + warp + PW * lane, i1, s, e, rs);
@@ -231,8 +229,7 @@ StreamExpandKernel(const __grid_constant__ typename Problem::DataSlice ds_in,
                     const int bulk = (main_cnt - head) & ~3;
                     int *dst = buf + d + shift;
                     const VertexId *src = col + pos;
-                    tile_tx += (unsigned)bulk * 4u;                         // len >= 32: bulk > 0; announced once per warp and tile
-                    used_cp_async = true;
+                    util::MbarExpectTx(bar, (unsigned)bulk * 4u);           // len >= 32: bulk > 0
                     util::BulkCopyG2S(dst + head, src + head, (unsigned)bulk * 4u, bar);
                     // the <= 3 entries before the aligned run and the <= 6 behind it (no loops: lanes differ)
 #pragma unroll
@@ -273,24 +270,13 @@ StreamExpandKernel(const __grid_constant__ typename Problem::DataSlice ds_in,
                         if (x < T) {
                             const int rank = wp + __popc(word & (0xffffffffu >> (31 - lane))) - 1;
                             util::CpAsync4(buf + (sm.dbase[warp][rank] + x), col + (sm.base[warp][rank] + x));
-                            used_cp_async = true;
                         }
                     }
                     __syncwarp();                                           // flags / base are rewritten by the next batch
                 }
                 s = ns; e = ne; rs = nrs;
             }
-            // the slot's barrier expects ONE arrival per producer warp (256 per-lane arrivals on one shared-memory word were a
-            // serial bottleneck): lanes that issued cp.asyncs join the phase until those have landed, the warp's bulk bytes
-            // are announced in one expect_tx (the count may dip below zero meanwhile: the phase cannot complete before
-            // this warp's own arrival, which comes last)
-            if (used_cp_async) util::MbarJoinOnCpAsync(bar);
-            const unsigned warp_tx = util::WarpReduceSum(tile_tx);
-            __syncwarp();
-            if (lane == 0) {
-                if (warp_tx) util::MbarExpectTx(bar, warp_tx);
-                util::MbarArrive(bar);
-            }
+            util::MbarArriveOnCpAsync(bar);     // fires when this lane's cp.asyncs have landed; bulk bytes are counted by the barrier
             i0 = n_i0; i1 = n_i1;
         }
     } else {

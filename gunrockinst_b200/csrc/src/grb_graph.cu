@@ -64,6 +64,26 @@ extern "C" int grb_graph_from_host(int device, int64_t nodes, int64_t edges,
                          force_offset_bytes, false, out);
 }
 
+// one device's slice of a 1D-partitioned graph, from host arrays (local rows, GLOBAL neighbour ids): what a caller who
+// keeps the partitioned CSR on the host uploads per rank (the reference declares the striping, problem_base.cuh:186-210,
+// and never builds the slices)
+extern "C" int grb_graph_slice_from_host(int device, int64_t global_nodes, int log_parts, int rank, int64_t local_nodes,
+                                         int64_t edges, const void *row_offsets, int offset_bytes_in,
+                                         const int32_t *col_indices, const uint32_t *weights,
+                                         int symmetric, int force_offset_bytes, grb_graph_t *out)
+{
+    if (log_parts < 0 || log_parts > 3 || rank < 0 || rank >= (1 << log_parts) || local_nodes < 0 ||
+        (local_nodes << log_parts) != global_nodes)
+        return (int)cudaErrorInvalidValue;
+    int rc = GraphFromHost(device, local_nodes, edges, row_offsets, offset_bytes_in, col_indices, weights, symmetric,
+                           force_offset_bytes, false, out);
+    if (rc) return rc;
+    grb_graph_s *h = *out;
+    if (h->g32) { h->g32->nodes = global_nodes; h->g32->part.log_parts = log_parts; h->g32->part.rank = rank; }
+    else        { h->g64->nodes = global_nodes; h->g64->part.log_parts = log_parts; h->g64->part.rank = rank; }
+    return 0;
+}
+
 // the reference's stream_from_host (gunrock/app/problem_base.cuh:252-276)
 extern "C" int grb_graph_from_host_mapped(int device, int64_t nodes, int64_t edges,
                                           const void *row_offsets, int offset_bytes_in,

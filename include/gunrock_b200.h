@@ -59,6 +59,15 @@ int grb_graph_from_host(int device, int64_t nodes, int64_t edges,
                         const int32_t *col_indices, const uint32_t *weights,
                         int symmetric, int force_offset_bytes, grb_graph_t *out);
 
+/* One device's slice of a 1D-partitioned graph from host arrays: `local_nodes` rows (row r is global vertex
+ * Global(r) of the partition rule in csrc/gunrock/graph/csr.cuh; global_nodes = local_nodes << log_parts), neighbour ids
+ * are GLOBAL.  For the grb_mg* contexts of a caller whose partitioned CSR lives on the host; grb_graph_rmat with
+ * log_parts > 0 and grb_graph_download produce / return exactly these arrays. */
+int grb_graph_slice_from_host(int device, int64_t global_nodes, int log_parts, int rank, int64_t local_nodes,
+                              int64_t edges, const void *row_offsets, int offset_bytes_in,
+                              const int32_t *col_indices, const uint32_t *weights,
+                              int symmetric, int force_offset_bytes, grb_graph_t *out);
+
 /* same, but only the offsets are uploaded: col_indices (and weights) stay in the caller's memory,
  * page-locked and mapped into the device's address space, and the kernels read them over PCIe as
  * they go -- the reference's stream_from_host (gunrock/app/problem_base.cuh:252-276) for graphs

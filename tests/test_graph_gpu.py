@@ -116,3 +116,27 @@ def test_stream_from_host_matches_resident_graph(gr, orc, pinned):
     want_r, it = orc.pagerank(ro, co, 0.85, 1e-6, 1000, -1)
     assert st["iterations"] == it and np.max(np.abs(ranks - want_r)) <= 1e-6 * max(1.0, float(want_r.max()))
     g.close()
+
+
+def test_slice_from_host_round_trip(gr, orc):
+    """grb_graph_slice_from_host: a rank's slice of a partitioned graph uploaded from host arrays is the slice the
+    device generator built (same arrays back, same partition in the info block), and a world-1 'slice' is the graph"""
+    import numpy as np
+    for lp in (1, 2):
+        for rank in range(1 << lp):
+            a = gr.Graph.rmat(12, 8, log_parts=lp, rank=rank)
+            ro, co = a.download()
+            b = gr.Graph.from_slice(ro, co, a.nodes, lp, rank)
+            ro2, co2 = b.download()
+            assert np.array_equal(ro, ro2) and np.array_equal(co, co2)
+            assert (b.nodes, b.local_nodes, b.edges) == (a.nodes, a.local_nodes, a.edges)
+            assert (int(b.info.log_parts), int(b.info.rank)) == (lp, rank)
+            a.close()
+            b.close()
+    ro, co = orc.rmat_csr(10, 8)
+    g = gr.Graph.from_slice(ro, co, ro.size - 1, 0, 0)
+    labels, _, _ = gr.Bfs(g, direction_optimized=True).run(0)
+    assert np.array_equal(labels, orc.bfs(ro, co, 0))
+    g.close()
+    with pytest.raises(Exception):
+        gr.Graph.from_slice(ro, co, ro.size, 1, 0)             # local_nodes << log_parts != global_nodes

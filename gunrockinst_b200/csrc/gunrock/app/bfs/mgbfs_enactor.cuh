@@ -451,6 +451,13 @@ class MGBFSEnactor : public EnactorBase {
     {
         if (!p2p_ready) return util::GRError(cudaErrorNotReady, "peer mappings have not been imported", __FILE__, __LINE__);
         typename Problem::Base::Graph &g = *problem->graph;
+        if (dopt && !g.HasInverse()) {          // a directed slice: the pull direction needs in-edges this device does not hold
+            static bool told = false;
+            if (!told) fprintf(stderr, "libgunrock (B200 build): partitioned BFS on a directed graph runs top-down only "
+                                       "(no per-device transpose)\n");
+            told = true;
+            dopt = false;
+        }
         const int P = peers.parts;
         const unsigned long long seg_words = SegWords(problem);
         const unsigned long long n = (unsigned long long)g.nodes;

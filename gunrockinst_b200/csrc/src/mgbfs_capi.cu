@@ -40,8 +40,7 @@ struct MgRunner : MgRunnerBase {
     cudaError_t Create(gunrock::graph::DeviceCsr<int, SizeT> *g, cudaStream_t s)
     {
         stream = s;
-        if (!g->HasInverse())
-            return gunrock::util::GRError(cudaErrorInvalidValue, "partitioned BFS needs a symmetric graph", __FILE__, __LINE__);
+        // a directed slice without a transpose is searched top-down only (no pull levels): see RunPeer
         if (g->local_nodes % 32 != 0 && g->part.log_parts != 0)
             return gunrock::util::GRError(cudaErrorInvalidValue, "partition segments must be word aligned", __FILE__, __LINE__);
         GR_TRY(problem.Init(g, s));

@@ -54,6 +54,7 @@ class DeviceEngine:
         self.nodes = int(info.nodes)
         self.local_nodes = int(info.local_nodes)
         self.local_edges = int(info.edges)
+        self.symmetric = bool(info.symmetric)
         self.seg_words = self.local_nodes // 32
         self.device = torch.device("cuda", int(info.device))
         s = C.c_void_p()
@@ -211,7 +212,8 @@ class PartitionedBfs:
         if exchange == "peer" and not getattr(engine, "peer_ready", False):
             engine.enable_peer_exchange(group)
         self.group = group
-        self.dopt = direction_optimized
+        # a directed slice has no in-edges on this device: top-down only (the native loop takes the same decision)
+        self.dopt = direction_optimized and bool(getattr(engine, "symmetric", True))
         self.alpha, self.beta = alpha, beta
         self.record_levels = record_levels
         self.world = dist.get_world_size(group) if dist.is_initialized() else 1

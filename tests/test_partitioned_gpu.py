@@ -43,6 +43,26 @@ def test_world1_matches_oracle(gr, orc, scale, dopt, exchange, monkeypatch):
     eng.close()
 
 
+@pytest.mark.parametrize("exchange", ["nccl", "peer", "peer-persistent"])
+def test_world1_directed_graph_is_searched_top_down(gr, orc, exchange, monkeypatch):
+    """a directed slice has no transpose: the partitioned search runs push levels only and still returns the oracle's depths"""
+    from gunrockinst_b200 import partitioned as pt
+    ro, co = rmat_graph(orc, 14, 8, False)
+    g = gr.Graph.from_csr(ro, co, symmetric=False)
+    if exchange == "peer-persistent":
+        monkeypatch.setenv("GRB_MG_PERSISTENT", "1")
+        exchange = "peer"
+    else:
+        monkeypatch.delenv("GRB_MG_PERSISTENT", raising=False)
+    eng = pt.DeviceEngine(g)
+    bfs = pt.PartitionedBfs(eng, direction_optimized=True, exchange=exchange)
+    for src in (0, 7, ro.size - 2):
+        st = bfs.run(src)
+        assert np.array_equal(pt.gather_labels(eng), orc.bfs(ro, co, src))
+        assert all(lv["kind"] == "push" for lv in st["levels"])
+    eng.close()
+
+
 def _free_port():
     s = socket.socket()
     s.bind(("127.0.0.1", 0))
@@ -83,6 +103,15 @@ def _worker(rank, world, port, scale, q):
                                 st["edges_visited"] == oracle.edges_visited(ro, want),
                                 st["exchange_bytes"] > 0,
                                 e is not eng_p or st["gpu_launches"] <= 3))
+        # a directed graph (no per-device transpose): top-down only, both level loops
+        gd = gr.Graph.rmat(scale, 16, undirected=False, device=rank, log_parts=lp, rank=rank)
+        rod, cod = oracle.rmat_csr(scale, 16, undirected=False)
+        for e in (pt.DeviceEngine(gd),):
+            bfs = pt.PartitionedBfs(e, direction_optimized=True, exchange="peer")
+            for src in (0, 5):
+                st = bfs.run(src)
+                res.append((bool(np.array_equal(pt.gather_labels(e), oracle.bfs(rod, cod, src))),
+                            all(lv["kind"] == "push" for lv in st["levels"])))
         if rank == 0:
             q.put(res)
     finally:
@@ -137,6 +166,21 @@ def test_sssp_world1_matches_oracle(gr, orc, scale):
         dist_, preds = sp.gather()
         assert _check_sssp(ro, co, w, src, dist_, preds, want)
         assert st["iterations"] >= 1 or ro[src + 1] == ro[src]
+    sp.close()
+
+
+def test_sssp_world1_directed_graph(gr, orc):
+    """the partitioned SSSP only pushes along out-edges: directed slices need no transpose"""
+    from gunrockinst_b200 import partitioned as pt
+    ro, co = rmat_graph(orc, 13, 8, False)
+    w = orc.edge_weights(ro, co, 3)
+    g = gr.Graph.from_csr(ro, co, weights=w, symmetric=False)
+    sp = pt.PartitionedSssp(g)
+    for src in (0, 9):
+        sp.run(src)
+        want, _ = orc.sssp(ro, co, w, src)
+        dist_, preds = sp.gather()
+        assert _check_sssp(ro, co, w, src, dist_, preds, want)
     sp.close()
 
 

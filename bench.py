@@ -474,11 +474,11 @@ def run_single(args):
         return top
     operators = {
         "advance_lb": best_launch(dict(traversal_mode=1, degree_order=True), ("push-lb", "push-stream"), lambda r: level_bytes(r, osz, n)),
-        "filter": best_launch(dict(idempotence=True), ("filter", "filter-stream"), lambda r: 5 * r["frontier"] + 4 * r["discovered"]),
+        "filter": best_launch(dict(idempotence=True, degree_order=True), ("filter", "filter-stream"), lambda r: 5 * r["frontier"] + 4 * r["discovered"]),
         "note": "largest launch of each operator in a top-down / an idempotent search from sources[0]; algorithmic "
-                "bytes as in DESIGN.md section 3 (advance: F(4+2o)+5E+8D, filter: 5 in + 4 out).  The advance runs on the "
-                "degree-ordered twin of the graph (grb_bfs_config.degree_order) and its time covers the whole level: degree "
-                "scan, mask snapshot, StreamExpandKernel and HarvestKernel when `kernel` is push-stream",
+                "bytes as in DESIGN.md section 3 (advance: F(4+2o)+5E+8D, filter: 5 in + 4 out).  Both run on the "
+                "degree-ordered twin of the graph (grb_bfs_config.degree_order); the time covers the whole operator call: degree "
+                "scan, mask snapshot, StreamExpandKernel and HarvestKernel when `kernel` is push-stream / filter-stream",
     }
 
     # ---- end to end through the reference's entry point, CSR in pinned host memory

@@ -115,6 +115,9 @@ struct BFSOptions {
     // streaming advance (oprtr/advance/lb_stream.cuh); 0 = never
     unsigned long long stream_min_edges = 1ull << 20;
 };
+// (the runner leaves stream_min_edges at its default only for degree-ordered twins: with the caller's vertex order the hot
+//  range of the visited map answers few probes and lb::ExpandKernel / filter::Kernel are as fast or faster -- scale 25,
+//  top-down: 8.5 against 7.2 ms; on the twin 4.2 against 6.2 ms)
 
 struct LevelRecord {
     int level; int pull;                 // pull: 0 push-TWC, 1 pull, 2 push-LB, 5 push-LB streaming (lb_stream.cuh)
@@ -141,6 +144,7 @@ class BFSEnactor : public EnactorBase {
     typedef oprtr::advance::KernelPolicy<Problem, 256, 4, GRB_PULL_CTAS, false, false> PullPolicy;
     // streaming advance (lb_stream.cuh): one 1024-thread CTA per SM, 8 producer + 24 consumer warps, 6144-entry tiles
     typedef oprtr::advance::KernelPolicy<Problem, 1024, 6, 1, true, true>   StreamPolicy;
+    typedef oprtr::advance::KernelPolicy<Problem, 1024, 6, 1, true, false>  IdemStreamPolicy;   // the filter's streaming instance
     // reference: END_BITMASK_CULL = 5 (bfs_enactor.cuh:594); the word-atomic mask stays exact, so keep it on
     typedef oprtr::filter::KernelPolicy<Problem, 256, GRB_FILTER_IPT, GRB_FILTER_CTAS, -1> FilterPolicy;
 
@@ -610,11 +614,29 @@ class BFSEnactor : public EnactorBase {
             fa.queue_index = frontier_attribute.queue_index;
             fa.iteration = level + 1;
             fa.compact = true;
-            GR_TRY((oprtr::filter::LaunchKernel<FilterPolicy, Problem, BfsFunctor>(dev.sm_count, ds, fa, stream)));
+            // big frontiers go through the streaming instance (filter/stream_kernel.cuh); which one this is is only
+            // known on the device, so a level whose input frontier is large pays one fetch of the advance's counters
+            // in between (~10 us against levels of hundreds)
+            oprtr::LevelCounters ca, cf;
+            bool filter_streamed = false, have_ca = false;
+            if constexpr (Problem::ENABLE_IDEMPOTENCE && !Problem::MARK_PREDECESSORS) {
+                if (opt.stream_min_edges && (F >= 32768 || opt.stream_min_edges <= 2) && oprtr::filter::StreamEligible<Problem>(fa, g.part.log_parts)) {
+                    GR_TRY(work_progress.Fetch(frontier_attribute.queue_index, ca, stream));
+                    have_ca = true;
+                    if (!ca.overflow && ca.out_len >= 4 * opt.stream_min_edges) {
+                        fa.in_len = ca.out_len; fa.d_in_len = nullptr;
+                        filter_streamed = true;
+                        ++enactor_stats.launches;                   // kernel + harvest
+                        GR_TRY((oprtr::filter::LaunchStreamKernel<IdemStreamPolicy, Problem, BfsFunctor>(
+                            dev, ds, fa, g.View(), &lb_scratch, HotWords<IdemStreamPolicy>(problem), stream)));
+                    }
+                }
+            }
+            if (!filter_streamed)
+                GR_TRY((oprtr::filter::LaunchKernel<FilterPolicy, Problem, BfsFunctor>(dev.sm_count, ds, fa, stream)));
             if (opt.record_levels) GR_TRY(cudaEventRecord(ev_c, stream));
             // one fetch covers both slots (advance wrote queue_index, filter queue_index + 1)
-            oprtr::LevelCounters ca, cf;
-            GR_TRY(work_progress.Fetch(frontier_attribute.queue_index, ca, stream));
+            if (!have_ca) GR_TRY(work_progress.Fetch(frontier_attribute.queue_index, ca, stream));
             GR_TRY(work_progress.Fetch(frontier_attribute.queue_index + 1, cf, stream));
             if (ca.overflow || cf.overflow)
                 return util::GRError(cudaErrorInvalidConfiguration,
@@ -630,7 +652,7 @@ class BFSEnactor : public EnactorBase {
                 LevelRecord ra, rf;
                 ra.level = level; ra.pull = (mode == oprtr::advance::LB) ? 2 : 0;
                 ra.frontier = F; ra.edges = ca.edges; ra.discovered = ca.out_len; ra.candidates = 0; ra.switch_ms = 0;
-                rf.level = level; rf.pull = 4;
+                rf.level = level; rf.pull = filter_streamed ? 6 : 4;
                 rf.frontier = ca.out_len; rf.edges = 0; rf.discovered = cf.out_len; rf.candidates = 0; rf.switch_ms = 0;
                 GR_TRY(cudaEventElapsedTime(&ra.ms, ev_a, ev_b));
                 GR_TRY(cudaEventElapsedTime(&rf.ms, ev_b, ev_c));

@@ -9,6 +9,7 @@
 #pragma once
 #include "../oprtr/advance/kernel.cuh"
 #include "../oprtr/filter/kernel.cuh"
+#include "../oprtr/filter/stream_kernel.cuh"
 
 namespace gunrock {
 namespace app {

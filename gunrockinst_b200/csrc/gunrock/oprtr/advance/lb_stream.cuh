@@ -97,7 +97,10 @@ __device__ __forceinline__ unsigned ProbeVisitedWord(bool hot, bool cold, unsign
     return w;
 }
 
-template <typename Policy, typename Problem, typename Functor>
+// DIRECT = true is the streaming instance of the FILTER operator (filter::LaunchStreamKernel): the "edge space" is the
+// input queue itself -- one TMA bulk copy per tile, no scan, no pieces -- holes (-1) are skipped, and the harvest applies
+// Functor::CondFilter / ApplyFilter to the winners instead of ApplyEdge.  Everything else (ring, probes, claims) is shared.
+template <typename Policy, typename Problem, typename Functor, bool DIRECT = false>
 __global__ void __launch_bounds__(Policy::THREADS, 1)
 StreamExpandKernel(const __grid_constant__ typename Problem::DataSlice ds_in,
                    const __grid_constant__ Args<typename Policy::VertexId, typename Policy::SizeT> args,
@@ -132,10 +135,10 @@ StreamExpandKernel(const __grid_constant__ typename Problem::DataSlice ds_in,
     LevelCounters *slot_out = args.slots + ((args.queue_index + 1) & 3);
     if (cta == 0 && tid == 0) {
         ClearFutureSlot(args.slots, args.queue_index);
-        *scratch.ticket = 0;                    // the scan of this call is complete (stream order)
+        if (!DIRECT) *scratch.ticket = 0;       // the scan of this call is complete (stream order)
     }
     if (tid == 0) {
-        sm.total = scratch.scanned[in_len];
+        sm.total = DIRECT ? in_len : scratch.scanned[in_len];
         util::MbarInit(&sm.bar, 1);
         for (int s = 0; s < N; ++s) { util::MbarInit(&sm.full[s], PW * 32); util::MbarInit(&sm.empty[s], CW); }
         util::MbarInitFence();
@@ -156,7 +159,7 @@ StreamExpandKernel(const __grid_constant__ typename Problem::DataSlice ds_in,
     }
     const ScanT total = sm.total;
     unsigned long long num_tiles = (total + TILE - 1) / TILE;
-    if (num_tiles > scratch.part_cap) {         // a frontier with duplicates expanded past the scratch
+    if (!DIRECT && num_tiles > scratch.part_cap) {      // a frontier with duplicates expanded past the scratch
         num_tiles = scratch.part_cap;
         if (tid == 0) slot_out->overflow = 1;
     }
@@ -165,6 +168,36 @@ StreamExpandKernel(const __grid_constant__ typename Problem::DataSlice ds_in,
     unsigned long long my_edges = 0;            // one consumer thread
 
     if (warp < PW) {
+      if constexpr (DIRECT) {
+        // ================================ producers, filter instance ========================================
+        // the tiles are consecutive stretches of the input queue: one bulk copy each (the queue's allocation is 16-byte
+        // aligned and padded), issued by the first producer thread; the other producer lanes only keep the barrier's count
+        unsigned refresh_phase = 0;
+        for (long long k = 0; k < my_tiles; ++k) {
+            const unsigned long long t = cta + (unsigned long long)k * nctas;
+            const ScanT tile_start = t * TILE;
+            const unsigned items = (unsigned)((total - tile_start < (ScanT)TILE) ? (total - tile_start) : (ScanT)TILE);
+            unsigned long long *bar = &sm.full[k % N];
+            if (hot_words && tid == 0 && k > 0 && (k % kStreamRefresh) == 0 && util::MbarTryWait(&sm.bar, refresh_phase & 1u)) {
+                ++refresh_phase;
+                const unsigned copy_words = (hot_words + 3u) & ~3u;
+                util::MbarExpectTx(&sm.bar, copy_words * 4u);
+                for (unsigned w = 0; w < copy_words; w += 8192) {
+                    const unsigned cnt = copy_words - w < 8192u ? copy_words - w : 8192u;
+                    util::BulkCopyG2S(s_hot + w, ds.d_visited_mask + w, cnt * 4u, &sm.bar);
+                }
+                util::MbarArrive(&sm.bar);
+            }
+            if (k >= N) util::MbarWait(&sm.empty[k % N], (unsigned)(((k / N) - 1) & 1));
+            if (tid == 0) {
+                const unsigned bytes = ((items + 3u) & ~3u) * 4u;
+                util::MbarArriveExpectTx(bar, bytes);           // arrival and announcement in one: the copy cannot be missed
+                util::BulkCopyG2S(sm.tile[k % N], args.in_queue + tile_start, bytes, bar);
+            } else {
+                util::MbarArrive(bar);
+            }
+        }
+      } else {
         // ================================ producers ==========================================================
         // tile k of this CTA is global tile cta + k * nctas and lives in ring slot k % N; all producers work on the same
         // tile, its items dealt round-robin to their lanes.  Nothing here waits for data.
@@ -279,6 +312,7 @@ StreamExpandKernel(const __grid_constant__ typename Problem::DataSlice ds_in,
             util::MbarArriveOnCpAsync(bar);     // fires when this lane's cp.asyncs have landed; bulk bytes are counted by the barrier
             i0 = n_i0; i1 = n_i1;
         }
+      }
     } else {
         // ================================ consumers ==========================================================
         const int cw = warp - PW;
@@ -291,6 +325,13 @@ StreamExpandKernel(const __grid_constant__ typename Problem::DataSlice ds_in,
             util::MbarWait(&sm.full[k % N], (unsigned)((k / N) & 1));
             const int4 *t4 = reinterpret_cast<const int4 *>(sm.tile[k % N]);
             qa = t4[qa_i]; qb = t4[qb_i];
+            // The slot goes back to the async proxy (its next tenant arrives by TMA): the reads above have to be COMPLETE
+            // and ordered before that write.  Issuing them is not enough -- with producers that have nothing else to do
+            // (the filter instance) the refill overtook loads still in flight and a few ids per million were read from
+            // the next tile instead (found as missing depths at scale 22 / 25).  The fence takes the loaded registers as
+            // operands, so it cannot issue before the data is there, and orders the generic reads before the async write.
+            asm volatile("fence.proxy.async.shared::cta; // %0 %1 %2 %3 %4 %5 %6 %7"
+                         :: "r"(qa.x), "r"(qa.y), "r"(qa.z), "r"(qa.w), "r"(qb.x), "r"(qb.y), "r"(qb.z), "r"(qb.w) : "memory");
             __syncwarp();
             if (lane == 0) util::MbarArrive(&sm.empty[k % N]);          // the ids are in registers: the slot is free
         };
@@ -310,6 +351,10 @@ StreamExpandKernel(const __grid_constant__ typename Problem::DataSlice ds_in,
                     valid |= (unsigned)(qa_i * 4 + i < tile_edges) << i;
                     valid |= (unsigned)(qb_i * 4 + i < tile_edges) << (4 + i);
                 }
+            }
+            if constexpr (DIRECT) {                                     // holes (-1) a previous operator left in the queue
+#pragma unroll
+                for (int i = 0; i < 8; ++i) valid &= ~((unsigned)(v[i] < 0) << i);
             }
             // ---- probe: eight words in flight per lane
             unsigned word[8];
@@ -341,7 +386,7 @@ StreamExpandKernel(const __grid_constant__ typename Problem::DataSlice ds_in,
 // taken before the level.  Each exactly once and in vertex order.  A warp takes 32 words of the mask at a time (lane <->
 // word for the counts, lane <-> vertex of word j for the work), so Functor::ApplyEdge (BFS: the label store), the output
 // frontier and the row-offset reads of the out-degree sum are coalesced; one global atomic per 1024 vertices scanned.
-template <typename Policy, typename Problem, typename Functor>
+template <typename Policy, typename Problem, typename Functor, bool FILTER = false>
 __global__ void __launch_bounds__(256)
 HarvestKernel(const __grid_constant__ typename Problem::DataSlice ds_in,
               const __grid_constant__ Args<typename Policy::VertexId, typename Policy::SizeT> args,
@@ -376,7 +421,12 @@ HarvestKernel(const __grid_constant__ typename Problem::DataSlice ds_in,
             if (wj == 0) continue;                              // warp-uniform
             if ((wj >> lane) & 1u) {
                 const VertexId v = (VertexId)(((g * 32 + j) << 5) + lane);
-                Functor::ApplyEdge((VertexId)args.iteration, v, &ds, (SizeT)0, (SizeT)0);
+                if constexpr (FILTER) {
+                    // (the streamed filter's queue holds vertices only: CondFilter's "not a hole" test has passed by construction)
+                    Functor::ApplyFilter(v, &ds, (typename Problem::Value)args.iteration, (SizeT)0);
+                } else {
+                    Functor::ApplyEdge((VertexId)args.iteration, v, &ds, (SizeT)0, (SizeT)0);
+                }
                 if (args.output == OUT_COMPACT) {
                     const unsigned long long at = base + pj + __popc(wj & below);
                     if (at < args.out_cap) args.out_queue[at] = v; else slot_out->overflow = 1;

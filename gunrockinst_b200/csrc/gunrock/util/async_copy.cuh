@@ -31,6 +31,13 @@ __device__ __forceinline__ void MbarExpectTx(unsigned long long *bar, unsigned b
 {
     asm volatile("mbarrier.expect_tx.relaxed.cta.shared::cta.b64 [%0], %1;" :: "r"(SharedAddr(bar)), "r"(bytes) : "memory");
 }
+// one arrival that also adds `bytes` to the transaction count, as ONE operation on the barrier word: the form to use when
+// the arrival follows the announcement immediately (an expect_tx and a cp.async-tracked arrival travel through different
+// pipes and may reach the barrier in either order)
+__device__ __forceinline__ void MbarArriveExpectTx(unsigned long long *bar, unsigned bytes)
+{
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" :: "r"(SharedAddr(bar)), "r"(bytes) : "memory");
+}
 __device__ __forceinline__ void MbarArrive(unsigned long long *bar)
 {
     asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" :: "r"(SharedAddr(bar)) : "memory");

@@ -42,6 +42,7 @@ struct BfsRunner : BfsRunnerBase {
     {
         stream = s;
         to_new = map_to_new; to_old = map_to_old;
+        if (!cfg && !map_to_new) opt.stream_min_edges = 0;
         if (cfg) {
             opt.traversal_mode = cfg->traversal_mode;
             opt.direction_optimized = cfg->direction_optimized != 0;
@@ -53,7 +54,8 @@ struct BfsRunner : BfsRunnerBase {
             // launch + counter fetch there), the host-driven loop of stand-alone kernels above (at scale
             // 25 they run the big levels 1.1-1.35x faster: 5 instead of 4 resident CTAs per SM, fewer
             // live registers around the operator bodies); 1: host loop; 2: persistent kernel
-            if (cfg->stream_min_edges == 1) opt.stream_min_edges = 0;                  // streaming advance off
+            // streaming advance / filter: 0 = by default on degree-ordered twins only, 1 = off, n > 1 = from n entries upward
+            if (cfg->stream_min_edges == 1 || (cfg->stream_min_edges == 0 && !map_to_new)) opt.stream_min_edges = 0;
             else if (cfg->stream_min_edges > 1) opt.stream_min_edges = (unsigned long long)cfg->stream_min_edges;
             opt.host_loop = cfg->host_loop == 1 || (cfg->host_loop == 0 && g->nodes >= (1ll << 24));
         }

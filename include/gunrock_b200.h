@@ -154,8 +154,11 @@ typedef struct {
                                      next to it: + one CSR of device memory).  Sources, labels and
                                      predecessors stay in the caller's ids.  Resident single-device graphs. */
     int32_t stream_min_edges;     /* host-driven loop: push levels with at least this many frontier edges take the
-                                     streaming advance (TMA-staged neighbour tiles, hot part of the visited map in
-                                     shared memory); 0: library default (2^20), 1: never */
+                                     streaming advance, and filters of idempotent searches with four times as many
+                                     items the streaming filter (TMA-staged tiles, hot part of the visited map in
+                                     shared memory, claims as reductions + harvest); 0: library default (2^20 on a
+                                     degree-ordered twin, never on the caller's vertex order, where the hot range
+                                     answers too few probes), 1: never, n > 1: from n entries upward on any order */
 } grb_bfs_config;
 
 typedef struct grb_bfs_s *grb_bfs_t;

@@ -339,7 +339,7 @@ def test_streaming_advance_matches_oracle(gr, orc, scale, mode):
     bfs = gr.Bfs(g, host_loop=True, stream_min_edges=2, record_levels=True, **mode)
     n = ro.size - 1
     rng = np.random.RandomState(7 + scale)
-    streamed = 0
+    streamed = filter_streamed = 0
     for src in [0, 1, n - 1] + rng.randint(0, n, 3).tolist():
         labels, _, st = bfs.run(src)
         want = orc.bfs(ro, co, src)
@@ -347,13 +347,16 @@ def test_streaming_advance_matches_oracle(gr, orc, scale, mode):
         assert st["edges_visited"] == orc.edges_visited(ro, want)
         lv = bfs.levels()
         streamed += sum(1 for r in lv if r["kind"] == "push-stream")
+        filter_streamed += sum(1 for r in lv if r["kind"] == "filter-stream")
         if not mode.get("idempotence") and not mode.get("direction_optimized"):
             # a top-down search inspects every entry of the visited rows exactly once
             assert sum(r["edges"] for r in lv) == st["edges_visited"]
-    # (idempotent searches keep the two-operator pipeline of lb::ExpandKernel + filter::Kernel: the streaming instance's
-    # claim IS the visited bit, which an idempotent advance must leave to the filter)
+    # (an idempotent search keeps lb::ExpandKernel for its advance -- the streaming advance's claim IS the visited bit, which
+    # an idempotent advance must leave to the filter -- and streams its FILTER instead: filter/stream_kernel.cuh)
     if not mode.get("idempotence") and (scale >= 16 or mode.get("traversal_mode") == 1):     # small graphs: only the LB-always modes reach the LB levels
         assert streamed > 0, mode
+    if mode.get("idempotence"):
+        assert filter_streamed > 0, mode
     bfs.close()
     g.close()
 

@@ -22,7 +22,7 @@ print(json.dumps({"graph": {"scale": scale, "n": g.nodes, "m": g.edges, "build_s
 
 VARIANTS = [
     ("td_r1", dict(traversal_mode=1, host_loop=1, stream_min_edges=1)),
-    ("td_stream", dict(traversal_mode=1, host_loop=1)),
+    ("td_stream", dict(traversal_mode=1, host_loop=1, stream_min_edges=1 << 20)),
     ("td_stream_twin", dict(traversal_mode=1, host_loop=1, degree_order=True)),
     ("td_r1_twin", dict(traversal_mode=1, host_loop=1, stream_min_edges=1, degree_order=True)),
     ("dobfs_r1", dict(direction_optimized=True, stream_min_edges=1)),
@@ -30,7 +30,7 @@ VARIANTS = [
     ("dobfs_host_r1", dict(direction_optimized=True, host_loop=1, stream_min_edges=1)),
     ("dobfs_host_twin", dict(direction_optimized=True, host_loop=1, degree_order=True)),
     ("idem_r1", dict(idempotence=True, stream_min_edges=1)),
-    ("idem_stream", dict(idempotence=True)),
+    ("idem_stream", dict(idempotence=True, stream_min_edges=1 << 20)),
     ("idem_stream_twin", dict(idempotence=True, degree_order=True)),
 ]
 ref_labels = None

@@ -140,7 +140,7 @@ StreamExpandKernel(const __grid_constant__ typename Problem::DataSlice ds_in,
     if (tid == 0) {
         sm.total = DIRECT ? in_len : scratch.scanned[in_len];
         util::MbarInit(&sm.bar, 1);
-        for (int s = 0; s < N; ++s) { util::MbarInit(&sm.full[s], PW * 32); util::MbarInit(&sm.empty[s], CW); }
+        for (int s = 0; s < N; ++s) { util::MbarInit(&sm.full[s], DIRECT ? PW * 32 : PW * 32 + 1); util::MbarInit(&sm.empty[s], CW); }
         util::MbarInitFence();
     }
     __syncthreads();
@@ -310,6 +310,13 @@ StreamExpandKernel(const __grid_constant__ typename Problem::DataSlice ds_in,
                 s = ns; e = ne; rs = nrs;
             }
             util::MbarArriveOnCpAsync(bar);     // fires when this lane's cp.asyncs have landed; bulk bytes are counted by the barrier
+            // The announcements of the bulk bytes (expect_tx) and the cp.async-tracked arrivals above reach the barrier
+            // through different pipes, in either order (seen in the filter instance: an arrival overtook the expect_tx
+            // issued just before it and the phase completed without the tile).  So the phase also waits for one plain
+            // arrival that is issued after every producer has issued its announcements: a named barrier among the 256
+            // producer threads, then one thread arrives.
+            asm volatile("bar.sync 1, %0;" :: "n"(PW * 32) : "memory");
+            if (tid == 0) util::MbarArrive(bar);
             i0 = n_i0; i1 = n_i1;
         }
       }

@@ -387,3 +387,22 @@ def test_streaming_advance_shapes(gr, orc):
                     assert np.array_equal(labels, orc.bfs(ro, co, src)), (ro.size, fob, mode, src)
                 bfs.close()
             g.close()
+
+
+@pytest.mark.parametrize("mode", [dict(traversal_mode=1, host_loop=True), dict(idempotence=True)],
+                         ids=["topdown", "idempotent"])
+def test_streaming_instances_at_scale_21(gr, orc, mode):
+    """the streaming advance / filter where they are the default path (degree-ordered twin, levels of tens of millions of
+    entries, several tiles per SM in flight): depths equal to the oracle's for several sources.  The ring's slot hand-back
+    hazard of round 2 only showed at this size."""
+    g = gr.Graph.rmat(21)
+    ro, co = g.download()
+    bfs = gr.Bfs(g, degree_order=True, record_levels=True, **mode)
+    kinds = set()
+    for src in (0, 1, 77777, (1 << 21) - 5):
+        labels, _, st = bfs.run(src)
+        assert np.array_equal(labels, orc.bfs(ro, co, src)), (src, mode)
+        kinds |= {r["kind"] for r in bfs.levels()}
+    assert ("filter-stream" if mode.get("idempotence") else "push-stream") in kinds
+    bfs.close()
+    g.close()

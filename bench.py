@@ -618,7 +618,12 @@ def main():
         run_single(args)
     else:
         from gunrockinst_b200 import partitioned
-        partitioned.bench(args, rank, world, workload_config, ClockSampler, pick_sources, measured_peaks)
+        cpu_check = None
+        if not args.no_cpu and rank == 0:
+            import oracle                   # the checker only: depths of the single-device search up to scale 24
+            oracle.build()
+            cpu_check = oracle.bfs
+        partitioned.bench(args, rank, world, workload_config, ClockSampler, pick_sources, measured_peaks, cpu_check)
 
 
 if __name__ == "__main__":

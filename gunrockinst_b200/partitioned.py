@@ -587,8 +587,9 @@ def _pick_sources(graph, eng, count, seed, group=None):
     return uniq[:count]
 
 
-def bench(args, rank, world, workload_config, ClockSampler, pick_sources, measured_peaks):
-    """One JSON line on rank 0: whole-job GTEPS of the 1D-partitioned DOBFS at `world` devices."""
+def bench(args, rank, world, workload_config, ClockSampler, pick_sources, measured_peaks, cpu_check=None):
+    """One JSON line on rank 0: whole-job GTEPS of the 1D-partitioned DOBFS at `world` devices.
+    cpu_check(row_offsets, col, src) -> depths: the harness's CPU checker (nothing in this package imports one)."""
     import json
     import os
     from . import Graph
@@ -644,11 +645,9 @@ def bench(args, rank, world, workload_config, ClockSampler, pick_sources, measur
                     single = {"gteps": s_edges / (s_ms * 1e-3) / 1e9, "ms_per_search": s_ms / s_steps, "searches": s_steps,
                               "graph": "the same seeded R-MAT scale %d, unpartitioned, resident on device 0" % scale,
                               "api": "grb_bfs_run_many (direction-optimising)", "setup_s": round(time.time() - t_s, 1)}
-                    if scale <= 24 and not getattr(args, "no_cpu", False):
-                        import oracle                       # the checker only
-                        oracle.build()
+                    if scale <= 24 and cpu_check is not None:      # the caller's CPU checker (bench.py: the oracle)
                         ro, co = gfull.download()
-                        oracle_parity = bool(np.array_equal(ref_labels.cpu().numpy(), oracle.bfs(ro, co, sources[0])))
+                        oracle_parity = bool(np.array_equal(ref_labels.cpu().numpy(), cpu_check(ro, co, sources[0])))
                         del ro, co
                     sb.close()
                     if world > 1:

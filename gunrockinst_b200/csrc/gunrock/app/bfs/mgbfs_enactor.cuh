@@ -276,6 +276,10 @@ class MGBFSEnactor : public EnactorBase {
     int  persistent_grid = 0;
     typedef void (*PersistentFn)(const DataSlice, const MgPersistentParams<VertexId, SizeT>);
     static PersistentFn PersistentEntry() { return MgPersistentKernel<AdvancePolicy, PullPolicy, Problem, PushFunctor, PullFunctor>; }
+    static PersistentFn TailEntry() { return MgPersistentKernel<AdvancePolicy, PullPolicy, Problem, PushFunctor, PullFunctor, true>; }
+    bool tail_ok = false;
+    int  tail_grid = 0;
+    static const unsigned long long kTailLimit = 1ull << 16;    // global frontier below which the end of a search runs in one kernel
     std::vector<LevelTrace> trace;
     std::vector<cudaEvent_t> events;
 
@@ -317,6 +321,16 @@ class MGBFSEnactor : public EnactorBase {
         const char *pe = getenv("GRB_MG_PERSISTENT");
         persistent_ok = coop != 0 && per_sm > 0 && pe && pe[0] == '1';
         persistent_grid = per_sm * dev.sm_count;
+        // the TAIL instance (the last, short levels of a search in one kernel): opt-in, GRB_MG_TAIL=1.  Measured at 2 devices,
+        // scale 27 (profiles/r02_tail_n2.txt): the two last levels take 0.28 ms in the kernel against 0.18 ms driven by the
+        // host -- with 2 CTAs per SM the dense scatter / absorb passes over the 16 MB maps are slower than the stand-alone
+        // kernels' full grids, and the grid-wide barriers cost what the launches did
+        int tail_per_sm = 0;
+        GR_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&tail_per_sm, TailEntry(), AdvancePolicy::THREADS, 0));
+        if (tail_per_sm > 2) tail_per_sm = 2;               // few CTAs: the grid-wide barriers are what a short level costs
+        const char *te = getenv("GRB_MG_TAIL");
+        tail_ok = coop != 0 && tail_per_sm > 0 && te && te[0] == '1';
+        tail_grid = tail_per_sm * dev.sm_count;
         return cudaStreamSynchronize(stream);
     }
 
@@ -362,13 +376,9 @@ class MGBFSEnactor : public EnactorBase {
     }
     void DestroyEvents() { for (cudaEvent_t e : events) cudaEventDestroy(e); events.clear(); }
 
-    // the search as one cooperative kernel (the reset and the seeding of the counters have been issued on the stream)
-    cudaError_t RunPersistent(Problem *problem, bool dopt, double alpha, double beta, bool record, cudaEvent_t ev_start,
-                              size_t &used, SearchStats *out)
+    void FillPersistentParams(Problem *problem, bool dopt, double alpha, double beta, bool record, MgPersistentParams<VertexId, SizeT> &P)
     {
         typename Problem::Base::Graph &g = *problem->graph;
-        GR_TRY(d_status.Zero(stream));
-        MgPersistentParams<VertexId, SizeT> P;
         P.g = g.View(); P.ginv = g.InverseView();
         P.fwd_row_offsets = g.symmetric ? nullptr : g.row_offsets.ptr;
         for (int i = 0; i < 2; ++i) {
@@ -389,8 +399,55 @@ class MGBFSEnactor : public EnactorBase {
         P.mailbox_epoch = epoch; P.barrier_count = bar_count; P.budget_ns = PeerComm::BudgetFromEnv();
         P.global_edges = global_edges; P.seg_words = SegWords(problem);
         P.desc_words = (unsigned long long)lb_scratch.tile_desc.size;
-        P.dopt = dopt ? 1 : 0; P.in_sel = 0;
+        P.dopt = dopt ? 1 : 0; P.in_sel = in_sel;
         P.alpha = alpha; P.beta = beta; P.lb_min_edges = 4096;
+    }
+
+    // The end of a search in one kernel (MgPersistentKernel<..., TAIL>): called from the host loop with its state after a
+    // counter exchange; on return `st` holds the state after the last exchange the kernel made (st.F == 0: search over).
+    // -> cudaErrorCooperativeLaunchTooLarge if the launch is refused (the caller goes on level by level).
+    cudaError_t RunTail(Problem *problem, bool dopt, double alpha, double beta, bool record, VertexId level_in, MgTailState &st,
+                        MgPersistentSummary &sum_out)
+    {
+        GR_TRY(d_status.Zero(stream));
+        MgPersistentParams<VertexId, SizeT> P;
+        FillPersistentParams(problem, dopt, alpha, beta, record, P);
+        P.tail = st;
+        DataSlice ds = problem->MakeDataSlice(level_in);
+        void *kargs[] = {(void *)&ds, (void *)&P};
+        cudaError_t le = cudaLaunchCooperativeKernel((const void *)TailEntry(), dim3((unsigned)tail_grid),
+                                                     dim3(AdvancePolicy::THREADS), kargs, 0, stream);
+        if (le != cudaSuccess) {
+            (void)cudaGetLastError();
+            tail_ok = false;
+            return cudaErrorCooperativeLaunchTooLarge;
+        }
+        ++enactor_stats.launches;
+        GR_TRY(cudaMemcpyAsync(h_mg_summary.ptr, d_summary.ptr, sizeof(MgPersistentSummary), cudaMemcpyDeviceToHost, stream));
+        if (record)
+            GR_TRY(cudaMemcpyAsync(h_records.ptr, d_records.ptr, sizeof(MgLevelRecord) * kMaxRecords, cudaMemcpyDeviceToHost, stream));
+        GR_TRY(cudaStreamSynchronize(stream));
+        sum_out = *h_mg_summary.ptr;
+        epoch = sum_out.mailbox_epoch; bar_count = sum_out.barrier_count;
+        in_sel = (int)sum_out.in_sel;
+        if (sum_out.error == 1)
+            return util::GRError(cudaErrorLaunchTimeout, "peer exchange timed out (a peer stopped or the ranks diverged)", __FILE__, __LINE__);
+        if (sum_out.error)
+            return util::GRError(cudaErrorInvalidConfiguration, "frontier queue overflow on a partitioned level", __FILE__, __LINE__);
+        st.F = sum_out.F; st.frontier_edges = sum_out.frontier_edges; st.local_q = sum_out.local_q; st.local_hint = sum_out.local_hint;
+        st.prev_len = sum_out.prev_len; st.unexplored = sum_out.unexplored; st.level = (int)sum_out.level; st.cur = (int)sum_out.cur;
+        st.queue_valid = (int)sum_out.queue_valid; st.gathered = (int)sum_out.gathered;
+        return cudaSuccess;
+    }
+
+    // the search as one cooperative kernel (the reset and the seeding of the counters have been issued on the stream)
+    cudaError_t RunPersistent(Problem *problem, bool dopt, double alpha, double beta, bool record, cudaEvent_t ev_start,
+                              size_t &used, SearchStats *out)
+    {
+        GR_TRY(d_status.Zero(stream));
+        MgPersistentParams<VertexId, SizeT> P;
+        FillPersistentParams(problem, dopt, alpha, beta, record, P);
+        P.in_sel = 0;
         DataSlice ds = problem->MakeDataSlice(0);
         void *kargs[] = {(void *)&ds, (void *)&P};
         cudaError_t le = getenv("GRB_FAIL_COOP_LAUNCH") ? cudaErrorCooperativeLaunchTooLarge
@@ -508,6 +565,39 @@ class MGBFSEnactor : public EnactorBase {
             if (dopt) {
                 if (!pull && (double)frontier_edges > (double)unexplored / alpha) pull = true;
                 else if (pull && frontier < prev_len && (double)frontier < (double)n / beta) pull = false;
+            }
+            // ---- the end of the search: once the frontier is short and shrinking, the remaining levels run in one kernel
+            if (tail_ok && !pull && level > 0 && frontier < kTailLimit && frontier < prev_len) {
+                MgTailState ts;
+                ts.F = frontier; ts.frontier_edges = frontier_edges; ts.local_q = local_q; ts.local_hint = local_hint;
+                ts.prev_len = prev_len; ts.unexplored = unexplored; ts.limit = kTailLimit;
+                ts.level = (int)level; ts.cur = cur; ts.queue_valid = queue_valid ? 1 : 0; ts.gathered = gathered ? 1 : 0;
+                MgPersistentSummary ts_sum;
+                cudaError_t te = RunTail(problem, dopt, alpha, beta, record, (VertexId)level, ts, ts_sum);
+                if (te == cudaSuccess) {
+                    if (record) {
+                        for (unsigned long long i = 0; i < ts_sum.levels && i < (unsigned long long)kMaxRecords; ++i) {
+                            const MgLevelRecord &r = h_records.ptr[i];
+                            LevelTrace t;
+                            t.level = r.level; t.kind = r.kind; t.frontier = r.frontier; t.discovered = r.discovered; t.edges = r.edges;
+                            t.max_edges = r.max_edges; t.candidates = 0;
+                            t.exchange_bytes = P > 1 ? 4ull * (r.sent_words - sent_so_far) : 0ull;
+                            sent_so_far = r.sent_words;
+                            exch_bytes += t.exchange_bytes;
+                            t.compute_ms = (float)((double)r.ns_compute * 1e-6); t.exchange_ms = (float)((double)r.ns_exchange * 1e-6);
+                            trace.push_back(t);
+                        }
+                    }
+                    push_levels += (long long)ts_sum.push_levels;
+                    inspected += ts_sum.edges_inspected;
+                    edges_visited += ts_sum.edges_visited;
+                    nodes_visited += ts_sum.nodes_visited;
+                    frontier = ts.F; frontier_edges = ts.frontier_edges; local_q = ts.local_q; local_hint = ts.local_hint;
+                    prev_len = ts.prev_len; unexplored = ts.unexplored; level = ts.level; cur = ts.cur;
+                    queue_valid = ts.queue_valid != 0; gathered = ts.gathered != 0;
+                    continue;                       // frontier == 0: done; else the kernel handed the loop back
+                }
+                if (te != cudaErrorCooperativeLaunchTooLarge) return te;
             }
             cudaEvent_t m0 = 0, m1 = 0, m2 = 0, m3 = 0, m4 = 0;
             unsigned long long lvl_bytes = 0;

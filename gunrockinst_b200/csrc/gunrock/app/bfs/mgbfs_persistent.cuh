@@ -47,6 +47,14 @@ struct MgPersistentSummary {
     unsigned long long error;                           // 1: a peer did not answer in time, 2: queue overflow
     unsigned long long ns_kernel, grid_syncs;
     unsigned long long gather_bytes;                    // frontier-map bytes this device stored into peers (pull levels)
+    // TAIL instance: the loop state when the kernel returned (F == 0: the search is over; handoff != 0: the host loop goes on)
+    unsigned long long handoff, F, frontier_edges, local_q, local_hint, prev_len, unexplored, level, cur, queue_valid, gathered;
+};
+
+// what the host loop hands to the TAIL instance (the state after its last counter exchange)
+struct MgTailState {
+    unsigned long long F = 0, frontier_edges = 0, local_q = 0, local_hint = 0, prev_len = 0, unexplored = 0, limit = 0;
+    int level = 0, cur = 0, queue_valid = 1, gathered = 0;
 };
 
 template <typename VertexId, typename SizeT>
@@ -72,6 +80,7 @@ struct MgPersistentParams {
     int          dopt, in_sel;
     double       alpha, beta;
     unsigned long long lb_min_edges;
+    MgTailState  tail;
 };
 
 // ---- bodies shared with the stand-alone kernels of mgbfs_enactor.cuh / mgbfs_p2p.cuh (grid-stride over `nctas` CTAs) ----
@@ -248,7 +257,12 @@ union MgPersistentStorage {
 #endif
 constexpr int kMgPersistentCtasPerSm = GRB_MG_PERSISTENT_CTAS;
 
-template <typename PushPolicy, typename PullPolicy, typename Problem, typename PushFunctor, typename PullFunctor>
+// TAIL = true is the instance the host loop uses for the END of a search: once the global frontier is short and shrinking
+// (a few thousand vertices per level, where a level is two barriers between the devices and nothing else) the remaining
+// push levels run here, top-down with the TWC expansion only -- no sweep, no LB scan in the kernel, so it is small -- until
+// the frontier is empty, or until the direction rule asks for a pull level or the frontier grows past P.tail.limit again
+// (then the loop state goes back to the host).
+template <typename PushPolicy, typename PullPolicy, typename Problem, typename PushFunctor, typename PullFunctor, bool TAIL = false>
 __global__ void __launch_bounds__(PushPolicy::THREADS, kMgPersistentCtasPerSm)
 MgPersistentKernel(const __grid_constant__ typename Problem::DataSlice ds0,
                    const __grid_constant__ MgPersistentParams<typename Problem::VertexId, typename Problem::SizeT> P)
@@ -285,11 +299,24 @@ MgPersistentKernel(const __grid_constant__ typename Problem::DataSlice ds0,
     sum.levels = sum.push_levels = sum.pull_levels = 0;
     sum.edges_visited = sum.edges_inspected = sum.nodes_visited = 0;
     sum.error = sum.grid_syncs = sum.gather_bytes = 0;
+    sum.handoff = 0;
     unsigned long long t_level = 0, ns_exchange = 0;    // leader only
     unsigned long long lvl_frontier = 0;
     int lvl_kind = 0;
+    bool entering = TAIL;                               // TAIL: the host's last exchange stands for this kernel's first
+    if constexpr (TAIL) {
+        F = P.tail.F; frontier_edges = P.tail.frontier_edges; local_q = P.tail.local_q; local_hint = P.tail.local_hint;
+        prev_len = P.tail.prev_len; unexplored = P.tail.unexplored;
+        level = (VertexId)P.tail.level; cur = P.tail.cur; queue_valid = P.tail.queue_valid != 0; gathered = P.tail.gathered != 0;
+        first = false;
+        // the host loop's counter block of the level before is still in the slot (its kernels clear it when a level starts)
+        if (gtid < 8) reinterpret_cast<unsigned long long *>(slot)[gtid] = 0;
+        grid.sync(); ++sum.grid_syncs;
+    }
 
     for (;;) {
+      const bool decided = entering;                    // TAIL: the host has taken the direction decision of the first level
+      if (!entering) {
         // ---- the level ends (the search begins) with the counter exchange: the barrier between the devices --------
         const unsigned long long t_x0 = leader ? GlobalTimerNs() : 0ull;
         if (parts > 1) __threadfence_system();          // this thread's stores into peer memory, before the flag goes out
@@ -340,17 +367,21 @@ MgPersistentKernel(const __grid_constant__ typename Problem::DataSlice ds0,
         sum.edges_visited += fe;
         sum.nodes_visited += f;
         if (F == 0) break;
+      }
+        entering = false;
         if (leader) { t_level = GlobalTimerNs(); ns_exchange = 0; }
         lvl_frontier = F;
 
         // ---- direction (Beamer's rule on the global figures, as MGBFSEnactor::RunPeer) ---------------------------
-        if (P.dopt) {
+        if constexpr (TAIL) {
+            if (!decided && ((P.dopt && (double)frontier_edges > (double)unexplored / P.alpha) || F >= P.tail.limit)) { sum.handoff = 1; break; }
+        } else if (P.dopt) {
             if (!pull && (double)frontier_edges > (double)unexplored / P.alpha) pull = true;
             else if (pull && F < prev_len && (double)F < (double)n / P.beta) pull = false;
         }
         ds.level = level;
         lvl_kind = pull ? 1 : 0;
-        if (pull) {
+        if constexpr (!TAIL) if (pull) {
             if (!gathered && parts > 1) {               // first pull level after push levels: own segment -> every peer
                 const unsigned long long t0 = leader ? GlobalTimerNs() : 0ull;
                 ScatterSegmentBody(P.peers, cur, P.seg_words, cta, num_ctas);
@@ -385,7 +416,9 @@ MgPersistentKernel(const __grid_constant__ typename Problem::DataSlice ds0,
             queue_valid = false;
             gathered = true;
             ++sum.pull_levels;
-        } else {
+            continue;
+        }
+        {
             if (!queue_valid) {                         // own segment of map `cur` -> local queue (length known: local_q)
                 if (leader) P.slots[3].out_len = 0;
                 grid.sync(); ++sum.grid_syncs;
@@ -401,7 +434,8 @@ MgPersistentKernel(const __grid_constant__ typename Problem::DataSlice ds0,
                 a.in_len = local_q; a.d_in_len = nullptr; a.out_cap = 0;
                 a.slots = P.slots; a.queue_index = 0; a.iteration = level;
                 a.output = adv::OUT_NONE;
-                if (local_hint >= 4096) {
+                if (!TAIL && local_hint >= 4096) {
+                  if constexpr (!TAIL) {
                     if (lb_epoch + 1 >= adv::lb::kEpochLimit) {
                         for (unsigned long long w = gtid; w < P.desc_words; w += gthreads) P.scratch.tile_desc[w] = 0;
                         grid.sync(); ++sum.grid_syncs;
@@ -414,6 +448,7 @@ MgPersistentKernel(const __grid_constant__ typename Problem::DataSlice ds0,
                     grid.sync(); ++sum.grid_syncs;
                     if (leader) *sv.ticket = 0;
                     adv::lb::ExpandTiles<PushPolicy, Problem, PushFunctor, false>(ds, a, sv, sm.push.expand, local_q, slot, cta, num_ctas);
+                  }
                 } else {
                     adv::twc::ExpandItems<PushPolicy, Problem, PushFunctor>(ds, a, sm.twc, local_q, slot, cta, num_ctas);
                 }
@@ -437,7 +472,10 @@ MgPersistentKernel(const __grid_constant__ typename Problem::DataSlice ds0,
         }
     }
     if (leader) {
-        sum.gather_bytes += 4ull * util::LoadCG(P.sent_words);     // + the discovery lines of the push levels = all peer stores
+        if (!TAIL) sum.gather_bytes += 4ull * util::LoadCG(P.sent_words);     // + the discovery lines of the push levels = all peer stores
+        sum.F = F; sum.frontier_edges = frontier_edges; sum.local_q = local_q; sum.local_hint = local_hint;
+        sum.prev_len = prev_len; sum.unexplored = unexplored; sum.level = (unsigned long long)level; sum.cur = (unsigned long long)cur;
+        sum.queue_valid = queue_valid ? 1 : 0; sum.gathered = gathered ? 1 : 0;
         sum.mailbox_epoch = epoch; sum.barrier_count = bar; sum.lb_epoch_end = lb_epoch; sum.in_sel = (unsigned long long)in_sel;
         sum.ns_kernel = GlobalTimerNs() - t_start;
         *P.summary = sum;

@@ -16,13 +16,20 @@ pytestmark = pytest.mark.gpu
 
 @pytest.mark.parametrize("scale", [10, 16])
 @pytest.mark.parametrize("dopt", [False, True])
-@pytest.mark.parametrize("exchange", ["nccl", "peer", "peer-persistent"])
+@pytest.mark.parametrize("exchange", ["nccl", "peer", "peer-persistent", "peer-tail"])
 def test_world1_matches_oracle(gr, orc, scale, dopt, exchange, monkeypatch):
-    """"peer-persistent": the whole search as one cooperative kernel (mgbfs_persistent.cuh, GRB_MG_PERSISTENT=1)"""
+    """"peer-persistent": the whole search as one cooperative kernel (mgbfs_persistent.cuh, GRB_MG_PERSISTENT=1);
+    "peer-tail": the host loop hands the last, short levels to the kernel's TAIL instance (GRB_MG_TAIL=1)"""
     from gunrockinst_b200 import partitioned as pt
     ro, co = rmat_graph(orc, scale)
     g = gr.Graph.from_csr(ro, co, symmetric=True)
-    if exchange == "peer-persistent":
+    monkeypatch.delenv("GRB_MG_TAIL", raising=False)
+    if exchange == "peer-tail":
+        monkeypatch.setenv("GRB_MG_TAIL", "1")
+        monkeypatch.delenv("GRB_MG_PERSISTENT", raising=False)
+        exchange = "peer"
+        persistent = False
+    elif exchange == "peer-persistent":
         monkeypatch.setenv("GRB_MG_PERSISTENT", "1")
         exchange = "peer"
         persistent = True
@@ -89,9 +96,13 @@ def _worker(rank, world, port, scale, q):
         os.environ["GRB_MG_PERSISTENT"] = "1"                   # read when the context is created
         eng_p = pt.DeviceEngine(g)                              # the search as one cooperative kernel per device
         os.environ.pop("GRB_MG_PERSISTENT")
+        os.environ["GRB_MG_TAIL"] = "1"
+        eng_t = pt.DeviceEngine(g)                              # host loop + the TAIL instance for the last levels
+        os.environ.pop("GRB_MG_TAIL")
         ro, co = oracle.rmat_csr(scale, 16)
         res = []
-        for e, exchange in ((eng, "nccl"), (eng, "peer"), (eng_p, "peer"), (eng, "nccl"), (eng, "peer"), (eng_p, "peer")):
+        for e, exchange in ((eng, "nccl"), (eng, "peer"), (eng_p, "peer"), (eng_t, "peer"), (eng, "nccl"), (eng, "peer"), (eng_p, "peer"),
+                            (eng_t, "peer")):
             # alternating: either path starts from the other's leftovers
             for dopt in (True, False):
                 bfs = pt.PartitionedBfs(e, direction_optimized=dopt, exchange=exchange)

@@ -3,9 +3,9 @@
 # with the host loop beside it
 out=gpurun_out; mkdir -p $out
 export GRB_PEER_TIMEOUT_MS=3000
-timeout 200 python -m pytest tests/test_partitioned_gpu.py -m gpu -x -q -k "world1_matches_oracle" > $out/pytest_mgp1.log 2>&1; echo "pytest rc=$?"; tail -3 $out/pytest_mgp1.log
-for mode in persistent; do
-  if [ $mode = host ]; then export GRB_MG_HOST_LOOP=1; else unset GRB_MG_HOST_LOOP; fi
+timeout 200 python -m pytest tests/test_partitioned_gpu.py -m gpu -x -q -k "world1" > $out/pytest_mgp1.log 2>&1; echo "pytest rc=$?"; tail -3 $out/pytest_mgp1.log
+for mode in host; do
+  true
   timeout 300 python -m torch.distributed.run --nnodes=1 --nproc-per-node 1 --master-addr 127.0.0.1 --master-port 29511 bench.py --gpus 1 --steps 32 --warmup 3 --scale 24 --no-cpu > $out/bench_mgp1_$mode.json 2> $out/bench_mgp1_$mode.err; echo "$mode rc=$?"; tail -2 $out/bench_mgp1_$mode.err
   python - <<PY
 import json

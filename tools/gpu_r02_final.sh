@@ -17,3 +17,11 @@ timeout 600 ncu --set full --clock-control none --import-source on --kernel-name
     -k regex:'StreamExpandKernel|HarvestKernel' -s 4 -c 4 -f -o $out/prof_stream_expand_$tag \
     python tools/stream_eval.py 25 1 td_stream_twin > $out/ncu_stream_expand_$tag.log 2>&1
 echo "stream capture rc=$?"
+python tools/stream_eval.py 25 1 idem_stream_twin > $out/ncu_plain_f_$tag.log 2>&1 &&
+timeout 600 ncu --set full --clock-control none --import-source on --kernel-name-base demangled \
+    -k regex:'StreamExpandKernel' -s 1 -c 1 -f -o $out/prof_stream_filter_$tag \
+    python tools/stream_eval.py 25 1 idem_stream_twin > $out/ncu_stream_filter_$tag.log 2>&1
+echo "filter capture rc=$?"
+timeout 300 python tools/stream_eval.py 25 3 td_r1,td_r1_twin,td_stream_twin,dobfs_r1,dobfs_twin,idem_r1,idem_stream_twin > $out/stream_eval_s25_$tag.jsonl 2>/dev/null
+timeout 300 python tools/stream_eval.py 22 3 td_r1,td_r1_twin,td_stream_twin,dobfs_r1,dobfs_twin,idem_r1,idem_stream_twin > $out/stream_eval_s22_$tag.jsonl 2>/dev/null
+echo "evals done"

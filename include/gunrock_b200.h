@@ -233,6 +233,37 @@ int grb_test_bisect(int device, int64_t nodes, const uint32_t *scores, const int
                     int32_t *near_out, int64_t near_cap, int64_t *near_len,
                     int32_t *far_out, int64_t far_cap, int64_t *far_len, uint32_t *min_far_score);
 
+/* ---- the LB advance for callers that cannot allocate --------------------------------
+ * No counterpart in the reference: this entry point was added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight
+ * serving loops, harnesses that forbid it).  It is grb_test_advance(mode = 1 (LB), V2V,
+ * output 0 none / 1 compact) with the same probe functor, except that
+ *   - EVERY array argument is a DEVICE pointer owned by the caller (the graph handle already
+ *     holds the CSR on its device), the kernels are queued on `cuda_stream` (a cudaStream_t,
+ *     NULL = the default stream) and the call returns without synchronising;
+ *   - edge_hits_dev [edges], src_sum_dev [nodes], dst_hits_dev [nodes] are ACCUMULATED into: the
+ *     caller zeroes them; out_queue_dev holds out_cap ids;
+ *   - counters_dev (optional) receives eight 64-bit words: out_len, out_degree (not tracked: 0),
+ *     edges inspected, degree sum of the input frontier, aux0, aux1, overflow (!= 0: out_cap or
+ *     GRB_NOALLOC_MAX_EDGES exceeded, the output is incomplete), reserved;
+ *   - it allocates NOTHING (no cudaMalloc / cudaFree / cudaMallocHost, none of the library's pooled
+ *     arrays): the scratch of the LB mode lives in a static __device__ array of
+ *     GRB_NOALLOC_SCRATCH_BYTES that every GPU which loads the library holds until exit.
+ * Limits: in_len <= GRB_NOALLOC_MAX_ITEMS (a longer frontier is rejected with
+ * cudaErrorInvalidValue and a message on stderr, nothing is launched); at most
+ * GRB_NOALLOC_MAX_EDGES neighbour entries per call (known on the device only: reported through
+ * the overflow counter); a whole graph, not a slice of a partition.
+ * Every call on a device shares the one scratch array: calls that overlap on the GPU (two streams
+ * with no ordering between them, two host threads) race on it -- serialise them. */
+#define GRB_NOALLOC_MAX_ITEMS     262144        /* 2^18 frontier items per call */
+#define GRB_NOALLOC_MAX_EDGES     16777216      /* 2^24 neighbour entries per call */
+#define GRB_NOALLOC_SCRATCH_BYTES 4328960       /* static device memory held per GPU */
+int grb_advance_lb_noalloc(grb_graph_t g, int output,
+                           const int32_t *in_queue_dev, int64_t in_len,
+                           int32_t *out_queue_dev, int64_t out_cap,
+                           int32_t *edge_hits_dev, int64_t *src_sum_dev, int32_t *dst_hits_dev,
+                           uint64_t *counters_dev, void *cuda_stream);
+
 /* ---- 1D-partitioned BFS, one device per process -----------------------------------
  * No reference counterpart (the reference's multi-GPU path is a TODO,
  * gunrock/app/problem_base.cuh:336-338); the striping rule is the reference's

@@ -19,6 +19,10 @@
 //                 (byte offsets), so that the walk below runs with dense lanes
 //                 whatever fraction of the chunk is left (late pull levels leave < 1 %);
 //                 a chunk with nothing to do costs two coalesced loads per word;
+//   1'. dense  -- a chunk with at least kDenseMin vertices to do (the first sweeps of a search) skips the
+//                 list: lane l takes bit l of each word, so the heads, offsets and label stores of a word are
+//                 coalesced accesses of 32 consecutive rows, a word's discoveries are one ballot, and only
+//                 the vertices whose first entry was no parent are listed for the walk (DenseChunk);
 //   2. probe   -- phase-wise over the WHOLE list (up to 8 vertices per lane): first all
 //                 row-offset pairs, then all first-neighbour ids, then all frontier-bit
 //                 probes, so the dependent chain offsets -> neighbour -> bit is three
@@ -80,6 +84,16 @@ struct PullArgs {
 constexpr int kChunkWords = 8;                  // bitmap words a warp sweeps at a time
 constexpr int kChunkVerts = kChunkWords * 32;   // ... = 256 vertices, so list entries fit a byte
 constexpr int kChunkPerLane = kChunkVerts / 32;
+#ifndef GRB_PULL_DENSE_MIN
+#define GRB_PULL_DENSE_MIN 48
+#endif
+#ifndef GRB_PULL_WALK_BATCH
+#define GRB_PULL_WALK_BATCH 4
+#endif
+#ifndef GRB_PULL_DENSE_GROUP
+#define GRB_PULL_DENSE_GROUP 4
+#endif
+constexpr int kDenseMin = GRB_PULL_DENSE_MIN;   // a chunk with at least this many vertices to do takes the dense path (> 256: never)
 constexpr int kTicketCounters = 16;             // chunk tickets are drawn from 16 counters on 16 different L2 lines:
 constexpr int kTicketStride   = 16;             // one counter would serialise ~16K atomics per sweep at scale 22
 
@@ -93,6 +107,90 @@ struct SweepStorage {
     unsigned           found[Policy::WARPS][kChunkWords];   // per warp: discoveries of the chunk, one bit each
     unsigned long long red[Policy::WARPS + 1];
 };
+
+// what a dense chunk adds to the warp's running sums (see SweepImpl)
+struct DenseResult {
+    unsigned n_retry, cands, edges;
+    unsigned long long degree;
+};
+
+// The dense-chunk path of the sweep (steps 1' + 2' in SweepImpl): lane l takes bit l of each of the chunk's words.
+// (Measured as a __noinline__ function, to keep its registers away from the list path: 45 % slower, scale 22 and 25.)
+template <typename Policy, typename Problem, typename Functor, bool SINGLE>
+__device__ __forceinline__ DenseResult DenseChunk(
+    const typename Problem::DataSlice &ds,
+    const PullArgs<typename Policy::VertexId, typename Policy::SizeT> &args,
+    LevelCounters *slot_out, long long w0, unsigned todo,
+    unsigned char *s_cand, unsigned char *s_retry, typename Policy::SizeT *s_begin, unsigned *s_deg, unsigned *s_found)
+{
+    typedef typename Policy::VertexId VertexId;
+    typedef typename Policy::SizeT    SizeT;
+    constexpr bool NEED_SRC = Problem::MARK_PREDECESSORS;
+    const int lane = util::LaneId();
+    DenseResult r;
+    r.n_retry = 0; r.cands = 0; r.edges = 0; r.degree = 0;
+    {
+            constexpr int G = GRB_PULL_DENSE_GROUP;                                // words per group: G independent loads per phase
+#pragma unroll
+            for (int g = 0; g < kChunkWords; g += G) {
+                VertexId h[G];
+                SizeT    rb[G], re[G];
+                unsigned pr[G];
+#pragma unroll
+                for (int j = 0; j < G; ++j) {
+                    const unsigned tw = __shfl_sync(util::kFullMask, todo, (g + j) << 2);
+                    const long long row = ((w0 + g + j) << 5) + lane;
+                    h[j] = -1; rb[j] = 0; re[j] = 0;
+                    if ((tw >> lane) & 1u) {
+                        h[j]  = util::LoadStream(args.head + row);
+                        rb[j] = args.g.row_offsets[row];
+                        re[j] = args.g.row_offsets[row + 1];
+                        ++r.cands;
+                    }
+                }
+#pragma unroll
+                for (int j = 0; j < G; ++j)
+                    pr[j] = h[j] >= 0 ? util::LoadCA(args.frontier_in + (ds.BitPos(h[j]) >> 5)) : 0u;
+#pragma unroll
+                for (int j = 0; j < G; ++j) {
+                    const bool hit = h[j] >= 0 && ((pr[j] >> (ds.BitPos(h[j]) & 31)) & 1u);
+                    const unsigned long long d = (unsigned long long)(re[j] - rb[j]);
+                    bool ok = false;
+                    if (h[j] >= 0) ++r.edges;
+                    if (hit) {
+                        const long long row = ((w0 + g + j) << 5) + lane;
+                        const VertexId child = SINGLE ? (VertexId)row : (VertexId)args.g.part.Global(row);
+                        const VertexId s_id = NEED_SRC ? h[j] : (VertexId)args.iteration;
+                        ok = VisitEdge<Policy, Problem, Functor>(&ds, s_id, child, rb[j], (SizeT)row);
+                        if (ok) {
+                            if (args.fwd_row_offsets)
+                                r.degree += (unsigned long long)(args.fwd_row_offsets[row + 1] - args.fwd_row_offsets[row]);
+                            else
+                                r.degree += d;
+                            if (args.out_queue) {
+                                const unsigned long long at = atomicAdd(&slot_out->out_len, 1ull);
+                                if (at < args.out_cap) args.out_queue[at] = child;
+                                else slot_out->overflow = 1;
+                            }
+                        }
+                    }
+                    const unsigned fm = __ballot_sync(util::kFullMask, ok);
+                    if (lane == 0) s_found[g + j] = fm;
+                    const bool again = !hit && d > 1;
+                    const unsigned am = __ballot_sync(util::kFullMask, again);
+                    if (again) {
+                        const unsigned p = r.n_retry + __popc(am & ((1u << lane) - 1));
+                        s_cand[p]  = (unsigned char)((g + j) * 32 + lane);
+                        s_begin[p] = rb[j];
+                        s_deg[p]   = d > 0x7fffffffull ? 0x7fffffffu : (unsigned)d;
+                        s_retry[p] = (unsigned char)p;
+                    }
+                    r.n_retry += (unsigned)__popc(am);
+                }
+            }
+    }
+    return r;
+}
 
 // The sweep itself, callable from any kernel whose CTAs have Policy::THREADS threads:
 // warp `first_chunk` of `chunk_stride` warps takes chunks first_chunk, first_chunk + chunk_stride, ...
@@ -177,6 +275,17 @@ __device__ __forceinline__ void SweepImpl(
                         : c + chunk_stride;
             continue;
         }
+        unsigned n_retry = 0;
+        if (kDenseMin <= kChunkVerts && args.head != nullptr && total >= (unsigned)kDenseMin) {
+            // ---- 1' + 2'. dense chunk: lane l takes bit l of each word, no candidate list --------------
+            // (early pull levels: most of the chunk is still to do, so packing positions into a list
+            //  buys nothing and its bookkeeping -- ~11 warp instructions per candidate -- was what bound
+            //  the sweep; here heads, offsets and label stores of a word are coalesced accesses of 32
+            //  consecutive rows, the discoveries of a word are one ballot, and only the misses are listed)
+            const DenseResult r = DenseChunk<Policy, Problem, Functor, SINGLE>(ds, args, slot_out, w0, todo, s_cand, s_retry,
+                                                                                   s_begin, s_deg, s_found);
+            n_retry = r.n_retry; my_cands += r.cands; my_edges += r.edges; my_degree += r.degree;
+        } else {
         {
             unsigned at = incl - cnt, m = mine;
             const unsigned pos0 = (unsigned)(my_word * 32 + my_shift);
@@ -275,7 +384,6 @@ __device__ __forceinline__ void SweepImpl(
             }
         }
 #endif
-        unsigned n_retry = 0;
 #pragma unroll
         for (int u = 0; u < U; ++u) {
             if (u * 32 < total) {                               // uniform
@@ -288,6 +396,7 @@ __device__ __forceinline__ void SweepImpl(
                 n_retry += (unsigned)__popc(am);
             }
         }
+        }   // list path
         __syncwarp();
         // ---- 3. walk what is left ------------------------------------------------------------------
         for (unsigned k0 = 0; k0 < n_retry; k0 += 32) {
@@ -305,13 +414,35 @@ __device__ __forceinline__ void SweepImpl(
                 }
                 k = begin + 1;
                 const long long lim = (end - begin > SERIAL_LIMIT) ? begin + SERIAL_LIMIT : end;
-                // (measured: fetching these as aligned groups of four, or four probes per step, is slower --
-                //  the level is bound by L1 wavefronts, one per lane per distinct line, not by latency)
+#if GRB_PULL_WALK_BATCH > 1
+                // WB entries and their frontier words are requested together: the chain of a list shrinks from
+                // two dependent loads per entry to two per batch (a sweep with 3-4 chunks per warp is bound by the
+                // latency of its slowest lane, not by throughput); the entries counted are those an early-exit
+                // walk looks at, as before.  Measured with the dense-chunk path (profiles/r02_pull_dense_ab.txt):
+                // WB = 4 takes the first sweep of a scale-22 search from 48 to 41 us, WB = 8 spills and loses it
+                // again; without the dense path (every vertex walks through the list) batches were no gain.
+                constexpr int WB = GRB_PULL_WALK_BATCH;
+                while (k < lim) {
+                    VertexId x[WB];
+                    unsigned pw[WB];
+#pragma unroll
+                    for (int b = 0; b < WB; ++b) x[b] = (k + b < lim) ? util::LoadStream(args.g.col_indices + k + b) : (VertexId)-1;
+#pragma unroll
+                    for (int b = 0; b < WB; ++b) pw[b] = x[b] >= 0 ? util::LoadCA(args.frontier_in + (ds.BitPos(x[b]) >> 5)) : 0u;
+                    int first = -1;
+#pragma unroll
+                    for (int b = WB - 1; b >= 0; --b)
+                        if (x[b] >= 0 && ((pw[b] >> (ds.BitPos(x[b]) & 31)) & 1u)) { first = b; parent = x[b]; }
+                    if (first >= 0) { found = true; epos = k + first; k = epos + 1; break; }
+                    k = (k + WB < lim) ? k + WB : lim;
+                }
+#else
                 while (k < lim) {
                     const VertexId x = util::LoadStream(args.g.col_indices + k);
                     if (util::BitTest(args.frontier_in, ds.BitPos(x))) { found = true; parent = x; epos = k; ++k; break; }
                     ++k;
                 }
+#endif
                 my_edges += (unsigned long long)(k - begin - 1);    // entries an early-exit walk looks at
             }
             unsigned rest = __ballot_sync(util::kFullMask, act && !found && k < end);

@@ -11,6 +11,8 @@ import numpy as np
 
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import gunrockinst_b200 as gr
+if os.environ.get("GRB_EVAL_LIB"):          # A/B runs: another build of the library (before the first call loads it)
+    gr._capi.LIB_PATH = os.environ["GRB_EVAL_LIB"]
 
 scale = int(sys.argv[1]) if len(sys.argv) > 1 else 22
 runs = int(sys.argv[2]) if len(sys.argv) > 2 else 3

@@ -161,6 +161,7 @@ def lib():
     sig("grb_test_filter", C.c_int, [C.c_int, i64, C.c_int, p, i64, p, i64, C.POINTER(i64), p])
     sig("grb_test_bisect", C.c_int, [C.c_int, i64, p, p, i64, C.c_int, C.c_uint32, C.c_uint32, p, p, i64, C.POINTER(i64),
                                      p, i64, C.POINTER(i64), C.POINTER(C.c_uint32)])
+    sig("grb_test_row_bins", C.c_int, [p, p, i64, p, p, p, p, i64, p])
     # no allocation inside: every array argument is a device pointer (include/gunrock_b200.h)
     sig("grb_advance_lb_noalloc", C.c_int, [p, C.c_int, p, i64, p, i64, p, p, p, p, p])
     sig("grb_mgbfs_create", C.c_int, [p, pp])

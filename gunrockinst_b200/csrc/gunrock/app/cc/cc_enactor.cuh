@@ -11,11 +11,17 @@
 //   2. filter in apply-only mode (the reference's Kernel2) with PtrJumpFunctor over the
 //      identity frontier: flatten every vertex to its root and count the roots.
 // Labels: smallest vertex id of the component, as in the reference.
+// Default route of pass 1 (cc_row_hook.cuh): the rows binned by length inside Enact (one small
+// kernel + one 64-byte read-back, part of the measured time) and ONE kernel in which the lanes
+// that walk a row keep its root; GRB_CC_HOOK=lb selects the advance.
 //
 // Algorithmic HBM bytes: hook pass 2*sizeof(SizeT) per vertex + 4 (column id) + 8 (two
 // parent probes) per CSR entry; jump pass 12 per vertex.
 #pragma once
+#include <cstdlib>
+#include <cstring>
 #include "cc_functor.cuh"
+#include "cc_row_hook.cuh"
 #include "../enactor_base.cuh"
 
 namespace gunrock {
@@ -35,11 +41,16 @@ class CCEnactor : public EnactorBase {
     typedef oprtr::filter::KernelPolicy<Problem, 256, 4, 6, 0>             FilterPolicy;
 
     oprtr::advance::LbScratch<SizeT> lb_scratch;
+    oprtr::rows::Bins<SizeT> row_bins;
+    bool by_rows = false;
     bool set_up = false;
 
     cudaError_t Setup(Problem *problem, cudaStream_t s)
     {
         GR_TRY(SetupBase(problem->graph->device, s));
+        const char *route = getenv("GRB_CC_HOOK");
+        by_rows = problem->graph->part.log_parts == 0 && !(route && strcmp(route, "lb") == 0);
+        if (by_rows) GR_TRY(row_bins.Allocate((size_t)problem->graph->local_nodes, (size_t)problem->graph->edges));
         GR_TRY(lb_scratch.Allocate((size_t)problem->graph->local_nodes + 1, (size_t)problem->graph->edges + 1,
                                    AdvancePolicy::SCAN_TILE, AdvancePolicy::TILE_EDGES, s));
         set_up = true;
@@ -58,18 +69,34 @@ class CCEnactor : public EnactorBase {
         const unsigned osz = (unsigned)sizeof(SizeT);
 
         // ---- 1. hook: one pass over the CSR entries ------------------------------------------------
-        oprtr::advance::Args<VertexId, SizeT> a;
-        a.g = g.View();
-        a.in_queue = nullptr; a.out_queue = nullptr;        // identity frontier, functor side effects only
-        a.in_len = n; a.d_in_len = nullptr; a.out_cap = 0;
-        a.slots = work_progress.d_slots.ptr;
-        a.queue_index = frontier_attribute.queue_index;
-        a.iteration = 0;
-        a.output = oprtr::advance::OUT_NONE;
-        GR_TRY((oprtr::advance::LaunchKernel<AdvancePolicy, Problem, HookFn>(
-            oprtr::advance::LB, dev, ds, a, &lb_scratch, (unsigned long long)g.edges, stream)));
-        enactor_stats.launches += 2;
-        frontier_attribute.queue_index++;
+        unsigned long long row_entries = 0;
+        if (by_rows) {
+            GR_TRY(row_bins.Build(g.row_offsets.ptr, nullptr, n, g.part, stream));
+            CcRowHookArgs<SizeT> h;
+            h.row_offsets = g.row_offsets.ptr; h.col_indices = g.col_indices.ptr;
+            h.parent = ds.d_component_ids; h.skip_upper = ds.skip_upper;
+            h.bins = row_bins.view;
+            row_entries = h.bins.entries;
+            if (h.bins.Blocks()) {
+                CcRowHookKernel<SizeT><<<h.bins.Blocks(), oprtr::rows::kThreads, 0, stream>>>(h);
+                GR_TRY(cudaGetLastError());
+            }
+            enactor_stats.launches += 2;
+            frontier_attribute.queue_index++;
+        } else {
+            oprtr::advance::Args<VertexId, SizeT> a;
+            a.g = g.View();
+            a.in_queue = nullptr; a.out_queue = nullptr;        // identity frontier, functor side effects only
+            a.in_len = n; a.d_in_len = nullptr; a.out_cap = 0;
+            a.slots = work_progress.d_slots.ptr;
+            a.queue_index = frontier_attribute.queue_index;
+            a.iteration = 0;
+            a.output = oprtr::advance::OUT_NONE;
+            GR_TRY((oprtr::advance::LaunchKernel<AdvancePolicy, Problem, HookFn>(
+                oprtr::advance::LB, dev, ds, a, &lb_scratch, (unsigned long long)g.edges, stream)));
+            enactor_stats.launches += 2;
+            frontier_attribute.queue_index++;
+        }
 
         // ---- 2. pointer jumping: flatten + count roots ---------------------------------------------
         oprtr::filter::Args<VertexId, Value> fa;
@@ -87,6 +114,7 @@ class CCEnactor : public EnactorBase {
                                cudaMemcpyDeviceToHost, stream));
         oprtr::LevelCounters c;
         GR_TRY(work_progress.Fetch(1, c, stream));           // the hook pass accumulated into slot 1
+        if (by_rows) c.edges = row_entries;
         enactor_stats.edges_inspected = c.edges;
         enactor_stats.total_queued = 2 * n;
         enactor_stats.algo_bytes = n * (2ull * osz) + 12ull * c.edges + 12ull * n;

@@ -1,0 +1,145 @@
+// cc_row_hook.cuh -- the hook pass of connected components over rows binned by length.
+//
+// Same hook rule as HookFunctor (cc_functor.cuh; the reference's HookInit / HookMax,
+// gunrock/app/cc/cc_functor.cuh:65-103,184-250: the larger root goes under the smaller one) and the
+// same fixed point, so the labels after the flattening pass are identical.  What changes is who
+// does the work.  Through the LB advance every CSR entry is a thread of its own: it pays the tile
+// owner search, then chases BOTH end points to their roots (two dependent loads each once the
+// giant component has formed).  Here a row stays with the lanes that walk it (oprtr/row_bins.cuh:
+// four lanes, a warp, or a warp per 2048-entry piece), and every lane remembers the last root it
+// found for the row's vertex: an ancestor stays an ancestor for ever (parents only move to
+// ancestors, roots only get linked under smaller ids), so the next entry starts its chase from
+// there -- one load that hits the same hot line for the whole warp -- and only the neighbour's
+// side is a chase through memory.  The first hop of four neighbours is requested at once.
+// GRB_CC_HOOK=lb selects the advance route.
+#pragma once
+#include "cc_functor.cuh"
+#include "../../oprtr/row_bins.cuh"
+
+namespace gunrock {
+namespace app {
+namespace cc {
+
+namespace rows = oprtr::rows;
+
+template <typename SizeT>
+struct CcRowHookArgs {
+    const SizeT *row_offsets;
+    const int   *col_indices;
+    int         *parent;
+    bool         skip_upper;        // symmetric CSR: each undirected edge appears twice, hook it once
+    rows::View   bins;
+};
+
+// FindRoot for a vertex whose parent has already been loaded
+__device__ __forceinline__ int FindRootFrom(int *parent, int x, int p)
+{
+    while (p != x) {
+        const int gp = util::LoadCG(parent + p);
+        if (gp != p) util::StoreCG(parent + x, gp);     // path halving
+        x = p; p = gp;
+    }
+    return x;
+}
+
+// link the components of u (an ancestor of the row's vertex) and of d, whose parent is pd;
+// returns the root both ended under
+__device__ __forceinline__ int HookPair(int *parent, int u, int d, int pd)
+{
+    int v = FindRootFrom(parent, d, pd);
+    u = FindRoot(parent, u);
+    for (;;) {
+        if (u == v) return u;
+        const int hi = u > v ? u : v, lo = u > v ? v : u;
+        const int old = atomicCAS(parent + hi, hi, lo);
+        if (old == hi) return lo;               // linked larger root -> smaller root
+        u = FindRoot(parent, old);              // `hi` stopped being a root meanwhile: chase again
+        v = lo;
+        v = FindRoot(parent, v);
+    }
+}
+
+// entries [beg, end) of row s by a whole warp; u = this lane's known ancestor of s
+template <typename SizeT>
+__device__ __forceinline__ void WarpHookRange(const CcRowHookArgs<SizeT> &a, int s, SizeT beg, SizeT end, int &u)
+{
+    const int *col = a.col_indices;
+    SizeT e = beg + (SizeT)util::LaneId();
+    for (; end - e > 96; e += 128) {
+        int d[4], pd[4];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) d[j] = util::LoadStream(col + e + 32 * j);
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            const bool take = d[j] != s && !(a.skip_upper && d[j] > s);
+            if (!take) d[j] = -1;
+            pd[j] = take ? util::LoadCG(a.parent + d[j]) : 0;
+        }
+#pragma unroll
+        for (int j = 0; j < 4; ++j)
+            if (d[j] >= 0) u = HookPair(a.parent, u, d[j], pd[j]);
+    }
+    for (; e < end; e += 32) {
+        const int d = util::LoadStream(col + e);
+        if (d != s && !(a.skip_upper && d > s)) u = HookPair(a.parent, u, d, util::LoadCG(a.parent + d));
+    }
+}
+
+template <typename SizeT>
+__global__ void __launch_bounds__(rows::kThreads)
+CcRowHookKernel(const __grid_constant__ CcRowHookArgs<SizeT> a)
+{
+    constexpr int WARPS = rows::kWarps;
+    const rows::View &b = a.bins;
+    const int lane = util::LaneId(), warp = util::WarpId();
+    if (blockIdx.x < b.blocks_big) {
+        const unsigned long long piece = (unsigned long long)blockIdx.x * WARPS + warp;
+        if (piece < b.n_pieces) {
+            SizeT beg, end;
+            const int s = rows::PieceRange<SizeT>(b, a.row_offsets, piece, beg, end);
+            int u = s;
+            WarpHookRange<SizeT>(a, s, beg, end, u);
+        }
+    } else if (blockIdx.x < b.blocks_big + b.blocks_medium) {
+        const unsigned long long first =
+            ((unsigned long long)(blockIdx.x - b.blocks_big) * WARPS + warp) * (unsigned long long)rows::kMediumPerWarp;
+        for (int k = 0; k < rows::kMediumPerWarp; ++k) {
+            const unsigned long long idx = first + k;
+            if (idx >= b.n_medium) break;                       // warp-uniform
+            const int s = b.medium_rows[idx];
+            int u = s;
+            WarpHookRange<SizeT>(a, s, a.row_offsets[s], a.row_offsets[s + 1], u);
+        }
+    } else {
+        const int group = lane >> 2, g = lane & 3;
+        const unsigned long long first =
+            ((unsigned long long)(blockIdx.x - b.blocks_big - b.blocks_medium) * WARPS + warp) *
+            (unsigned long long)(8 * rows::kSmallIters);
+        for (int k = 0; k < rows::kSmallIters; ++k) {
+            const unsigned long long idx = first + (unsigned long long)(k * 8 + group);
+            if (idx >= b.n_small) continue;
+            const int s = b.small_rows[idx];
+            const SizeT beg = a.row_offsets[s], end = a.row_offsets[s + 1];
+            int d[rows::kSmallMax / 4], pd[rows::kSmallMax / 4];
+#pragma unroll
+            for (int j = 0; j < rows::kSmallMax / 4; ++j) {
+                const SizeT e = beg + (SizeT)(g + 4 * j);
+                d[j] = e < end ? util::LoadStream(a.col_indices + e) : -1;
+            }
+#pragma unroll
+            for (int j = 0; j < rows::kSmallMax / 4; ++j) {
+                const bool take = d[j] >= 0 && d[j] != s && !(a.skip_upper && d[j] > s);
+                if (!take) d[j] = -1;
+                pd[j] = take ? util::LoadCG(a.parent + d[j]) : 0;
+            }
+            int u = s;
+#pragma unroll
+            for (int j = 0; j < rows::kSmallMax / 4; ++j)
+                if (d[j] >= 0) u = HookPair(a.parent, u, d[j], pd[j]);
+        }
+    }
+}
+
+}  // namespace cc
+}  // namespace app
+}  // namespace gunrock

@@ -27,10 +27,13 @@
 //     exchange  64-byte counter blocks of all devices (also the barrier behind the stores)
 // Needs a symmetric graph (in-edges == out-edges), like the partitioned BFS.
 #pragma once
+#include <cstdlib>
+#include <cstring>
 #include <vector>
 #include "../enactor_base.cuh"
 #include "../bfs/mgbfs_p2p.cuh"
 #include "../../util/memset_kernel.cuh"
+#include "pr_row_sweep.cuh"
 
 namespace gunrock {
 namespace app {
@@ -177,7 +180,7 @@ MgPrPruneFinishKernel(long long local_nodes, graph::Partition part, PrPeerTable 
 }
 
 // after the pruning: queue of the surviving rows (global ids), first contributions
-// (curr / degree, 0 for pruned rows) into generation 0 of every replica; a pruned row's rank is
+// (curr / degree, 0 for pruned rows -- these in both generations) into generation 0 of every replica; a pruned row's rank is
 // what the single-device loop leaves it with after its first sweep, 0
 template <int THREADS>
 __global__ void __launch_bounds__(THREADS)
@@ -187,6 +190,7 @@ MgPrStartKernel(long long local_nodes, graph::Partition part, PrPeerTable peers,
     __shared__ unsigned s_warp[THREADS / 32 + 1];
     __shared__ unsigned long long s_base;
     const unsigned long long first = (unsigned long long)part.rank * (unsigned long long)local_nodes;
+    const unsigned long long half = (unsigned long long)local_nodes * (unsigned long long)peers.parts;
     const long long rounds = (local_nodes + (long long)gridDim.x * THREADS - 1) / ((long long)gridDim.x * THREADS);
     for (long long k = 0; k < rounds; ++k) {
         const long long r = (k * gridDim.x + blockIdx.x) * THREADS + threadIdx.x;
@@ -197,6 +201,8 @@ MgPrStartKernel(long long local_nodes, graph::Partition part, PrPeerTable peers,
             double cv = 0.0;
             if (alive) cv = rank[r] / (double)d; else rank[r] = 0.0;
             for (int p = 0; p < peers.parts; ++p) peers.contrib[p][first + (unsigned long long)r] = cv;
+            // (a sweep that only visits the alive rows -- pr_row_sweep.cuh -- reads both generations of a pruned row)
+            if (!alive) for (int p = 0; p < peers.parts; ++p) peers.contrib[p][half + first + (unsigned long long)r] = 0.0;
         }
         unsigned total;
         const unsigned excl = util::BlockExclusiveSum<THREADS>(alive ? 1u : 0u, s_warp, total);
@@ -253,6 +259,7 @@ class MGPREnactor : public EnactorBase {
         double elapsed_ms = 0, sweep_ms = 0;
         long long iterations = 0, prune_sweeps = 0, launches = 0;
         unsigned long long edges = 0, valid_nodes = 0, exchange_bytes = 0;
+        bool by_rows = false;           // the sweeps ran as pr_row_sweep.cuh's kernel
     };
 
     Graph *graph = nullptr;
@@ -261,6 +268,9 @@ class MGPREnactor : public EnactorBase {
     util::DeviceArray<int>      deg;
     util::DeviceArray<VertexId> queue;
     oprtr::advance::LbScratch<SizeT> lb_scratch;
+    // single device: the rows of the power iteration binned by length (pr_row_sweep.cuh)
+    bool row_sweep = false;
+    oprtr::rows::Bins<SizeT> row_bins;
     bfs::PeerComm comm;
     PrPeerTable peers;
     unsigned long long half = 0, half_words = 0;
@@ -290,6 +300,9 @@ class MGPREnactor : public EnactorBase {
         GR_TRY(rank.Allocate(ln + 1)); GR_TRY(acc.Allocate(ln + 1));
         GR_TRY(deg.Allocate(ln + 1));  GR_TRY(queue.Allocate(ln + 1));
         GR_TRY(lb_scratch.Allocate(ln + 1, (size_t)g->edges + 1, AdvancePolicy::SCAN_TILE, AdvancePolicy::TILE_EDGES, s));
+        const char *route = getenv("GRB_PR_SWEEP");
+        row_sweep = P == 1 && !(route && strcmp(route, "lb") == 0);
+        if (row_sweep) GR_TRY(row_bins.Allocate(ln, (size_t)g->edges));
         GR_TRY(comm.Setup((int)P, g->part.rank, s));
         peers = PrPeerTable();
         peers.parts = (int)P; peers.rank = g->part.rank;
@@ -323,6 +336,27 @@ class MGPREnactor : public EnactorBase {
         enactor_stats.launches += 2;
         return oprtr::advance::LaunchKernel<AdvancePolicy, Problem, Functor>(
             oprtr::advance::LB, dev, ds, a, &lb_scratch, (unsigned long long)g.edges, stream);
+    }
+
+    // the alive rows (queue[0 .. qlen)) into the three bins of oprtr/row_bins.cuh; fills everything of `out` that
+    // does not change from sweep to sweep
+    cudaError_t BinRows(unsigned long long qlen, double delta, double threshold, VertexId src, PrRowSweepArgs<SizeT> *out)
+    {
+        Graph &g = *graph;
+        GR_TRY(row_bins.Build(g.row_offsets.ptr, queue.ptr, qlen, g.part, stream));
+        ++enactor_stats.launches;
+        PrRowSweepArgs<SizeT> a;
+        a.bins = row_bins.view;
+        if (a.bins.n_small + a.bins.n_medium + a.bins.n_big != qlen)       // every alive row has entries
+            return util::GRError(cudaErrorUnknown, "PageRank row bins do not add up", __FILE__, __LINE__);
+        a.row_offsets = g.row_offsets.ptr; a.col_indices = g.col_indices.ptr;
+        a.contrib_in = nullptr; a.contrib_out = nullptr;
+        a.deg = deg.ptr; a.rank = rank.ptr; a.acc = acc.ptr;
+        a.delta = delta; a.threshold = threshold; a.src = src;
+        a.part = g.part; a.local_nodes = g.local_nodes;
+        a.counters = Counters();
+        *out = a;
+        return cudaSuccess;
     }
 
     // every rank calls it with the same arguments
@@ -374,16 +408,34 @@ class MGPREnactor : public EnactorBase {
             st.exchange_bytes += 8ull * (unsigned long long)ln * (unsigned long long)(P - 1);
             local_q = comm.h_all.ptr[me].out_len;
 
+            PrRowSweepArgs<SizeT> rows;
+            const bool by_rows = row_sweep && local_q > 0;
+            if (by_rows) GR_TRY(BinRows(local_q, delta, threshold, src, &rows));
+            st.by_rows = by_rows;
+
             // ---- (b) power iteration (pr_enactor.cuh:346-487) ---------------------------------------------
             GR_TRY(cudaEventRecord(ev1, stream));
             swept = true;
             int cgen = 0;
             for (;;) {
                 GR_TRY(cudaMemsetAsync(Counters(), 0, sizeof(oprtr::LevelCounters), stream));
-                if (local_q) GR_TRY(Advance<GatherFunctor>(MakeDataSlice(cgen, 0), local_q, st.iterations));
-                MgPrFinishKernel<<<util::FillGrid(row_grid), 256, 0, stream>>>(
-                    ln, g.part, peers, cgen ^ 1, deg.ptr, rank.ptr, acc.ptr, delta, threshold, src, Counters());
-                GR_TRY(cudaGetLastError());
+                if (by_rows) {
+                    rows.contrib_in  = contrib.ptr + (unsigned long long)cgen * half;
+                    rows.contrib_out = contrib.ptr + (unsigned long long)(cgen ^ 1) * half +
+                                       (unsigned long long)me * (unsigned long long)ln;
+                    PrRowSweepKernel<SizeT><<<rows.bins.Blocks(), oprtr::rows::kThreads, 0, stream>>>(rows);
+                    GR_TRY(cudaGetLastError());
+                    if (rows.bins.n_big) {
+                        PrBigRowFinishKernel<SizeT><<<util::FillGrid(rows.bins.n_big), 256, 0, stream>>>(rows);
+                        GR_TRY(cudaGetLastError());
+                        ++enactor_stats.launches;
+                    }
+                } else {
+                    if (local_q) GR_TRY(Advance<GatherFunctor>(MakeDataSlice(cgen, 0), local_q, st.iterations));
+                    MgPrFinishKernel<<<util::FillGrid(row_grid), 256, 0, stream>>>(
+                        ln, g.part, peers, cgen ^ 1, deg.ptr, rank.ptr, acc.ptr, delta, threshold, src, Counters());
+                    GR_TRY(cudaGetLastError());
+                }
                 GR_TRY(comm.Exchange(Counters(), stream));
                 enactor_stats.launches += 2;
                 st.exchange_bytes += 8ull * (unsigned long long)ln * (unsigned long long)(P - 1);

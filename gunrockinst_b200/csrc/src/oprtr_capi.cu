@@ -16,6 +16,7 @@
 #include "graph_handle.cuh"
 #include "../gunrock/app/enactor_base.cuh"
 #include "../gunrock/app/problem_base.cuh"
+#include "../gunrock/oprtr/row_bins.cuh"
 
 namespace {
 
@@ -289,4 +290,41 @@ extern "C" int grb_test_bisect(int device, int64_t nodes, const uint32_t *scores
     GRB_TRY(d_mark.ToHost(far_mark, words, s));
     GRB_TRY(cudaStreamSynchronize(s));
     return 0;
+}
+
+// ---- rows binned by length (oprtr/row_bins.cuh), stand-alone ---------------------------------------------
+template <typename SizeT>
+static int TestRowBins(gunrock::graph::DeviceCsr<int, SizeT> *g, cudaStream_t s, const int32_t *queue, int64_t qlen,
+                       int32_t *small_rows, int32_t *medium_rows, int32_t *big_rows, int32_t *big_pieces,
+                       int64_t piece_cap, int64_t *counts)
+{
+    using namespace gunrock;
+    util::DeviceArray<int> d_queue;
+    oprtr::rows::Bins<SizeT> bins;
+    GRB_TRY(bins.Allocate((size_t)g->local_nodes, (size_t)g->edges));
+    if (queue) GRB_TRY(d_queue.FromHost(queue, (size_t)qlen, s));
+    GRB_TRY(bins.Build(g->row_offsets.ptr, queue ? d_queue.ptr : nullptr, (unsigned long long)qlen, g->part, s));
+    const oprtr::rows::View &v = bins.view;
+    if ((int64_t)v.n_pieces > piece_cap) return (int)cudaErrorInvalidValue;
+    counts[0] = (int64_t)v.n_small; counts[1] = (int64_t)v.n_medium; counts[2] = (int64_t)v.n_big;
+    counts[3] = (int64_t)v.n_pieces; counts[4] = (int64_t)v.entries;
+    counts[5] = v.blocks_big; counts[6] = v.blocks_medium; counts[7] = v.blocks_small;
+    GRB_TRY(bins.small_rows.ToHost(small_rows, (size_t)v.n_small, s));
+    GRB_TRY(bins.medium_rows.ToHost(medium_rows, (size_t)v.n_medium, s));
+    GRB_TRY(bins.big_rows.ToHost(big_rows, (size_t)v.n_big, s));
+    GRB_TRY(bins.big_pieces.ToHost((int2 *)big_pieces, (size_t)v.n_pieces, s));
+    GRB_TRY(cudaStreamSynchronize(s));
+    return 0;
+}
+
+extern "C" int grb_test_row_bins(grb_graph_t g, const int32_t *queue, int64_t qlen, int32_t *small_rows,
+                                 int32_t *medium_rows, int32_t *big_rows, int32_t *big_pieces, int64_t piece_cap,
+                                 int64_t *counts)
+{
+    if (!g || qlen < 0 || qlen > g->local_nodes() || !small_rows || !medium_rows || !big_rows || !big_pieces || !counts)
+        return (int)cudaErrorInvalidValue;
+    int rc = grb_select_device(g->device());
+    if (rc) return rc;
+    return g->g32 ? TestRowBins<int>(g->g32, g->stream, queue, qlen, small_rows, medium_rows, big_rows, big_pieces, piece_cap, counts)
+                  : TestRowBins<long long>(g->g64, g->stream, queue, qlen, small_rows, medium_rows, big_rows, big_pieces, piece_cap, counts);
 }

@@ -100,8 +100,10 @@ static cudaError_t RunPrGather(gunrock::graph::DeviceCsr<int, SizeT> *g, cudaStr
         stats->total_queued = st.valid_nodes * (unsigned long long)st.iterations;
         stats->nodes_visited = (int64_t)st.valid_nodes;
         // per walked entry 4 (column) + 8 (contribution); per alive vertex and sweep: queue 4, offsets,
-        // accumulator 8 + 8, rank 8 + 8, degree 4, contribution 8
-        stats->algo_bytes = 12ull * st.edges + (unsigned long long)st.iterations * st.valid_nodes * (48ull + 2ull * sizeof(SizeT));
+        // accumulator 8 + 8 (not with the row-binned sweep, whose sums stay in registers), rank 8 + 8,
+        // degree 4, contribution 8
+        stats->algo_bytes = 12ull * st.edges + (unsigned long long)st.iterations * st.valid_nodes *
+                                                   ((st.by_rows ? 32ull : 48ull) + 2ull * sizeof(SizeT));
         stats->push_levels = (int32_t)st.iterations;
         stats->pull_levels = (int32_t)st.prune_sweeps;
         stats->gpu_launches = st.launches;

@@ -233,6 +233,16 @@ int grb_test_bisect(int device, int64_t nodes, const uint32_t *scores, const int
                     int32_t *near_out, int64_t near_cap, int64_t *near_len,
                     int32_t *far_out, int64_t far_cap, int64_t *far_len, uint32_t *min_far_score);
 
+/* The row bins of the fixed-row-set passes on their own (oprtr/row_bins.cuh; the passes replace the reference's
+ * load-balanced advance, gunrock/oprtr/edge_map_partitioned/kernel.cuh:242-559, where the rows are known in advance:
+ * PageRank's sweeps, gunrock/app/pr/pr_enactor.cuh:346-487, and CC's hook pass, gunrock/app/cc/cc_enactor.cuh:443-560).
+ * queue: qlen global vertex ids in host memory, or NULL for rows 0 .. qlen.  Rows of 1..16 entries go to small_rows,
+ * 17..2048 to medium_rows, longer ones to big_rows and, cut into 2048-entry pieces, to big_pieces ((row, piece) pairs,
+ * room for piece_cap of them); each of the three row arrays needs room for qlen ids.  counts[8] = rows per list,
+ * pieces, entries of all listed rows, and the CTAs a pass assigns to pieces / medium rows / small rows. */
+int grb_test_row_bins(grb_graph_t g, const int32_t *queue, int64_t qlen, int32_t *small_rows, int32_t *medium_rows,
+                      int32_t *big_rows, int32_t *big_pieces, int64_t piece_cap, int64_t *counts);
+
 /* ---- the LB advance for callers that cannot allocate --------------------------------
  * No counterpart in the reference: this entry point was added
  * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight

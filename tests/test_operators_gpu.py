@@ -281,3 +281,66 @@ def test_near_far_split_reports_overflow(gr):
     scores = np.full(n, 5, np.uint32)
     _, nl, _, fl, _, _ = run_bisect(gr, n, scores, np.arange(n), False, 0, 10, np.zeros((n + 31) // 32, np.uint32), cap=100)
     assert nl == -1
+
+
+# ---- rows binned by length, stand-alone (oprtr/row_bins.cuh: the fixed-row-set passes of PageRank and CC) -----------
+def run_row_bins(gr, g, queue):
+    from gunrockinst_b200 import _capi
+    n, m = g.local_nodes, g.edges
+    q = np.ascontiguousarray(queue, dtype=np.int32) if queue is not None else None
+    qlen = q.size if q is not None else n
+    small = np.full(qlen + 1, -1, np.int32); medium = np.full(qlen + 1, -1, np.int32); big = np.full(qlen + 1, -1, np.int32)
+    cap = 2 * (m // 2048) + 2
+    pieces = np.full((cap, 2), -1, np.int32)
+    counts = np.zeros(8, np.int64)
+    p = lambda a: a.ctypes.data_as(C.c_void_p) if a is not None else None
+    rc = _capi.lib().grb_test_row_bins(g._h, p(q), qlen, p(small), p(medium), p(big), p(pieces), cap, p(counts))
+    assert rc == 0
+    return small[:counts[0]], medium[:counts[1]], big[:counts[2]], pieces[:counts[3]], counts
+
+
+def star_csr(n, hubs):
+    """undirected: every hub is adjacent to every vertex; plus a ring, so that all three bins are populated"""
+    rows = [set() for _ in range(n)]
+    for h in hubs:
+        for v in range(n):
+            if v != h:
+                rows[h].add(v); rows[v].add(h)
+    for v in range(0, n, 3):
+        for k in range(1, 1 + (v % 40)):
+            w = (v + k) % n
+            rows[v].add(w); rows[w].add(v)
+    ro = np.zeros(n + 1, np.int64)
+    ro[1:] = np.cumsum([len(r) for r in rows])
+    co = np.concatenate([np.array(sorted(r), np.int32) for r in rows])
+    return ro, co
+
+
+@pytest.mark.parametrize("case", ["rmat14", "star", "star_subset", "empty_rows"])
+def test_row_bins_contract(gr, orc, case):
+    if case == "rmat14":
+        ro, co = rmat_graph(orc, 14, 16)
+        queue = None
+    elif case in ("star", "star_subset"):
+        ro, co = star_csr(5000, [0, 17, 4999])
+        queue = None if case == "star" else np.random.RandomState(5).permutation(5000)[:3111]
+    else:
+        ro = np.array([0, 0, 3, 3, 3, 20, 20], np.int64)
+        co = np.arange(20, dtype=np.int32) % 6
+        queue = None
+    n = ro.size - 1
+    g = gr.Graph.from_csr(ro, co, symmetric=False)
+    small, medium, big, pieces, counts = run_row_bins(gr, g, queue)
+    g.close()
+    rows = np.arange(n) if queue is None else np.asarray(queue)
+    ln = (ro[1:] - ro[:-1])[rows]
+    assert np.array_equal(np.sort(small), np.sort(rows[(ln >= 1) & (ln <= 16)]))
+    assert np.array_equal(np.sort(medium), np.sort(rows[(ln >= 17) & (ln <= 2048)]))
+    assert np.array_equal(np.sort(big), np.sort(rows[ln > 2048]))
+    want_pieces = sorted((int(r), k) for r, l in zip(rows[ln > 2048], ln[ln > 2048]) for k in range((int(l) + 2047) // 2048))
+    assert sorted(map(tuple, pieces.tolist())) == want_pieces
+    assert counts[4] == int(ln.sum())
+    # the CTAs of a pass cover every list: 8 pieces, 32 medium rows, 256 small rows per CTA
+    assert counts[5] == (len(want_pieces) + 7) // 8 and counts[6] == (medium.size + 31) // 32 and counts[7] == (small.size + 255) // 256
+    if case == "star":
+        assert big.size == 3 and medium.size > 0 and small.size > 0

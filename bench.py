@@ -301,6 +301,9 @@ def run_full_size_configs(args, peak):
     g25 = ro = co = None
     try:
         g25 = gr.Graph.rmat(25)
+        t_tw = time.time()
+        g25.build_twin()                    # preprocessing (one more CSR, hubs first): the searches and PageRank below use it
+        out["s25_twin_build_s"] = round(time.time() - t_tw, 3)
         if check:
             import oracle
             oracle.build()
@@ -341,7 +344,16 @@ def run_full_size_configs(args, peak):
         r = rate(st, st["elapsed_ms"])
         r.update(sweeps=st["iterations"], ms_per_sweep=st["elapsed_ms"] / max(st["iterations"], 1),
                  rank_sum=float(ranks.sum()), rank_max=float(ranks.max()),
-                 parity_note="PageRank is unpinned by the reference's own tests (stale golden, SURVEY.md section 4); "
+                 layout="row-binned sweep kernel on the degree-ordered twin of the graph (grb_graph_build_twin, "
+                        "s25_twin_build_s); ranks in the caller's ids")
+        # the same sweeps in the caller's vertex order, and through the LB advance (the routes this one replaced)
+        for key, var, val in (("ms_per_sweep_callers_order", "GRB_PR_TWIN", "0"), ("ms_per_sweep_lb_advance", "GRB_PR_SWEEP", "lb")):
+            os.environ["GRB_PR_TWIN"] = "0"
+            os.environ[var] = val
+            _, _, st8 = gr.pagerank(g25, delta=0.85, threshold=1e-6, max_iter=8)
+            r[key] = st8["reserved"] / 1000.0 / max(st8["iterations"], 1)
+            os.environ.pop("GRB_PR_TWIN", None); os.environ.pop(var, None)
+        r.update(parity_note="PageRank is unpinned by the reference's own tests (stale golden, SURVEY.md section 4); "
                              "checked against the fp64 restatement of its functors: per-vertex 1e-6 after 5 sweeps here, "
                              "to convergence at scale 22 in tests/test_pr_gpu.py")
         if check:

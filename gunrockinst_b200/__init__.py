@@ -124,6 +124,17 @@ class Graph:
         """attach the transpose (CSC) of a directed graph: the inverse graph of a direction-optimising BFS"""
         _capi.check(_capi.lib().grb_graph_build_transpose(self._h), "grb_graph_build_transpose")
 
+    def build_twin(self):
+        """attach the degree-ordered twin (same graph, hubs first): searches with degree_order=True and PageRank
+        sweeps of a symmetric graph run on it; results stay in the caller's vertex ids"""
+        _capi.check(_capi.lib().grb_graph_build_twin(self._h), "grb_graph_build_twin")
+
+    def twin_entries(self):
+        """entries of the attached twin (== `edges`), -1 without one"""
+        out = C.c_int64(-1)
+        _capi.check(_capi.lib().grb_graph_twin_entries(self._h, C.byref(out)), "grb_graph_twin_entries")
+        return int(out.value)
+
     def check_symmetric(self):
         """True iff the resident CSR equals its transpose (what `symmetric=True` promises)"""
         out = C.c_int(0)

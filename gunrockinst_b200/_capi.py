@@ -138,6 +138,8 @@ def lib():
     sig("grb_graph_rmat", C.c_int, [C.c_int, C.c_int, i64, u64, C.c_int, dbl, dbl, dbl, dbl,
                                     C.c_int, C.c_int, u64, C.c_int, pp])
     sig("grb_graph_build_transpose", C.c_int, [p])
+    sig("grb_graph_build_twin", C.c_int, [p])
+    sig("grb_graph_twin_entries", C.c_int, [p, C.POINTER(i64)])
     sig("grb_graph_check_symmetric", C.c_int, [p, C.POINTER(C.c_int)])
     sig("grb_graph_get_info", C.c_int, [p, C.POINTER(GraphInfo)])
     sig("grb_graph_download", C.c_int, [p, p, p, p])

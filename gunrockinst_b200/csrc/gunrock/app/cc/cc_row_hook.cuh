@@ -9,8 +9,9 @@
 // four lanes, a warp, or a warp per 2048-entry piece), and every lane remembers the last root it
 // found for the row's vertex: an ancestor stays an ancestor for ever (parents only move to
 // ancestors, roots only get linked under smaller ids), so the next entry starts its chase from
-// there -- one load that hits the same hot line for the whole warp -- and only the neighbour's
-// side is a chase through memory.  The first hop of four neighbours is requested at once.
+// there, and an entry whose neighbour already hangs under that root (parent[d] == root: almost every
+// entry once the giant component has formed) is done after ONE load, the neighbour's parent word.  The
+// first hop of four neighbours is requested at once; chases read through L1 (see RootCached).
 // GRB_CC_HOOK=lb selects the advance route.
 #pragma once
 #include "cc_functor.cuh"
@@ -31,31 +32,38 @@ struct CcRowHookArgs {
     rows::View   bins;
 };
 
-// FindRoot for a vertex whose parent has already been loaded
-__device__ __forceinline__ int FindRootFrom(int *parent, int x, int p)
+// The chases of this pass read parents through L1 (ld.global.ca).  A line in L1 can be stale -- another SM has
+// moved a pointer meanwhile -- but every value a parent word ever held is an ancestor of its vertex (or the
+// vertex itself, from the time it was a root), so a stale chase still walks upwards and ends at a vertex that
+// was a root at some time; only the compare-and-swap (at L2) decides whether it still is.  What the cache buys:
+// the root of the giant component is read by almost every hook, and at L2 that one sector serialises the pass
+// (CcRowHookKernel with L2 loads took exactly as long as the LB advance: 12.8 of 14.4 ms at R-MAT scale 25).
+__device__ __forceinline__ int RootCached(int *parent, int x, int p)     // p = a value of parent[x]
 {
     while (p != x) {
-        const int gp = util::LoadCG(parent + p);
+        const int gp = util::LoadCA(parent + p);
         if (gp != p) util::StoreCG(parent + x, gp);     // path halving
         x = p; p = gp;
     }
     return x;
 }
 
-// link the components of u (an ancestor of the row's vertex) and of d, whose parent is pd;
-// returns the root both ended under
+// link the components of u (a vertex that is or once was the root above the row's vertex) and of d, whose
+// parent word read pd; returns the root both ended under.  No load at all when d already hangs under u.
 __device__ __forceinline__ int HookPair(int *parent, int u, int d, int pd)
 {
-    int v = FindRootFrom(parent, d, pd);
-    u = FindRoot(parent, u);
+    if (pd == u) return u;                          // parent[d] == u: same tree, whatever u is by now
+    int v = RootCached(parent, d, pd);
+    if (v == u) return u;
+    u = RootCached(parent, u, util::LoadCA(parent + u));
     for (;;) {
         if (u == v) return u;
         const int hi = u > v ? u : v, lo = u > v ? v : u;
         const int old = atomicCAS(parent + hi, hi, lo);
-        if (old == hi) return lo;               // linked larger root -> smaller root
-        u = FindRoot(parent, old);              // `hi` stopped being a root meanwhile: chase again
-        v = lo;
-        v = FindRoot(parent, v);
+        if (old == hi) return lo;                   // linked larger root -> smaller root
+        // `hi` stopped being a root meanwhile (old < hi): chase both sides again; max(u, v) strictly decreases
+        u = RootCached(parent, old, util::LoadCG(parent + old));
+        v = RootCached(parent, lo, util::LoadCG(parent + lo));
     }
 }
 
@@ -73,7 +81,7 @@ __device__ __forceinline__ void WarpHookRange(const CcRowHookArgs<SizeT> &a, int
         for (int j = 0; j < 4; ++j) {
             const bool take = d[j] != s && !(a.skip_upper && d[j] > s);
             if (!take) d[j] = -1;
-            pd[j] = take ? util::LoadCG(a.parent + d[j]) : 0;
+            pd[j] = take ? util::LoadCA(a.parent + d[j]) : 0;
         }
 #pragma unroll
         for (int j = 0; j < 4; ++j)
@@ -81,7 +89,7 @@ __device__ __forceinline__ void WarpHookRange(const CcRowHookArgs<SizeT> &a, int
     }
     for (; e < end; e += 32) {
         const int d = util::LoadStream(col + e);
-        if (d != s && !(a.skip_upper && d > s)) u = HookPair(a.parent, u, d, util::LoadCG(a.parent + d));
+        if (d != s && !(a.skip_upper && d > s)) u = HookPair(a.parent, u, d, util::LoadCA(a.parent + d));
     }
 }
 
@@ -130,7 +138,7 @@ CcRowHookKernel(const __grid_constant__ CcRowHookArgs<SizeT> a)
             for (int j = 0; j < rows::kSmallMax / 4; ++j) {
                 const bool take = d[j] >= 0 && d[j] != s && !(a.skip_upper && d[j] > s);
                 if (!take) d[j] = -1;
-                pd[j] = take ? util::LoadCG(a.parent + d[j]) : 0;
+                pd[j] = take ? util::LoadCA(a.parent + d[j]) : 0;
             }
             int u = s;
 #pragma unroll

@@ -102,6 +102,22 @@ extern "C" int grb_graph_build_transpose(grb_graph_t g)
     return 0;
 }
 
+extern "C" int grb_graph_build_twin(grb_graph_t g)
+{
+    if (!g) return (int)cudaErrorInvalidValue;
+    GRB_TRY(cudaSetDevice(g->device()));
+    GRB_TRY(g->EnsureTwin());
+    GRB_TRY(cudaStreamSynchronize(g->stream));
+    return 0;
+}
+
+extern "C" int grb_graph_twin_entries(grb_graph_t g, int64_t *entries)
+{
+    if (!g || !entries) return (int)cudaErrorInvalidValue;
+    *entries = g->twin32 ? (int64_t)g->twin32->edges : (g->twin64 ? (int64_t)g->twin64->edges : -1);
+    return 0;
+}
+
 // CSR == its transpose?  (graph/build.cuh: both are canonical sorted CSRs of the same multiset iff equal)
 template <typename G>
 static cudaError_t CheckSymmetric(G &g, cudaStream_t s, int *out)

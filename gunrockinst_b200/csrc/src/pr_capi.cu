@@ -57,22 +57,47 @@ static cudaError_t RunPr(gunrock::graph::DeviceCsr<int, SizeT> *g, cudaStream_t 
     return err;
 }
 
+// out[v] = in[to_new[v]]: ranks computed on the degree-ordered twin, back in the caller's vertex order
+static __global__ void RanksThroughKernel(const double *in, const int *to_new, long long nodes, double *out)
+{
+    const long long stride = (long long)gridDim.x * blockDim.x;
+    for (long long v = (long long)blockIdx.x * blockDim.x + threadIdx.x; v < nodes; v += stride) out[v] = in[to_new[v]];
+}
+
 // Symmetric graphs: the gather formulation of mgpr_enactor.cuh on one device (in-edges == the rows
 // already held, so a sweep sums contributions from a dense vector instead of issuing one fp64 atomic
 // per edge to a random line: 11.4 instead of 16.8 ms per sweep at scale 25).  Same pruning, damping,
 // moving test and sweep count; outputs as RunPr.
+// to_new != nullptr: g is the degree-ordered twin of the caller's graph (graph/build.cuh) and to_new[v] the
+// twin's id of the caller's vertex v -- the same graph with the hubs' contributions packed into the first
+// few MB of the vector every sweep gathers from; src goes in and the ranks come out in the caller's ids.
 template <typename SizeT>
 static cudaError_t RunPrGather(gunrock::graph::DeviceCsr<int, SizeT> *g, cudaStream_t stream, int src, double delta,
                                double threshold, int max_iter, double *ranks64_host, int *sorted_ids_host,
-                               float *sorted_ranks_host, size_t top, grb_stats *stats)
+                               float *sorted_ranks_host, size_t top, grb_stats *stats, const int *to_new = nullptr)
 {
     typedef gunrock::app::pr::MGPREnactor<SizeT> Enactor;
     Enactor enactor;
     typename Enactor::RunStats st;
+    const size_t n = (size_t)g->local_nodes;
+    if (to_new && src >= 0 && (size_t)src < n) {
+        GR_TRY(cudaMemcpyAsync(&src, to_new + src, sizeof(int), cudaMemcpyDeviceToHost, stream));
+        GR_TRY(cudaStreamSynchronize(stream));
+    }
     GR_TRY(enactor.Setup(g, stream));
     GR_TRY(enactor.Run(src, delta, threshold, max_iter, &st));
-    const size_t n = (size_t)g->local_nodes;
-    if (ranks64_host) GR_TRY(enactor.Extract(ranks64_host));
+    gunrock::util::DeviceArray<double> caller_order;
+    const double *d_rank = enactor.rank.ptr;
+    if (to_new) {
+        GR_TRY(caller_order.Allocate(n + 1));
+        RanksThroughKernel<<<gunrock::util::FillGrid(n), 256, 0, stream>>>(enactor.rank.ptr, to_new, (long long)n, caller_order.ptr);
+        GR_TRY(cudaGetLastError());
+        d_rank = caller_order.ptr;
+    }
+    if (ranks64_host) {
+        if (n) GR_TRY(cudaMemcpyAsync(ranks64_host, d_rank, sizeof(double) * n, cudaMemcpyDeviceToHost, stream));
+        GR_TRY(cudaStreamSynchronize(stream));
+    }
     if (sorted_ids_host || sorted_ranks_host) {
         // all (id, fp32 rank) pairs in descending rank, ties by ascending id (pr_enactor.cuh:497-500)
         gunrock::util::DeviceArray<unsigned long long> keys_a, keys_b;
@@ -80,7 +105,7 @@ static cudaError_t RunPrGather(gunrock::graph::DeviceCsr<int, SizeT> *g, cudaStr
         gunrock::util::DeviceArray<float> d_ranks;
         gunrock::util::RadixSortScratch scratch;
         GR_TRY(keys_a.Allocate(n)); GR_TRY(keys_b.Allocate(n)); GR_TRY(d_ids.Allocate(n)); GR_TRY(d_ranks.Allocate(n));
-        gunrock::app::pr::MakeSortKeysKernel<<<gunrock::util::FillGrid(n), 256, 0, stream>>>(enactor.rank.ptr, n, keys_a.ptr);
+        gunrock::app::pr::MakeSortKeysKernel<<<gunrock::util::FillGrid(n), 256, 0, stream>>>(d_rank, n, keys_a.ptr);
         GR_TRY(cudaGetLastError());
         unsigned long long *sorted = nullptr;
         GR_TRY(gunrock::util::RadixSort64(keys_a.ptr, keys_b.ptr, n, 64, scratch, &sorted, stream));
@@ -109,6 +134,7 @@ static cudaError_t RunPrGather(gunrock::graph::DeviceCsr<int, SizeT> *g, cudaStr
         stats->gpu_launches = st.launches;
         stats->reserved = (int32_t)(st.sweep_ms * 1000.0);         // microseconds of the power iteration alone
     }
+    GR_TRY(cudaStreamSynchronize(stream));      // caller_order is released below
     return cudaSuccess;
 }
 
@@ -130,6 +156,19 @@ static int PrDispatch(grb_graph_t g, int32_t src, double delta, double threshold
 {
     if (!g) return (int)cudaErrorInvalidValue;
     GRB_TRY(cudaSetDevice(g->device()));
+    // a symmetric graph that already has its degree-ordered twin attached (grb_graph_build_twin, or a search with
+    // grb_bfs_config.degree_order) is swept on the twin -- the same multiset of entries under other vertex names
+    // (BuildDegreeOrdered keeps duplicates and self loops; the entry counts are compared all the same);
+    // GRB_PR_TWIN=0 keeps the caller's order
+    const char *tw = getenv("GRB_PR_TWIN");
+    if (g->has_twin() && !(tw && tw[0] == '0')) {
+        if (g->twin32 && g->g32->symmetric && g->twin32->edges == g->g32->edges && g->g32->edges > 0)
+            return (int)RunPrGather<int>(g->twin32, g->stream, src, delta, threshold, max_iter, ranks64_host,
+                                         sorted_ids_host, sorted_ranks_host, top, stats, g->to_new.ptr);
+        if (g->twin64 && g->g64->symmetric && g->twin64->edges == g->g64->edges && g->g64->edges > 0)
+            return (int)RunPrGather<long long>(g->twin64, g->stream, src, delta, threshold, max_iter, ranks64_host,
+                                               sorted_ids_host, sorted_ranks_host, top, stats, g->to_new.ptr);
+    }
     return (int)(g->g32 ? RunPrAny<int>(g->g32, g->stream, src, delta, threshold, max_iter, ranks64_host,
                                         sorted_ids_host, sorted_ranks_host, top, stats)
                         : RunPrAny<long long>(g->g64, g->stream, src, delta, threshold, max_iter, ranks64_host,

@@ -97,6 +97,15 @@ int grb_graph_rmat(int device, int scale, int64_t edges, uint64_t seed, int undi
  * app/dobfs/dobfs_problem.cuh:211-260, tests/dobfs/test_dobfs.cu:477-560).  No-op on a symmetric
  * graph; grb_bfs_create does this on demand.  Single-device resident graphs. */
 int  grb_graph_build_transpose(grb_graph_t g);
+/* build the degree-ordered twin of a resident single-device graph: the same graph with the vertices renumbered by
+ * descending degree and every row sorted by the new ids (graph/build.cuh), kept beside the caller's arrays (one more
+ * CSR in HBM).  Preprocessing in the sense of the reference's Problem::Init (gunrock/app/problem_base.cuh:279-303:
+ * whatever layout the enactor wants is made before the timed Enact).  Searches ask for it with
+ * grb_bfs_config.degree_order (built on demand); grb_pagerank sweeps a symmetric graph on its twin when one is
+ * attached (ranks come back in the caller's ids; GRB_PR_TWIN=0 opts out). */
+int  grb_graph_build_twin(grb_graph_t g);
+/* entries of the attached twin (always those of the graph: duplicates and self loops are kept), -1 without a twin */
+int  grb_graph_twin_entries(grb_graph_t g, int64_t *entries);
 /* symmetric_out = 1 iff the CSR equals its transpose as a multiset of (row, col) entries -- what the
  * `symmetric` promise of grb_graph_from_host means.  Costs a sort of the edge list. */
 int  grb_graph_check_symmetric(grb_graph_t g, int *symmetric_out);

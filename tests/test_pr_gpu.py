@@ -19,10 +19,13 @@ def assert_per_vertex(got, want, tol=TOL):
     assert bad.size == 0, (int(bad.size), int(bad[0]), float(err[bad[0]]), float(want[bad[0]]))
 
 
-def _check(gr, orc, ro, co, symmetric, **kw):
+def _check(gr, orc, ro, co, symmetric, twin=False, **kw):
     src = kw.get("src", -1)
     want, it = orc.pagerank(ro, co, kw.get("delta", 0.85), kw.get("threshold", 1e-6), kw.get("max_iter", 1000), src)
     g = gr.Graph.from_csr(ro, co, symmetric=symmetric)
+    if twin:
+        g.build_twin()
+        assert g.twin_entries() == g.edges          # same entries: grb_pagerank sweeps the twin
     ranks, srt, st = gr.pagerank(g, src=src, delta=kw.get("delta", 0.85), threshold=kw.get("threshold", 1e-6),
                                  max_iter=kw.get("max_iter", 1000), want_sorted=True)
     assert st["iterations"] == it
@@ -67,6 +70,30 @@ def test_rmat(gr, orc, scale, ef, undirected):
     assert st["iterations"] > 3
     if not undirected:
         assert st["pull_levels"] > 2                                   # pruning cascaded over several sweeps
+
+
+@pytest.mark.parametrize("name", ["bips98_606", "chesapeake", "test_cc", "test_pr"])
+def test_fixtures_on_degree_ordered_twin(gr, orc, name):
+    """grb_graph_build_twin + grb_pagerank: the sweeps run on the relabelled graph, the source goes in and the ranks
+    and the sorted pairs come out in the caller's ids"""
+    n, ro, co, _ = load_golden(name)
+    _check(gr, orc, ro, co, True, twin=True)
+    _check(gr, orc, ro, co, True, twin=True, src=min(3, n - 1), threshold=0.01, max_iter=20)
+
+
+@pytest.mark.parametrize("scale,ef", [(10, 16), (16, 16), (18, 8)])
+def test_rmat_on_degree_ordered_twin(gr, orc, scale, ef):
+    ro, co = rmat_graph(orc, scale, ef, True)
+    _check(gr, orc, ro, co, True, twin=True)
+    _check(gr, orc, ro, co, True, twin=True, src=7, max_iter=30)
+
+
+def test_twin_keeps_duplicate_entries(gr, orc):
+    """a row that lists a neighbour twice counts it twice; the twin is the same multiset of entries (nothing is
+    merged), so the sweeps on it give the oracle's ranks"""
+    ro = np.array([0, 4, 6, 8], np.int64)
+    co = np.array([1, 1, 2, 2, 0, 0, 0, 0], np.int32)       # edges 0-1 and 0-2, each listed twice on both sides
+    _check(gr, orc, ro, co, True, twin=True)
 
 
 def test_edge_cases(gr, orc):

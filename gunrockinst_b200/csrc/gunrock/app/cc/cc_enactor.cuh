@@ -99,14 +99,20 @@ class CCEnactor : public EnactorBase {
         }
 
         // ---- 2. pointer jumping: flatten + count roots ---------------------------------------------
-        oprtr::filter::Args<VertexId, Value> fa;
-        fa.in_queue = nullptr; fa.in_pred_queue = nullptr; fa.out_queue = nullptr;
-        fa.in_len = n; fa.d_in_len = nullptr; fa.out_cap = 0;
-        fa.slots = work_progress.d_slots.ptr;
-        fa.queue_index = frontier_attribute.queue_index;
-        fa.iteration = 1;
-        fa.compact = false;
-        GR_TRY((oprtr::filter::LaunchKernel<FilterPolicy, Problem, JumpFn>(dev.sm_count, ds, fa, stream)));
+        if (by_rows) {
+            CcFlattenKernel<<<util::FillGrid(n, 256, (unsigned)dev.sm_count * 8u), 256, 0, stream>>>(
+                ds.d_component_ids, (long long)n, ds.d_num_components);
+            GR_TRY(cudaGetLastError());
+        } else {
+            oprtr::filter::Args<VertexId, Value> fa;
+            fa.in_queue = nullptr; fa.in_pred_queue = nullptr; fa.out_queue = nullptr;
+            fa.in_len = n; fa.d_in_len = nullptr; fa.out_cap = 0;
+            fa.slots = work_progress.d_slots.ptr;
+            fa.queue_index = frontier_attribute.queue_index;
+            fa.iteration = 1;
+            fa.compact = false;
+            GR_TRY((oprtr::filter::LaunchKernel<FilterPolicy, Problem, JumpFn>(dev.sm_count, ds, fa, stream)));
+        }
         ++enactor_stats.launches;
         frontier_attribute.queue_index++;
 

@@ -269,8 +269,10 @@ class MGPREnactor : public EnactorBase {
     util::DeviceArray<VertexId> queue;
     oprtr::advance::LbScratch<SizeT> lb_scratch;
     // single device: the rows of the power iteration binned by length (pr_row_sweep.cuh)
-    bool row_sweep = false;
+    bool row_sweep = false, row_tickets = false;
     oprtr::rows::Bins<SizeT> row_bins;
+    util::DeviceArray<unsigned long long> sweep_ticket;
+    int ticket_ctas_per_sm = 0;
     bfs::PeerComm comm;
     PrPeerTable peers;
     unsigned long long half = 0, half_words = 0;
@@ -302,7 +304,14 @@ class MGPREnactor : public EnactorBase {
         GR_TRY(lb_scratch.Allocate(ln + 1, (size_t)g->edges + 1, AdvancePolicy::SCAN_TILE, AdvancePolicy::TILE_EDGES, s));
         const char *route = getenv("GRB_PR_SWEEP");
         row_sweep = P == 1 && !(route && strcmp(route, "lb") == 0);
-        if (row_sweep) GR_TRY(row_bins.Allocate(ln, (size_t)g->edges));
+        row_tickets = row_sweep && !(route && strcmp(route, "rows1") == 0);     // rows1: the static grid of PrRowSweepKernel
+        if (row_sweep) {
+            GR_TRY(row_bins.Allocate(ln, (size_t)g->edges));
+            GR_TRY(sweep_ticket.Allocate(1));
+            GR_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&ticket_ctas_per_sm, PrRowSweepTicketKernel<SizeT>,
+                                                                 oprtr::rows::kThreads, 0));
+            if (ticket_ctas_per_sm < 1) ticket_ctas_per_sm = 1;
+        }
         GR_TRY(comm.Setup((int)P, g->part.rank, s));
         peers = PrPeerTable();
         peers.parts = (int)P; peers.rank = g->part.rank;
@@ -423,7 +432,17 @@ class MGPREnactor : public EnactorBase {
                     rows.contrib_in  = contrib.ptr + (unsigned long long)cgen * half;
                     rows.contrib_out = contrib.ptr + (unsigned long long)(cgen ^ 1) * half +
                                        (unsigned long long)me * (unsigned long long)ln;
-                    PrRowSweepKernel<SizeT><<<rows.bins.Blocks(), oprtr::rows::kThreads, 0, stream>>>(rows);
+                    if (row_tickets) {
+                        const unsigned long long units = rows.bins.n_pieces + (rows.bins.n_medium + kMediumUnit - 1) / kMediumUnit +
+                                                         (rows.bins.n_small + kSmallUnit - 1) / kSmallUnit;
+                        const unsigned long long want = (units + oprtr::rows::kWarps - 1) / oprtr::rows::kWarps;
+                        const unsigned long long resident = (unsigned long long)dev.sm_count * (unsigned long long)ticket_ctas_per_sm;
+                        GR_TRY(cudaMemsetAsync(sweep_ticket.ptr, 0, sizeof(unsigned long long), stream));
+                        PrRowSweepTicketKernel<SizeT><<<(unsigned)(want < resident ? (want ? want : 1) : resident),
+                                                        oprtr::rows::kThreads, 0, stream>>>(rows, sweep_ticket.ptr);
+                    } else {
+                        PrRowSweepKernel<SizeT><<<rows.bins.Blocks(), oprtr::rows::kThreads, 0, stream>>>(rows);
+                    }
                     GR_TRY(cudaGetLastError());
                     if (rows.bins.n_big) {
                         PrBigRowFinishKernel<SizeT><<<util::FillGrid(rows.bins.n_big), 256, 0, stream>>>(rows);

@@ -17,6 +17,6 @@ except Exception as e:
     print("no configs", e)
 P
 timeout 240 ncu --set full --clock-control none --import-source on --kernel-name-base demangled \
-    -k regex:'PrRowSweepKernel|CcRowHookKernel' -c 2 -f -o $out/prof_rows_$tag \
+    -k regex:'PrRowSweepTicketKernel|CcRowHookKernel|CcFlattenKernel' -c 5 -f -o $out/prof_rows_$tag \
     python tools/rows_ab.py 25 2 1 > $out/ncu_rows_$tag.log 2>&1
 echo "rows capture rc=$?"; tail -2 $out/ncu_rows_$tag.log

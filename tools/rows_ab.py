@@ -1,5 +1,5 @@
 """A/B of the row-binned passes (oprtr/row_bins.cuh) against the LB-advance routes they replace,
-same process, same graph:  PageRank sweeps (GRB_PR_SWEEP=lb | rows) and the hook pass of connected
+same process, same graph:  PageRank sweeps (GRB_PR_SWEEP=lb | rows1 = static grid | default = tickets) and the hook pass of connected
 components (GRB_CC_HOOK=lb | rows).
 
 usage: python tools/rows_ab.py [scale=25] [pr_sweeps=24] [runs=2]
@@ -63,7 +63,7 @@ def main():
     rec = {"primitive": "pagerank", "scale": scale, "nodes": int(n), "entries": int(m), "max_iter": sweeps}
     ranks = {}
     import time
-    for name, val in (("lb", "lb"), ("rows", None), ("rows_twin", None)):
+    for name, val in (("lb", "lb"), ("rows1", "rows1"), ("rows", None), ("rows_twin", None)):
         route("GRB_PR_SWEEP", val)
         if name == "rows_twin":             # the same kernel on the degree-ordered twin of the graph
             t0 = time.time()
@@ -80,7 +80,7 @@ def main():
                      "entries_per_sweep": int(st["edges_inspected"] // max(1, st["iterations"])),
                      "gpu_launches": st["gpu_launches"], "rank_sum": float(r.sum())}
     route("GRB_PR_SWEEP", None)
-    for name in ("rows", "rows_twin"):
+    for name in ("rows1", "rows", "rows_twin"):
         d = np.abs(ranks["lb"] - ranks[name])
         rec[name]["max_abs_diff_vs_lb"] = float(d.max())
         rec[name]["within_1e-6_per_vertex"] = bool(np.all(d <= 1e-6 * np.maximum(1.0, np.abs(ranks["lb"]))))

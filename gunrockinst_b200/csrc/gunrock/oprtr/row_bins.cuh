@@ -41,16 +41,18 @@ struct View {
 };
 
 // rows queue[0 .. qlen) (global ids; nullptr: local rows 0 .. qlen) -> the three lists (order follows
-// the queue within a warp) and the piece list; counts[ENTRIES] = entries of all listed rows
+// the queue within a CTA's round of 256 rows) and the piece list; counts[ENTRIES] = entries of all listed rows
 template <typename SizeT>
 __global__ void __launch_bounds__(256)
 BinKernel(const SizeT *row_offsets, const int *queue, unsigned long long qlen, graph::Partition part,
           int *small_rows, int *medium_rows, int *big_rows, int2 *big_pieces, unsigned long long *counts)
 {
     __shared__ unsigned long long s_red[256 / 32 + 1];
-    const unsigned long long rounded = (qlen + 31) & ~31ull;
+    __shared__ unsigned s_cnt[256 / 32][3];             // per warp and bin: rows of this round, then their offset in the CTA's run
+    __shared__ unsigned long long s_base[3];            // where the CTA's run of this round starts in each list
+    const unsigned long long rounded = (qlen + 255) & ~255ull;      // whole CTAs go round together
     const unsigned long long stride = (unsigned long long)gridDim.x * blockDim.x;
-    const unsigned lane = (unsigned)util::LaneId();
+    const unsigned lane = (unsigned)util::LaneId(), warp = (unsigned)util::WarpId();
     const unsigned below = (1u << lane) - 1u;
     unsigned long long entries = 0;
     for (unsigned long long i = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x; i < rounded; i += stride) {
@@ -62,19 +64,26 @@ BinKernel(const SizeT *row_offsets, const int *queue, unsigned long long qlen, g
         }
         entries += (unsigned long long)len;
         const int bin = len <= 0 ? -1 : (len <= kSmallMax ? SMALL : (len <= kChunk ? MEDIUM : BIG));
+        // one atomic per CTA, round and list (one per warp serialised the pass on three words: 1.1 ms at scale 25)
+        unsigned m[3];
 #pragma unroll
-        for (int b = 0; b < 3; ++b) {
-            const unsigned m = __ballot_sync(util::kFullMask, bin == b);
-            if (m == 0) continue;                               // warp-uniform
-            const int leader = __ffs(m) - 1;
-            unsigned long long base = 0;
-            if ((int)lane == leader) base = atomicAdd(&counts[b], (unsigned long long)__popc(m));
-            base = __shfl_sync(util::kFullMask, base, leader);
-            if (bin == b) {
-                int *list = b == SMALL ? small_rows : (b == MEDIUM ? medium_rows : big_rows);
-                list[base + (unsigned)__popc(m & below)] = r;
-            }
+        for (int b = 0; b < 3; ++b) m[b] = __ballot_sync(util::kFullMask, bin == b);
+        if (lane == 0) {
+#pragma unroll
+            for (int b = 0; b < 3; ++b) s_cnt[warp][b] = (unsigned)__popc(m[b]);
         }
+        __syncthreads();
+        if (threadIdx.x < 3) {
+            unsigned total = 0;
+            for (int w = 0; w < 256 / 32; ++w) { const unsigned c = s_cnt[w][threadIdx.x]; s_cnt[w][threadIdx.x] = total; total += c; }
+            s_base[threadIdx.x] = total ? atomicAdd(&counts[threadIdx.x], (unsigned long long)total) : 0ull;
+        }
+        __syncthreads();
+        if (bin >= 0) {
+            int *list = bin == SMALL ? small_rows : (bin == MEDIUM ? medium_rows : big_rows);
+            list[s_base[bin] + s_cnt[warp][bin] + (unsigned)__popc(m[bin] & below)] = r;
+        }
+        __syncthreads();                                // s_cnt / s_base are rewritten by the next round
         if (bin == BIG) {
             const unsigned long long pieces = (unsigned long long)((len + kChunk - 1) / kChunk);
             const unsigned long long at = atomicAdd(&counts[PIECES], pieces);

@@ -8,16 +8,18 @@
 // The generic route (LB advance with MgPrGatherFunctor + MgPrFinishKernel) pays a degree scan, the
 // owner search of the LB tiles, one fp64 atomic per row piece and a second pass over the rows:
 // ~100 thread instructions per entry, 11 ms per sweep at R-MAT scale 25.  The set of rows a sweep
-// walks never changes after the pruning phase, so here the rows are binned ONCE by their CSR length,
-//     small   1 .. 16 entries        4 lanes per row (8 rows per warp),
-//     medium  17 .. 2048             one warp per row, four column loads and four gathers in flight per lane,
-//     big     > 2048                 cut into 2048-entry pieces, one warp per piece, one atomic per piece,
-// and a sweep is a single launch whose CTAs take the big pieces first, then the medium and the small
-// rows.  The lane that ends up with a row's sum finishes the row on the spot (damping, moving test,
-// new rank, new contribution into the other generation of the contribution vector), so there is no
-// accumulator array, no atomic and no second pass for small and medium rows; only the big rows
-// (a few thousand at scale 25) are finished by a follow-up kernel.  Sums of small and medium rows are
-// taken in a fixed order (deterministic); big rows add their pieces atomically, as the generic route does.
+// walks never changes after the pruning phase, so the rows are binned ONCE by their CSR length
+// (oprtr/row_bins.cuh: 1..16 entries, 17..2048, longer ones cut into 2048-entry pieces) and a sweep
+// is a single launch over the bins.  The lane that ends up with a row's sum finishes the row on the
+// spot (damping, moving test, new rank, new contribution into the other generation of the
+// contribution vector), so there is no accumulator array, no atomic and no second pass for small
+// and medium rows; only the big rows (a few thousand at scale 25) are finished by a follow-up
+// kernel.  Sums of small and medium rows are taken in a fixed order (deterministic); big rows add
+// their pieces atomically, as the generic route does.
+//
+// Two kernels: PrRowSweepKernel (static grid: CTAs by bin, the first version, GRB_PR_SWEEP=rows1;
+// 7.4 ms per sweep) and PrRowSweepTicketKernel (resident grid, work drawn from a ticket counter,
+// metadata and column ids requested ahead; the default, 4.9 ms, 4.0 ms on the degree-ordered twin).
 //
 // Single device only (the partitioned enactor keeps the generic route: its finishing kernel is also
 // the coalesced publication into the peers' replicas).  GRB_PR_SWEEP=lb selects the generic route.

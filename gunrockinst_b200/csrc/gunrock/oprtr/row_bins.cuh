@@ -8,9 +8,11 @@
 //     small   1 .. 16 entries       four lanes per row (eight rows per warp),
 //     medium  17 .. 2048            one warp per row,
 //     big     > 2048                cut into 2048-entry pieces, one warp per piece,
-// and one launch covers them all: CTAs [0, blocks_big) take the pieces (the longest work first),
-// the next blocks_medium CTAs the medium rows, the rest the small rows.  Rows without entries are
-// in no list.  Users: app/pr/pr_row_sweep.cuh, app/cc/cc_row_hook.cuh.
+// and one launch covers them all: with a static grid CTAs [0, blocks_big) take the pieces (the
+// longest work first), the next blocks_medium CTAs the medium rows, the rest the small rows; with a
+// resident grid the warps draw pieces, then groups of medium rows, then groups of small rows from a
+// ticket counter (pr_row_sweep.cuh).  Rows without entries are in no list.
+// Users: app/pr/pr_row_sweep.cuh, app/cc/cc_row_hook.cuh; stand-alone: grb_test_row_bins.
 #pragma once
 #include "../graph/csr.cuh"
 #include "../util/array.cuh"

@@ -13,7 +13,8 @@
 // Labels: smallest vertex id of the component, as in the reference.
 // Default route of pass 1 (cc_row_hook.cuh): the rows binned by length inside Enact (one small
 // kernel + one 64-byte read-back, part of the measured time) and ONE kernel in which the lanes
-// that walk a row keep its root; GRB_CC_HOOK=lb selects the advance.
+// that walk a row keep its root (resident grid with tickets; GRB_CC_HOOK=rows1: static grid);
+// GRB_CC_HOOK=lb selects the advance.
 //
 // Algorithmic HBM bytes: hook pass 2*sizeof(SizeT) per vertex + 4 (column id) + 8 (two
 // parent probes) per CSR entry; jump pass 12 per vertex.
@@ -42,7 +43,9 @@ class CCEnactor : public EnactorBase {
 
     oprtr::advance::LbScratch<SizeT> lb_scratch;
     oprtr::rows::Bins<SizeT> row_bins;
-    bool by_rows = false;
+    bool by_rows = false, row_tickets = false;
+    util::DeviceArray<unsigned long long> hook_ticket;
+    int ticket_ctas_per_sm = 1;
     bool set_up = false;
 
     cudaError_t Setup(Problem *problem, cudaStream_t s)
@@ -50,7 +53,14 @@ class CCEnactor : public EnactorBase {
         GR_TRY(SetupBase(problem->graph->device, s));
         const char *route = getenv("GRB_CC_HOOK");
         by_rows = problem->graph->part.log_parts == 0 && !(route && strcmp(route, "lb") == 0);
-        if (by_rows) GR_TRY(row_bins.Allocate((size_t)problem->graph->local_nodes, (size_t)problem->graph->edges));
+        row_tickets = by_rows && !(route && strcmp(route, "rows1") == 0);      // rows1: the static grid of CcRowHookKernel
+        if (by_rows) {
+            GR_TRY(row_bins.Allocate((size_t)problem->graph->local_nodes, (size_t)problem->graph->edges));
+            GR_TRY(hook_ticket.Allocate(1));
+            GR_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&ticket_ctas_per_sm, CcRowHookTicketKernel<SizeT>,
+                                                                 oprtr::rows::kThreads, 0));
+            if (ticket_ctas_per_sm < 1) ticket_ctas_per_sm = 1;
+        }
         GR_TRY(lb_scratch.Allocate((size_t)problem->graph->local_nodes + 1, (size_t)problem->graph->edges + 1,
                                    AdvancePolicy::SCAN_TILE, AdvancePolicy::TILE_EDGES, s));
         set_up = true;
@@ -77,7 +87,16 @@ class CCEnactor : public EnactorBase {
             h.parent = ds.d_component_ids; h.skip_upper = ds.skip_upper;
             h.bins = row_bins.view;
             row_entries = h.bins.entries;
-            if (h.bins.Blocks()) {
+            if (h.bins.Blocks() && row_tickets) {
+                const unsigned long long units = h.bins.n_pieces + (h.bins.n_medium + kHookMediumUnit - 1) / kHookMediumUnit +
+                                                 (h.bins.n_small + kHookSmallUnit - 1) / kHookSmallUnit;
+                const unsigned long long want = (units + oprtr::rows::kWarps - 1) / oprtr::rows::kWarps;
+                const unsigned long long resident = (unsigned long long)dev.sm_count * (unsigned long long)ticket_ctas_per_sm;
+                GR_TRY(cudaMemsetAsync(hook_ticket.ptr, 0, sizeof(unsigned long long), stream));
+                CcRowHookTicketKernel<SizeT><<<(unsigned)(want < resident ? want : resident), oprtr::rows::kThreads, 0, stream>>>(
+                    h, hook_ticket.ptr);
+                GR_TRY(cudaGetLastError());
+            } else if (h.bins.Blocks()) {
                 CcRowHookKernel<SizeT><<<h.bins.Blocks(), oprtr::rows::kThreads, 0, stream>>>(h);
                 GR_TRY(cudaGetLastError());
             }

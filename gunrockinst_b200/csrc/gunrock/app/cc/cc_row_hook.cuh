@@ -148,6 +148,78 @@ CcRowHookKernel(const __grid_constant__ CcRowHookArgs<SizeT> a)
     }
 }
 
+// The same pass on a resident grid: warps draw a piece, 8 medium rows or 32 small rows per ticket (the next ticket is
+// requested before the current unit is walked), a unit's row ids and offsets are loaded by one lane each.  The static
+// grid above keeps a CTA's slots until its longest row is through (pr_row_sweep.cuh has the measurement).
+constexpr int kHookMediumUnit = 8, kHookSmallUnit = 32;
+
+template <typename SizeT>
+__global__ void __launch_bounds__(rows::kThreads)
+CcRowHookTicketKernel(const __grid_constant__ CcRowHookArgs<SizeT> a, unsigned long long *ticket)
+{
+    const rows::View &b = a.bins;
+    const int lane = util::LaneId();
+    const unsigned long long units_medium = (b.n_medium + kHookMediumUnit - 1) / kHookMediumUnit;
+    const unsigned long long units_small = (b.n_small + kHookSmallUnit - 1) / kHookSmallUnit;
+    const unsigned long long total = b.n_pieces + units_medium + units_small;
+    unsigned long long t = 0;
+    if (lane == 0) t = atomicAdd(ticket, 1ull);
+    t = __shfl_sync(util::kFullMask, t, 0);
+    while (t < total) {                                         // warp-uniform
+        unsigned long long next = 0;
+        if (lane == 0) next = atomicAdd(ticket, 1ull);
+        if (t < b.n_pieces) {
+            SizeT beg, end;
+            const int s = rows::PieceRange<SizeT>(b, a.row_offsets, t, beg, end);
+            int u = s;
+            WarpHookRange<SizeT>(a, s, beg, end, u);
+        } else if (t < b.n_pieces + units_medium) {
+            const unsigned long long first = (t - b.n_pieces) * (unsigned long long)kHookMediumUnit;
+            const int count = (int)(b.n_medium - first < (unsigned long long)kHookMediumUnit ? b.n_medium - first : kHookMediumUnit);
+            int r = 0;
+            SizeT beg = 0, end = 0;
+            if (lane < count) { r = b.medium_rows[first + lane]; beg = a.row_offsets[r]; end = a.row_offsets[r + 1]; }
+            for (int k = 0; k < count; ++k) {                   // warp-uniform
+                const int s = __shfl_sync(util::kFullMask, r, k);
+                const SizeT kb = __shfl_sync(util::kFullMask, beg, k), ke = __shfl_sync(util::kFullMask, end, k);
+                int u = s;
+                WarpHookRange<SizeT>(a, s, kb, ke, u);
+            }
+        } else {
+            const unsigned long long first = (t - b.n_pieces - units_medium) * (unsigned long long)kHookSmallUnit;
+            int r = 0;
+            SizeT beg = 0, end = 0;
+            if (first + (unsigned long long)lane < b.n_small) {
+                r = b.small_rows[first + lane]; beg = a.row_offsets[r]; end = a.row_offsets[r + 1];
+            }
+            const int group = lane >> 2, g = lane & 3;
+#pragma unroll 1
+            for (int k = 0; k < 4; ++k) {
+                const int s = __shfl_sync(util::kFullMask, r, 8 * k + group);
+                const SizeT jb = __shfl_sync(util::kFullMask, beg, 8 * k + group);
+                const SizeT je = __shfl_sync(util::kFullMask, end, 8 * k + group);
+                int d[rows::kSmallMax / 4], pd[rows::kSmallMax / 4];
+#pragma unroll
+                for (int j = 0; j < rows::kSmallMax / 4; ++j) {
+                    const SizeT e = jb + (SizeT)(g + 4 * j);
+                    d[j] = e < je ? util::LoadStream(a.col_indices + e) : -1;
+                }
+#pragma unroll
+                for (int j = 0; j < rows::kSmallMax / 4; ++j) {
+                    const bool take = d[j] >= 0 && d[j] != s && !(a.skip_upper && d[j] > s);
+                    if (!take) d[j] = -1;
+                    pd[j] = take ? util::LoadCA(a.parent + d[j]) : 0;
+                }
+                int u = s;
+#pragma unroll
+                for (int j = 0; j < rows::kSmallMax / 4; ++j)
+                    if (d[j] >= 0) u = HookPair(a.parent, u, d[j], pd[j]);
+            }
+        }
+        t = __shfl_sync(util::kFullMask, next, 0);
+    }
+}
+
 // The flattening pass of the row route: every vertex to its root, roots counted.  What PtrJumpFunctor does through
 // the apply-only filter (the reference's PtrJump, gunrock/app/cc/cc_functor.cuh:116-170), with the hops read through
 // L1 (roots do not move any more; a stale word still points upwards) and ONE atomic per CTA for the count instead

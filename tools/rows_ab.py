@@ -1,8 +1,8 @@
 """A/B of the row-binned passes (oprtr/row_bins.cuh) against the LB-advance routes they replace,
 same process, same graph:  PageRank sweeps (GRB_PR_SWEEP=lb | rows1 = static grid | default = tickets) and the hook pass of connected
-components (GRB_CC_HOOK=lb | rows).
+components (GRB_CC_HOOK=lb | rows1 = static grid | default = tickets).
 
-usage: python tools/rows_ab.py [scale=25] [pr_sweeps=24] [runs=2]
+usage: python tools/rows_ab.py [scale=25] [pr_sweeps=24] [runs=2] [cc]
 
 One JSON line per primitive: time per route, results compared between the routes (CC: labels equal;
 PageRank: same sweep count, max |diff| of the ranks), plus -- up to scale 20 -- the CPU oracle on the
@@ -30,6 +30,7 @@ def main():
     scale = int(sys.argv[1]) if len(sys.argv) > 1 else 25
     sweeps = int(sys.argv[2]) if len(sys.argv) > 2 else 24
     runs = int(sys.argv[3]) if len(sys.argv) > 3 else 2
+    only = sys.argv[4] if len(sys.argv) > 4 else ""         # "cc": skip PageRank
     g = gr.Graph.rmat(scale)
     n, m = g.local_nodes, g.info.edges
     want_cc = want_pr = None
@@ -42,7 +43,7 @@ def main():
     # ---- connected components
     rec = {"primitive": "cc", "scale": scale, "nodes": int(n), "entries": int(m)}
     labels = {}
-    for name, val in (("lb", "lb"), ("rows", None)):
+    for name, val in (("lb", "lb"), ("rows1", "rows1"), ("rows", None)):
         route("GRB_CC_HOOK", val)
         best = None
         for _ in range(runs):
@@ -53,11 +54,14 @@ def main():
         rec[name] = {"ms": round(best, 4), "components": ncomp, "gpu_launches": st["gpu_launches"],
                      "entries_per_s": round(m / best / 1e6, 2)}
     route("GRB_CC_HOOK", None)
-    rec["labels_equal"] = bool(np.array_equal(labels["lb"], labels["rows"]))
+    rec["labels_equal"] = bool(np.array_equal(labels["lb"], labels["rows"]) and np.array_equal(labels["lb"], labels["rows1"]))
     if want_cc is not None:
         rec["rows_equal_oracle"] = bool(np.array_equal(labels["rows"], want_cc))
     rec["speedup"] = round(rec["lb"]["ms"] / rec["rows"]["ms"], 3)
     print(json.dumps(rec), flush=True)
+    if only == "cc":
+        g.close()
+        return
 
     # ---- PageRank
     rec = {"primitive": "pagerank", "scale": scale, "nodes": int(n), "entries": int(m), "max_iter": sweeps}

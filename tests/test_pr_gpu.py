@@ -22,7 +22,7 @@ def assert_per_vertex(got, want, tol=TOL):
 def _check(gr, orc, ro, co, symmetric, twin=False, **kw):
     src = kw.get("src", -1)
     want, it = orc.pagerank(ro, co, kw.get("delta", 0.85), kw.get("threshold", 1e-6), kw.get("max_iter", 1000), src)
-    g = gr.Graph.from_csr(ro, co, symmetric=symmetric)
+    g = gr.Graph.from_csr(ro, co, symmetric=symmetric, force_offset_bytes=kw.get("offset_bytes", 0))
     if twin:
         g.build_twin()
         assert g.twin_entries() == g.edges          # same entries: grb_pagerank sweeps the twin
@@ -86,6 +86,13 @@ def test_rmat_on_degree_ordered_twin(gr, orc, scale, ef):
     ro, co = rmat_graph(orc, scale, ef, True)
     _check(gr, orc, ro, co, True, twin=True)
     _check(gr, orc, ro, co, True, twin=True, src=7, max_iter=30)
+
+
+@pytest.mark.parametrize("twin", [False, True])
+def test_rmat_with_64_bit_offsets(gr, orc, twin):
+    """the row-binned sweep instantiated for 64-bit row offsets (graphs past 2^31 entries use it)"""
+    ro, co = rmat_graph(orc, 14, 16, True)
+    _check(gr, orc, ro, co, True, twin=twin, offset_bytes=8, max_iter=40)
 
 
 def test_twin_keeps_duplicate_entries(gr, orc):

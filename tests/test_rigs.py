@@ -24,6 +24,20 @@ def test_rig_builds_and_prints_usage():
     assert p.returncode == 1
 
 
+def test_rig_answers_to_the_reference_binary_names():
+    """tests/_bin/test_{bfs,dobfs,sssp,cc,pr}: the reference's per-primitive programs (`test_bfs market <file> ...`,
+    tests/bfs/test_bfs.cu:58-89); the primitive comes from the name, the graph type is the first argument"""
+    _build()
+    for prim in ("bfs", "dobfs", "sssp", "cc", "pr"):
+        exe = os.path.join(ROOT, "tests", "_bin", "test_" + prim)
+        p = subprocess.run([exe], capture_output=True, text=True)
+        assert p.returncode == 1 and "market <file>" in p.stdout
+        p = subprocess.run([exe, "market", "/nonexistent/graph.mtx"], capture_output=True, text=True)
+        assert p.returncode == 1 and "cannot read /nonexistent/graph.mtx" in (p.stdout + p.stderr)
+        p = subprocess.run([exe, "nonsense", "x"], capture_output=True, text=True)
+        assert p.returncode == 1 and "market <file>" in p.stdout
+
+
 def _write_mtx(path, n, edges, values=None):
     with open(path, "w") as f:
         f.write("%%MatrixMarket matrix coordinate %s general\n" % ("integer" if values is not None else "pattern"))
@@ -50,6 +64,16 @@ def test_rig_market(tmp_path, args):
     assert "TEST PASSED" in p.stdout and "INCORRECT" not in p.stdout
     if args[0] in ("bfs", "dobfs", "sssp") and not ("--idempotence=1" in args and "--mark-pred" in args):
         assert "Label Validity: CORRECT" in p.stdout
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("prim", ["bfs", "cc"])
+def test_rig_under_the_reference_binary_name(prim):
+    _build()
+    exe = os.path.join(ROOT, "tests", "_bin", "test_" + prim)
+    p = subprocess.run([exe, "rmat", "--rmat_scale=12", "--rmat_edgefactor=8"], capture_output=True, text=True, timeout=600)
+    assert p.returncode == 0, p.stdout[-2000:] + p.stderr[-2000:]
+    assert "TEST PASSED" in p.stdout and "INCORRECT" not in p.stdout
 
 
 @pytest.mark.gpu
